@@ -1,0 +1,148 @@
+/* rtrt.h — C ABI of the B200-native hot path (LBVH build -> BVH traversal / path trace -> denoise).
+ *
+ * This is the drop-in boundary for the per-frame GPU hot path of wangkepfe/Real-Time-Ray-Tracing.
+ * The reference has no FFI layer: its boundary is the C++ class `RayTracer` (src/kernel.cuh:431-621)
+ * and the kernels it launches.  Every entry point below names the reference interface it replaces
+ * (file:line relative to the reference root).  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions
+ *   - every function returns 0 (RTRT_OK) or a negative rtrt_status; nothing exits or aborts
+ *     (the reference's GpuErrorCheck prints and exit()s: src/cudaError.cuh:6-13);
+ *   - one context per GPU; a context is not thread-safe, distinct contexts are independent;
+ *   - all work is enqueued on the context's stream; only rtrt_sync, rtrt_get_timings and the
+ *     *_host entry points synchronise with the host;
+ *   - device pointers returned by rtrt_get_buffer are borrowed, valid until the next rtrt_set_mesh*
+ *     or rtrt_destroy.
+ */
+#ifndef RTRT_H
+#define RTRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTRT_ABI_VERSION 1
+
+typedef enum rtrt_status {
+    RTRT_OK = 0,
+    RTRT_ERR_ARG = -1,       /* bad argument */
+    RTRT_ERR_CUDA = -2,      /* a CUDA call failed; see rtrt_last_error */
+    RTRT_ERR_CAPACITY = -3,  /* size outside supported range (reference: assert, src/init.cu:100-101,126) */
+    RTRT_ERR_STATE = -4,     /* call order (e.g. traverse before build) */
+    RTRT_ERR_IO = -5,        /* file / parse error */
+    RTRT_ERR_NCCL = -6
+} rtrt_status;
+
+typedef struct rtrt_ctx rtrt_ctx;
+
+/* GlobalSettings (src/globalSettings.h:5-22) as loaded by LoadConfig (src/configLoader.cpp:5-27).
+ * Same keys, same defaults; `[optimziation]` is the (misspelt) table name the reference reads. */
+typedef struct rtrt_config {
+    int32_t width, height;                 /* [resolution] width,height       default 1920x1080 */
+    char    inputMeshFileName[256];        /* [file]                                             */
+    char    inputTextureFileNames[4][256]; /* [file] (first 4 entries kept)                      */
+    int32_t numInputTextureFileNames;
+    int32_t loadCameraAtInit;              /* [file] default false                               */
+    char    inputCameraFileName[256];
+    char    cameraSaveFileName[256];
+    int32_t useDynamicResolution;          /* [optimziation] default true                        */
+    float   targetFps;                     /* default 60                                         */
+    int32_t maxWidth, maxHeight;           /* default 3840x2160                                  */
+    int32_t minWidth, minHeight;           /* default 640x480                                    */
+} rtrt_config;
+
+/* Ray (src/geometry.h:40-50) and the observable result of one TraverseBvh call (src/traverse.h:107-125). */
+typedef struct rtrt_ray { float orig[3]; float pad16; float dir[3]; float pad32; } rtrt_ray;
+typedef struct rtrt_hit {
+    float   t;    /* RayMax = 1e11 on miss (src/kernel.cuh:69)                                   */
+    float   u, v; /* barycentrics as left by RayTriangleWatertight (src/geometry.cuh:406-472)    */
+    int32_t tri;  /* objectIdx = batch*1024 + batch-local triangle id; -1 on miss                */
+} rtrt_hit;
+
+/* Per-stage device times of the most recent call of each stage, CUDA events on the context stream
+ * (replaces Timer/ScopeTimer, src/timer.h:7-99). */
+typedef struct rtrt_timings {
+    float build_bvh_ms, traverse_ms, pathtrace_ms, denoise_ms;
+    uint64_t kernel_launches;     /* kernels launched by this library since rtrt_create */
+    uint64_t rays_traced;         /* TraverseBvh calls executed by the last pathtrace / traverse */
+} rtrt_timings;
+
+/* Buffers observable through rtrt_get_buffer.  The first block are the DebugPrintFile observation
+ * points of src/bvh.cu:15-96; the second block are the Buffer2DName surfaces on the path
+ * (src/kernel.cuh:286-330, src/init.cu:473-500) exposed as linear device buffers. */
+typedef enum rtrt_buffer {
+    RTRT_BUF_TRIANGLES = 0,      /* Triangle[B*1024]   128 B each  (triangles.csv)            */
+    RTRT_BUF_AABBS,              /* AABB[B*1024]        24 B       (aabbs.csv)                */
+    RTRT_BUF_MORTON_PRESORT,     /* uint32[B*1024]  (morton.csv)  only with keep_presort=1    */
+    RTRT_BUF_MORTON,             /* uint32[B*1024]  sorted        (morton2.csv)               */
+    RTRT_BUF_REORDER_IDX,        /* uint32[B*1024]                (reorderIdx.csv)            */
+    RTRT_BUF_BVH_NODES,          /* BVHNode[B*1024]     64 B      (bvhNodes.csv)              */
+    RTRT_BUF_TLAS_AABBS,         /* AABB[Bp]                      (TLAS_aabbs.csv)            */
+    RTRT_BUF_TLAS_MORTON_PRESORT,/* uint32[Bp]                    (TLAS_morton.csv)           */
+    RTRT_BUF_TLAS_MORTON,        /* uint32[Bp]                    (TLAS_morton2.csv)          */
+    RTRT_BUF_TLAS_REORDER_IDX,   /* uint32[Bp]                    (TLAS_reorderIdx.csv)       */
+    RTRT_BUF_TLAS_BVH_NODES,     /* BVHNode[Bp]                   (TLAS_bvhNodes.csv)         */
+    RTRT_BUF_COUNT_STAGE1
+} rtrt_buffer;
+
+/* ---- lifetime: RayTracer::RayTracer / init / cleanup (src/kernel.cuh:435-449, src/init.cu:53, :601-663) ---- */
+int rtrt_create(const rtrt_config* cfg_or_null, int device, rtrt_ctx** out);
+int rtrt_destroy(rtrt_ctx* ctx);
+const char* rtrt_last_error(const rtrt_ctx* ctx);
+int rtrt_abi_version(void);
+
+/* ---- config: LoadConfig (src/configLoader.cpp:5-27); path is a parameter instead of the fixed
+ *      "resources/config.toml".  Missing keys take the reference defaults. ---- */
+int rtrt_config_defaults(rtrt_config* out);
+int rtrt_load_config_toml(const char* path, rtrt_config* out);
+
+/* ---- mesh: the upload block of RayTracer::init (src/init.cu:83-150).  Host arrays are copied, never
+ *      retained.  pos/nrm: V x 3 floats (Float3), idx: N x 3 uint32.  nrm may be NULL: smooth normals are
+ *      then generated on the device with GenerateSmoothNormals semantics (src/kernel.cu:228-257).
+ *      Capacity: 1 <= N; the reference's caps (N <= 1M, < 1024 batches: src/kernel.cuh:54,
+ *      src/init.cu:126) are lifted — see DESIGN.md "generalisation rule". ---- */
+int rtrt_set_mesh(rtrt_ctx* ctx, const float* pos, const float* nrm_or_null, const uint32_t* idx,
+                  uint32_t num_vertices, uint32_t num_triangles);
+/* Same, with inputs already resident in device memory (dynamic geometry: the caller animates the
+ * vertex buffer in place every frame, cf. MeshDisplace src/kernel.cu:139-226).  Pointers are borrowed. */
+int rtrt_set_mesh_device(rtrt_ctx* ctx, const float* d_pos, const float* d_nrm, const uint32_t* d_idx,
+                         uint32_t num_vertices, uint32_t num_triangles);
+/* Mesh file of LoadScene-era format `uint32 triCount; Triangle[triCount]` (src/init.cu:28-50,
+ * tool/meshProcessor.cpp:204-208), 128-byte triangles. */
+int rtrt_set_mesh_bin(rtrt_ctx* ctx, const char* path);
+
+/* ---- options ---- */
+int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
+/*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
+ *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
+ *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)                      */
+
+/* ---- stage 1: RayTracer::BuildBvhLevel1 + BuildBvhLevel2 (src/bvh.cu:7-97) ---- */
+int rtrt_build_bvh(rtrt_ctx* ctx);
+
+/* ---- stage 2 (traversal only): TraverseBvh (src/traverse.h:107-253) with the state initialisation of
+ *      RaySceneIntersect (src/traverse.cuh:86-101), one call per ray.  any_hit != 0 stops at the first
+ *      accepted triangle (shadow-ray query; the reference classifies after a closest-hit,
+ *      src/traverse.cuh:37-48).  d_rays / d_hits are DEVICE pointers. ---- */
+int rtrt_traverse(rtrt_ctx* ctx, const rtrt_ray* d_rays, uint32_t n, rtrt_hit* d_hits, int any_hit);
+/* Same through HOST buffers (H2D of rays, traversal, D2H of hits, synchronous). */
+int rtrt_traverse_host(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_hit* h_hits, int any_hit);
+
+/* ---- observation points: GetBuffer2D (src/kernel.cuh:455) + the DebugPrintFile dumps (src/bvh.cu) ---- */
+int rtrt_get_buffer(rtrt_ctx* ctx, int which /* rtrt_buffer */, void** dptr, size_t* bytes);
+/* convenience: synchronous copy of a buffer to host memory (dst must hold *bytes) */
+int rtrt_read_buffer(rtrt_ctx* ctx, int which, void* dst, size_t dst_bytes);
+
+int rtrt_get_counts(rtrt_ctx* ctx, uint32_t* num_triangles, uint32_t* num_batches, uint32_t* num_batches_padded);
+int rtrt_sync(rtrt_ctx* ctx);
+int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out);   /* synchronises the stream */
+/* the cudaStream_t all work is enqueued on, as an opaque pointer (for event timing by the caller) */
+void* rtrt_get_stream(rtrt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTRT_H */

@@ -1,0 +1,2 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  Parity status: UNPINNED (see oracle/orc_types.h).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this."""

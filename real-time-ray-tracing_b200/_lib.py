@@ -1,0 +1,83 @@
+"""ctypes binding of the C ABI declared in include/rtrt.h.
+
+The library is the product: there is no Python/NumPy/CPU fallback.  If librtrt.so is missing or does
+not load, importing this module raises — loudly, on purpose.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librtrt.so")
+
+RTRT_OK = 0
+STATUS_NAMES = {0: "RTRT_OK", -1: "RTRT_ERR_ARG", -2: "RTRT_ERR_CUDA", -3: "RTRT_ERR_CAPACITY",
+                -4: "RTRT_ERR_STATE", -5: "RTRT_ERR_IO", -6: "RTRT_ERR_NCCL"}
+
+# rtrt_buffer
+BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES, \
+    BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES = range(11)
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32),
+        ("inputMeshFileName", C.c_char * 256),
+        ("inputTextureFileNames", (C.c_char * 256) * 4),
+        ("numInputTextureFileNames", C.c_int32),
+        ("loadCameraAtInit", C.c_int32),
+        ("inputCameraFileName", C.c_char * 256),
+        ("cameraSaveFileName", C.c_char * 256),
+        ("useDynamicResolution", C.c_int32),
+        ("targetFps", C.c_float),
+        ("maxWidth", C.c_int32), ("maxHeight", C.c_int32),
+        ("minWidth", C.c_int32), ("minHeight", C.c_int32),
+    ]
+
+
+class Timings(C.Structure):
+    _fields_ = [("build_bvh_ms", C.c_float), ("traverse_ms", C.c_float), ("pathtrace_ms", C.c_float),
+                ("denoise_ms", C.c_float), ("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64)]
+
+
+# every symbol include/rtrt.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "rtrt_abi_version": (C.c_int, []),
+    "rtrt_create": (C.c_int, [C.POINTER(Config), C.c_int, C.POINTER(C.c_void_p)]),
+    "rtrt_destroy": (C.c_int, [C.c_void_p]),
+    "rtrt_last_error": (C.c_char_p, [C.c_void_p]),
+    "rtrt_config_defaults": (C.c_int, [C.POINTER(Config)]),
+    "rtrt_load_config_toml": (C.c_int, [C.c_char_p, C.POINTER(Config)]),
+    "rtrt_set_mesh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
+    "rtrt_set_mesh_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
+    "rtrt_set_mesh_bin": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_set_option_i": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
+    "rtrt_build_bvh": (C.c_int, [C.c_void_p]),
+    "rtrt_traverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int]),
+    "rtrt_traverse_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int]),
+    "rtrt_get_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "rtrt_read_buffer": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
+    "rtrt_get_counts": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "rtrt_sync": (C.c_int, [C.c_void_p]),
+    "rtrt_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
+    "rtrt_get_stream": (C.c_void_p, [C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen librtrt.so and bind every declared symbol.  Raises if the library is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: the CUDA extension is not built. Run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback).")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)      # AttributeError if a declared symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

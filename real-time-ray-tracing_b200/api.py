@@ -1,0 +1,171 @@
+"""Host-side mirror of the reference's `RayTracer` facade (src/kernel.cuh:431-621) over the C ABI.
+
+Method names follow the reference (`init`, `BuildBvhLevel1/2` folded into `build_bvh`, `cleanup`,
+`GetBuffer2D` -> `read_buffer`), arguments keep their meaning, errors are raised as `RtrtError`
+carrying the rtrt_status code instead of the reference's print-and-exit (src/cudaError.cuh:6-13).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+TRIANGLE_DTYPE = np.dtype([  # src/geometry.h:52-97, 128 bytes
+    ("v1", "<f4", 3), ("w1", "<f4"), ("v2", "<f4", 3), ("w2", "<f4"), ("v3", "<f4", 3), ("w3", "<f4"),
+    ("v4", "<f4", 3), ("w4", "<f4"), ("n1", "<f4", 3), ("u1", "<f4"), ("n2", "<f4", 3), ("u2", "<f4"),
+    ("n3", "<f4", 3), ("u3", "<f4"), ("n4", "<f4", 3), ("u4", "<f4")])
+AABB_DTYPE = np.dtype([("min", "<f4", 3), ("max", "<f4", 3)])  # src/geometry.h:14-33
+BVHNODE_DTYPE = np.dtype([  # src/geometry.h:138-151 + src/bvhNode.cuh:5-13, 64 bytes
+    ("box1maxX", "<f4"), ("box1maxY", "<f4"), ("box1maxZ", "<f4"), ("box2minX", "<f4"),
+    ("box1minX", "<f4"), ("box1minY", "<f4"), ("box1minZ", "<f4"), ("box2minY", "<f4"),
+    ("box2maxX", "<f4"), ("box2maxY", "<f4"), ("box2maxZ", "<f4"), ("box2minZ", "<f4"),
+    ("idxLeft", "<u4"), ("idxRight", "<u4"), ("isLeftLeaf", "<u4"), ("isRightLeaf", "<u4")])
+RAY_DTYPE = np.dtype([("orig", "<f4", 3), ("pad16", "<f4"), ("dir", "<f4", 3), ("pad32", "<f4")])  # src/geometry.h:40-50
+HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("tri", "<i4")])
+assert TRIANGLE_DTYPE.itemsize == 128 and AABB_DTYPE.itemsize == 24 and BVHNODE_DTYPE.itemsize == 64
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
+
+BUFFER_DTYPES = {
+    L.BUF_TRIANGLES: TRIANGLE_DTYPE, L.BUF_AABBS: AABB_DTYPE, L.BUF_MORTON_PRESORT: np.dtype("<u4"),
+    L.BUF_MORTON: np.dtype("<u4"), L.BUF_REORDER_IDX: np.dtype("<u4"), L.BUF_BVH_NODES: BVHNODE_DTYPE,
+    L.BUF_TLAS_AABBS: AABB_DTYPE, L.BUF_TLAS_MORTON_PRESORT: np.dtype("<u4"), L.BUF_TLAS_MORTON: np.dtype("<u4"),
+    L.BUF_TLAS_REORDER_IDX: np.dtype("<u4"), L.BUF_TLAS_BVH_NODES: BVHNODE_DTYPE,
+}
+
+RAY_MAX = np.float32(10e10)
+
+
+class RtrtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{L.STATUS_NAMES.get(code, code)}: {msg}")
+        self.code = code
+
+
+def load_config(path):
+    """LoadConfig (src/configLoader.cpp:5-27) with the path as a parameter."""
+    lib = L.load()
+    cfg = L.Config()
+    rc = lib.rtrt_load_config_toml(str(path).encode(), C.byref(cfg))
+    if rc:
+        raise RtrtError(rc, f"cannot load {path}")
+    return cfg
+
+
+def config_defaults():
+    lib = L.load()
+    cfg = L.Config()
+    lib.rtrt_config_defaults(C.byref(cfg))
+    return cfg
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class RayTracer:
+    """One context per GPU.  `RayTracer(w, h).init()` then `set_mesh` / `build_bvh` / `traverse` ..."""
+
+    def __init__(self, screenWidth=1920, screenHeight=1080, device=0, config=None):
+        self._lib = L.load()
+        self._h = C.c_void_p()
+        self._cfg = config if config is not None else config_defaults()
+        if config is None:
+            self._cfg.width, self._cfg.height = screenWidth, screenHeight
+        self._device = device
+
+    # -- lifetime ---------------------------------------------------------------------------
+    def init(self):
+        if self._h:
+            return self
+        rc = self._lib.rtrt_create(C.byref(self._cfg), self._device, C.byref(self._h))
+        if rc:
+            self._h = C.c_void_p()
+            raise RtrtError(rc, "rtrt_create failed (no CUDA device? there is no CPU fallback)")
+        return self
+
+    def cleanup(self):
+        if self._h:
+            self._lib.rtrt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self.init()
+
+    def __exit__(self, *a):
+        self.cleanup()
+
+    def __del__(self):
+        try:
+            self.cleanup()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc:
+            raise RtrtError(rc, (self._lib.rtrt_last_error(self._h) or b"").decode())
+
+    # -- inputs -----------------------------------------------------------------------------
+    def set_mesh(self, pos, idx, nrm=None):
+        pos = np.ascontiguousarray(pos, dtype=np.float32).reshape(-1, 3)
+        idx = np.ascontiguousarray(idx, dtype=np.uint32).reshape(-1, 3)
+        if nrm is not None:
+            nrm = np.ascontiguousarray(nrm, dtype=np.float32).reshape(-1, 3)
+            assert nrm.shape == pos.shape
+        self._check(self._lib.rtrt_set_mesh(self._h, _ptr(pos), _ptr(nrm) if nrm is not None else None, _ptr(idx),
+                                            pos.shape[0], idx.shape[0]))
+
+    def set_mesh_device(self, d_pos, d_nrm, d_idx, num_vertices, num_triangles):
+        """Device-resident inputs (ints = device addresses, e.g. torch_tensor.data_ptr()); borrowed."""
+        self._check(self._lib.rtrt_set_mesh_device(self._h, C.c_void_p(d_pos), C.c_void_p(d_nrm), C.c_void_p(d_idx),
+                                                   num_vertices, num_triangles))
+
+    def set_mesh_bin(self, path):
+        self._check(self._lib.rtrt_set_mesh_bin(self._h, str(path).encode()))
+
+    def set_option(self, name, value):
+        self._check(self._lib.rtrt_set_option_i(self._h, name.encode(), int(value)))
+
+    # -- stages -----------------------------------------------------------------------------
+    def build_bvh(self):
+        """BuildBvhLevel1 + BuildBvhLevel2 (src/bvh.cu:7-97)."""
+        self._check(self._lib.rtrt_build_bvh(self._h))
+
+    def traverse(self, rays, any_hit=False):
+        """Host-buffer traversal: rays = structured RAY_DTYPE array -> HIT_DTYPE array."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.empty(rays.shape[0], dtype=HIT_DTYPE)
+        self._check(self._lib.rtrt_traverse_host(self._h, _ptr(rays), rays.shape[0], _ptr(hits), int(any_hit)))
+        return hits
+
+    def traverse_device(self, d_rays, n, d_hits, any_hit=False):
+        self._check(self._lib.rtrt_traverse(self._h, C.c_void_p(d_rays), n, C.c_void_p(d_hits), int(any_hit)))
+
+    # -- observation points -------------------------------------------------------------------
+    def counts(self):
+        a, b, c = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self._check(self._lib.rtrt_get_counts(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def get_buffer(self, which):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._check(self._lib.rtrt_get_buffer(self._h, which, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def read_buffer(self, which):
+        _, nbytes = self.get_buffer(which)
+        dt = BUFFER_DTYPES[which]
+        out = np.empty(nbytes // dt.itemsize, dtype=dt)
+        self._check(self._lib.rtrt_read_buffer(self._h, which, _ptr(out), nbytes))
+        return out
+
+    def sync(self):
+        self._check(self._lib.rtrt_sync(self._h))
+
+    def timings(self):
+        t = L.Timings()
+        self._check(self._lib.rtrt_get_timings(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in L.Timings._fields_}
+
+    @property
+    def stream(self):
+        return self._lib.rtrt_get_stream(self._h)

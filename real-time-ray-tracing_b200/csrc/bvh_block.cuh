@@ -1,0 +1,296 @@
+// Block-level building blocks of the LBVH build: every step of one 1024-item segment runs out of
+// shared memory inside ONE CTA (the reference round-trips HBM between three kernels per level:
+// src/bvh.cu:12,29,44).  Shared by the BLAS kernel (one CTA per 1024-triangle batch) and the TLAS
+// kernel (one CTA over <= 1024 batch roots).
+//
+// All arithmetic that decides output bits (AABB padding, Morton scaling, min/max selection) is
+// written with the reference's operation order and compiled with --fmad=false.
+#pragma once
+#include "rtrt_types.h"
+#include <cuda_runtime.h>
+#include <float.h>
+
+namespace rtrt {
+
+constexpr int kSeg = 1024;                 // items per segment (BatchSize)
+constexpr uint32_t kLeafBit = 0x80000000u; // child link flag inside shared memory
+
+// select-style min/max of the reference (src/linearMath.h:25-31); NOT fminf/fmaxf
+__device__ __forceinline__ float sel_min(float a, float b) { return a < b ? a : b; }
+__device__ __forceinline__ float sel_max(float a, float b) { return a > b ? a : b; }
+
+__device__ __forceinline__ AABB aabb_empty() {
+    AABB b; b.min = Float3{FLT_MAX, FLT_MAX, FLT_MAX}; b.max = Float3{-FLT_MAX, -FLT_MAX, -FLT_MAX}; return b;
+}
+__device__ __forceinline__ void aabb_grow(AABB& a, const AABB& b) {
+    a.min.x = sel_min(a.min.x, b.min.x); a.min.y = sel_min(a.min.y, b.min.y); a.min.z = sel_min(a.min.z, b.min.z);
+    a.max.x = sel_max(a.max.x, b.max.x); a.max.y = sel_max(a.max.y, b.max.y); a.max.z = sel_max(a.max.z, b.max.z);
+}
+
+// 10 bits per axis -> 30-bit code, x lowest (src/updateGeometry.cuh:13-27)
+__device__ __forceinline__ uint32_t expand10(uint32_t x) {
+    x = (x | (x << 16)) & 0x030000FFu;
+    x = (x | (x << 8)) & 0x0300F00Fu;
+    x = (x | (x << 4)) & 0x030C30C3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+// src/updateGeometry.cuh:254-258 — cvt.rzi.u32.f32 saturates and maps NaN to 0 (flat axis gives 0/0)
+__device__ __forceinline__ uint32_t morton30(Float3 c, const AABB& box) {
+    float ux = (c.x - box.min.x) / (box.max.x - box.min.x);
+    float uy = (c.y - box.min.y) / (box.max.y - box.min.y);
+    float uz = (c.z - box.min.z) / (box.max.z - box.min.z);
+    return expand10(__float2uint_rz(ux * 1023.0f)) | (expand10(__float2uint_rz(uy * 1023.0f)) << 1) |
+           (expand10(__float2uint_rz(uz * 1023.0f)) << 2);
+}
+
+// Shared-memory working set of one segment.  `scratch` is time-multiplexed:
+//   gather phase : item centres (12 KB) ; sort phase : digit histograms (16 KB) ; refit : node boxes (24 KB)
+struct SegSmem {
+    AABB leafBox[kSeg];                        // 24 KB  per-item boxes, indexed by original (pre-sort) id
+    union {
+        Float3   centre[kSeg];
+        uint16_t hist[32][256];
+        AABB     nodeBox[kSeg];
+    } scratch;                                 // 24 KB
+    uint32_t keys[2][kSeg];                    //  8 KB  ping-pong
+    uint16_t ids[2][kSeg];                     //  4 KB
+    uint32_t childL[kSeg], childR[kSeg];       //  8 KB  link | kLeafBit
+    uint16_t parent[kSeg];                     //  2 KB  parent of internal node
+    uint16_t leafParent[kSeg];                 //  2 KB  parent of the leaf at sorted position p
+    uint32_t arrive[kSeg];                     //  4 KB  refit rendezvous counters
+    uint32_t digitBase[256];                   //  1 KB
+    uint32_t warpSum[8];
+    float    red[6][32];                       //  block AABB reduction
+    AABB     segBox;
+    uint32_t misc[4];
+};
+
+// ---- block-wide AABB reduction (exact; min/max are order independent) ----
+template <int NT>
+__device__ __forceinline__ AABB block_reduce_aabb(SegSmem& s, AABB v) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v.min.x = sel_min(v.min.x, __shfl_xor_sync(0xffffffffu, v.min.x, o));
+        v.min.y = sel_min(v.min.y, __shfl_xor_sync(0xffffffffu, v.min.y, o));
+        v.min.z = sel_min(v.min.z, __shfl_xor_sync(0xffffffffu, v.min.z, o));
+        v.max.x = sel_max(v.max.x, __shfl_xor_sync(0xffffffffu, v.max.x, o));
+        v.max.y = sel_max(v.max.y, __shfl_xor_sync(0xffffffffu, v.max.y, o));
+        v.max.z = sel_max(v.max.z, __shfl_xor_sync(0xffffffffu, v.max.z, o));
+    }
+    if (lane == 0) {
+        s.red[0][warp] = v.min.x; s.red[1][warp] = v.min.y; s.red[2][warp] = v.min.z;
+        s.red[3][warp] = v.max.x; s.red[4][warp] = v.max.y; s.red[5][warp] = v.max.z;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        constexpr int NW = NT / 32;
+        AABB w = aabb_empty();
+        if (lane < NW) {
+            w.min = Float3{s.red[0][lane], s.red[1][lane], s.red[2][lane]};
+            w.max = Float3{s.red[3][lane], s.red[4][lane], s.red[5][lane]};
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            w.min.x = sel_min(w.min.x, __shfl_xor_sync(0xffffffffu, w.min.x, o));
+            w.min.y = sel_min(w.min.y, __shfl_xor_sync(0xffffffffu, w.min.y, o));
+            w.min.z = sel_min(w.min.z, __shfl_xor_sync(0xffffffffu, w.min.z, o));
+            w.max.x = sel_max(w.max.x, __shfl_xor_sync(0xffffffffu, w.max.x, o));
+            w.max.y = sel_max(w.max.y, __shfl_xor_sync(0xffffffffu, w.max.y, o));
+            w.max.z = sel_max(w.max.z, __shfl_xor_sync(0xffffffffu, w.max.z, o));
+        }
+        if (lane == 0) s.segBox = w;
+    }
+    __syncthreads();
+    return s.segBox;
+}
+
+// ---- stable LSD radix sort of the 1024 (key,id) pairs in s.keys[0]/s.ids[0]; 4 passes x 8 bits ----
+// Replaces src/radixSort.cuh:21-246 (8 passes x 4 bits, ballot emulation of match-any, ~80 barriers).
+// Ranking inside a 32-key chunk uses __match_any_sync; chunk histograms are combined by a per-digit
+// column scan (one thread per digit) + one 256-wide block scan.  Result lands back in keys[0]/ids[0].
+template <int NT>
+__device__ __forceinline__ void block_sort_1024(SegSmem& s) {
+    static_assert(NT >= 256 && NT % 32 == 0 && kSeg % NT == 0, "block size");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
+    constexpr int CHUNKS_PER_WARP = 32 / NW;            // 32 chunks of 32 keys
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll 1
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = pass * 8;
+        const uint32_t* ksrc = s.keys[pass & 1]; uint32_t* kdst = s.keys[(pass + 1) & 1];
+        const uint16_t* isrc = s.ids[pass & 1];  uint16_t* idst = s.ids[(pass + 1) & 1];
+        uint32_t* h32 = reinterpret_cast<uint32_t*>(&s.scratch.hist[0][0]);
+        for (int i = tid; i < 32 * 256 / 2; i += NT) h32[i] = 0u;
+        __syncthreads();
+        uint32_t key[CHUNKS_PER_WARP], rank[CHUNKS_PER_WARP];
+#pragma unroll
+        for (int r = 0; r < CHUNKS_PER_WARP; ++r) {
+            const int c = warp * CHUNKS_PER_WARP + r;
+            key[r] = ksrc[c * 32 + lane];
+            const uint32_t d = (key[r] >> shift) & 255u;
+            const uint32_t m = __match_any_sync(0xffffffffu, d);
+            rank[r] = __popc(m & lt);
+            if (rank[r] == 0) s.scratch.hist[c][d] = (uint16_t)__popc(m);
+        }
+        __syncthreads();
+        // column scan over the 32 chunks for digit d = tid, then exclusive scan of the 256 totals
+        uint32_t total = 0;
+        if (tid < 256) {
+#pragma unroll 8
+            for (int c = 0; c < 32; ++c) {
+                const uint32_t v = s.scratch.hist[c][tid];
+                s.scratch.hist[c][tid] = (uint16_t)total;
+                total += v;
+            }
+        }
+        uint32_t incl = total;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (tid < 256 && lane == 31) s.warpSum[warp] = incl;
+        __syncthreads();
+        if (tid < 256) {
+            uint32_t base = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) if (w < warp) base += s.warpSum[w];
+            s.digitBase[tid] = base + incl - total;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < CHUNKS_PER_WARP; ++r) {
+            const int c = warp * CHUNKS_PER_WARP + r;
+            const uint32_t d = (key[r] >> shift) & 255u;
+            const uint32_t pos = s.digitBase[d] + s.scratch.hist[c][d] + rank[r];
+            kdst[pos] = key[r];
+            idst[pos] = isrc[c * 32 + lane];
+        }
+        __syncthreads();
+    }
+}
+
+// delta(i,j) of Karras 2012 with the index tie-break for equal keys (the reference's LCP,
+// src/buildBVH.cuh:8-14, has none and emits broken hierarchies when a key occurs 3+ times).
+__device__ __forceinline__ int seg_delta(const uint32_t* keys, int n, int i, uint32_t ki, int j) {
+    if (j < 0 || j >= n) return 0;
+    const uint32_t x = ki ^ keys[j];
+    return x ? __clz(x) : 32 + __clz((uint32_t)i ^ (uint32_t)j);
+}
+
+// ---- Karras hierarchy emit over the n sorted keys in s.keys[0] (src/buildBVH.cuh:60-134) ----
+// Leaf links carry the ORIGINAL item id (s.ids[0][gamma] = reorderIdx) like the reference.
+template <int NT>
+__device__ __forceinline__ void block_karras(SegSmem& s, int n) {
+    const uint32_t* keys = s.keys[0];
+    for (int i = threadIdx.x; i < n - 1; i += NT) {
+        const uint32_t ki = keys[i];
+        const int dl = seg_delta(keys, n, i, ki, i - 1), dr = seg_delta(keys, n, i, ki, i + 1);
+        const int d = (dr - dl) >= 0 ? 1 : -1;
+        const int dmin = seg_delta(keys, n, i, ki, i - d);
+        int lmax = 2;
+        while (seg_delta(keys, n, i, ki, i + lmax * d) > dmin) lmax <<= 1;
+        int l = 0;
+        for (int t = lmax >> 1; t >= 1; t >>= 1)
+            if (seg_delta(keys, n, i, ki, i + (l + t) * d) > dmin) l += t;
+        const int j = i + l * d;
+        const int dnode = seg_delta(keys, n, i, ki, j);
+        int sp = 0;
+        for (int div = 2;; div <<= 1) {
+            const int t = (l + div - 1) / div;
+            if (seg_delta(keys, n, i, ki, i + (sp + t) * d) > dnode) sp += t;
+            if (t <= 1) break;
+        }
+        const int gamma = i + sp * d + min(d, 0);
+        if (min(i, j) == gamma) { s.childL[i] = (uint32_t)s.ids[0][gamma] | kLeafBit; s.leafParent[gamma] = (uint16_t)i; }
+        else                    { s.childL[i] = (uint32_t)gamma; s.parent[gamma] = (uint16_t)i; }
+        if (max(i, j) == gamma + 1) { s.childR[i] = (uint32_t)s.ids[0][gamma + 1] | kLeafBit; s.leafParent[gamma + 1] = (uint16_t)i; }
+        else                        { s.childR[i] = (uint32_t)(gamma + 1); s.parent[gamma + 1] = (uint16_t)i; }
+    }
+}
+
+__device__ __forceinline__ AABB child_box(const SegSmem& s, uint32_t link) {
+    const volatile AABB* p = (link & kLeafBit) ? &s.leafBox[link & ~kLeafBit] : &s.scratch.nodeBox[link];
+    AABB b;
+    b.min.x = p->min.x; b.min.y = p->min.y; b.min.z = p->min.z;
+    b.max.x = p->max.x; b.max.y = p->max.y; b.max.z = p->max.z;
+    return b;
+}
+
+// ---- bottom-up refit in shared memory (src/buildBVH.cuh:138-267): one walker per leaf; the second
+// walker to reach a node merges its children.  Boxes are exact unions => order independent. ----
+template <int NT>
+__device__ __forceinline__ void block_refit(SegSmem& s, int n) {
+    for (int i = threadIdx.x; i < n - 1; i += NT) s.arrive[i] = 0u;
+    __syncthreads();
+    for (int p = threadIdx.x; p < n; p += NT) {
+        uint32_t cur = s.leafParent[p];
+        while (true) {
+            __threadfence_block();
+            if (atomicAdd(&s.arrive[cur], 1u) == 0u) break;      // first arrival: sibling subtree pending
+            __threadfence_block();
+            AABB b = child_box(s, s.childL[cur]);
+            aabb_grow(b, child_box(s, s.childR[cur]));
+            volatile AABB* o = &s.scratch.nodeBox[cur];
+            o->min.x = b.min.x; o->min.y = b.min.y; o->min.z = b.min.z;
+            o->max.x = b.max.x; o->max.y = b.max.y; o->max.z = b.max.z;
+            if (cur == 0u) break;
+            cur = s.parent[cur];
+        }
+    }
+    __syncthreads();
+}
+
+// ---- write the n-1 nodes of the segment: 4 lanes per 64-byte node, one float4 each (coalesced) ----
+template <int NT>
+__device__ __forceinline__ void block_write_nodes(const SegSmem& s, int n, BVHNode* __restrict__ out) {
+    float4* o4 = reinterpret_cast<float4*>(out);
+    for (int e = threadIdx.x; e < (n - 1) * 4; e += NT) {
+        const int i = e >> 2, q = e & 3;
+        const uint32_t L = s.childL[i], R = s.childR[i];
+        float4 v;
+        if (q == 3) {
+            v.x = __uint_as_float(L & ~kLeafBit); v.y = __uint_as_float(R & ~kLeafBit);
+            v.z = __uint_as_float(L >> 31);       v.w = __uint_as_float(R >> 31);
+        } else {
+            const AABB* bl = (L & kLeafBit) ? &s.leafBox[L & ~kLeafBit] : &s.scratch.nodeBox[L];
+            const AABB* br = (R & kLeafBit) ? &s.leafBox[R & ~kLeafBit] : &s.scratch.nodeBox[R];
+            if (q == 0)      v = make_float4(bl->max.x, bl->max.y, bl->max.z, br->min.x);
+            else if (q == 1) v = make_float4(bl->min.x, bl->min.y, bl->min.z, br->min.y);
+            else             v = make_float4(br->max.x, br->max.y, br->max.z, br->min.z);
+        }
+        o4[e] = v;
+    }
+}
+
+// n == 1: src/buildBVH.cuh:31-38 — left box = the only item, right box = the point AABB(0,0)
+__device__ __forceinline__ void write_single_leaf_node(const AABB& b, BVHNode* out) {
+    BVHNode nd;
+    nd.box1maxX = b.max.x; nd.box1maxY = b.max.y; nd.box1maxZ = b.max.z;
+    nd.box1minX = b.min.x; nd.box1minY = b.min.y; nd.box1minZ = b.min.z;
+    nd.box2maxX = nd.box2maxY = nd.box2maxZ = 0.0f; nd.box2minX = nd.box2minY = nd.box2minZ = 0.0f;
+    nd.idxLeft = 0; nd.idxRight = 0; nd.isLeftLeaf = 1; nd.isRightLeaf = 1;
+    *out = nd;
+}
+
+// sort -> publish sorted keys/reorderIdx -> Karras -> refit -> nodes, for a segment whose keys/ids and
+// leafBox are already in shared memory.
+template <int NT>
+__device__ __forceinline__ void block_build_segment(SegSmem& s, int n, uint32_t* __restrict__ gKeys,
+                                                    uint32_t* __restrict__ gReorder, BVHNode* __restrict__ gNodes) {
+    block_sort_1024<NT>(s);
+    for (int i = threadIdx.x; i < kSeg; i += NT) { gKeys[i] = s.keys[0][i]; gReorder[i] = s.ids[0][i]; }
+    if (n == 1) {
+        if (threadIdx.x == 0) write_single_leaf_node(s.leafBox[0], gNodes);
+        return;
+    }
+    block_karras<NT>(s, n);
+    __syncthreads();
+    block_refit<NT>(s, n);
+    block_write_nodes<NT>(s, n, gNodes);
+}
+
+}  // namespace rtrt

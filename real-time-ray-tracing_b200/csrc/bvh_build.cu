@@ -1,0 +1,177 @@
+// Stage 1 — two-level LBVH build for sm_100a.
+//
+// Replaces src/bvh.cu:7-97 (BuildBvhLevel1/2 = 6 dependent launches: UpdateSceneGeometry, RadixSort,
+// BuildLBVH, UpdateTLAS, RadixSort, BuildLBVH) with ONE launch when the scene has <= 1024 batches:
+//   * one CTA per 1024-triangle batch does gather -> Triangle/AABB emit -> batch AABB -> Morton30 ->
+//     stable radix sort -> Karras emit -> refit -> node write entirely out of shared memory, so keys,
+//     boxes and links never round-trip HBM between steps;
+//   * the last CTA to retire (device-wide ticket) builds the TLAS over the batch roots in the same launch.
+// Output arrays are the reference's (src/init.cu:159-187): Triangle[ ], AABB[ ], morton[ ] (sorted),
+// reorderIdx[ ], BVHNode[ ] + the TLAS equivalents, bit-identical to the reference's for scenes
+// without 3+-fold duplicate keys inside a segment (see bvh_block.cuh: seg_delta).
+#include "bvh_block.cuh"
+#include "context.h"
+
+namespace rtrt {
+
+constexpr int kBuildThreads = 256;
+
+struct BuildParams {
+    const float* __restrict__ pos;       // V x 3
+    const float* __restrict__ nrm;       // V x 3
+    const uint32_t* __restrict__ idx;    // N x 3
+    uint32_t numTris;                    // N
+    uint32_t numBatches;                 // B
+    Triangle* triangles; AABB* aabbs; uint32_t* morton; uint32_t* reorderIdx; BVHNode* nodes;
+    uint32_t* mortonPre;                 // optional debug observation point (may be null)
+    AABB* tlasAabbs; uint32_t* tlasMorton; uint32_t* tlasReorderIdx; BVHNode* tlasNodes;
+    uint32_t* tlasMortonPre;             // optional
+    uint32_t* ticket;                    // device-wide retirement counter (zeroed before launch)
+    int fuseTlas;                        // 1: last CTA builds the TLAS (B <= 1024)
+};
+
+__device__ __forceinline__ Float3 ld3(const float* __restrict__ p, uint32_t i) {
+    return Float3{__ldg(p + 3 * (size_t)i), __ldg(p + 3 * (size_t)i + 1), __ldg(p + 3 * (size_t)i + 2)};
+}
+
+// ---- TLAS over B <= 1024 batch roots, executed by one CTA (src/updateGeometry.cuh:267-364 + sort + emit) ----
+template <int NT>
+__device__ void tlas_build_block(SegSmem& s, const BuildParams& p) {
+    const int B = (int)p.numBatches;
+    AABB mine = aabb_empty();
+    for (int k = threadIdx.x; k < kSeg; k += NT) {
+        if (k < B) {
+            // root of BLAS k = nodes[1024*k]; written by other CTAs of this launch in the fused path -> L2 loads
+            const float4* r4 = reinterpret_cast<const float4*>(p.nodes + (size_t)kSeg * k);
+            const float4 a = __ldcg(r4), b = __ldcg(r4 + 1), c = __ldcg(r4 + 2);
+            AABB m;                                             // AABBCompact::GetMerged (src/geometry.h:107-110)
+            m.max.x = sel_max(a.x, c.x); m.max.y = sel_max(a.y, c.y); m.max.z = sel_max(a.z, c.z);
+            m.min.x = sel_min(b.x, a.w); m.min.y = sel_min(b.y, b.w); m.min.z = sel_min(b.z, c.w);
+            s.leafBox[k] = m;
+            s.scratch.centre[k] = Float3{(m.max.x + m.min.x) / 2.0f, (m.max.y + m.min.y) / 2.0f, (m.max.z + m.min.z) / 2.0f};
+            p.tlasAabbs[k] = m;
+            aabb_grow(mine, m);
+        }
+    }
+    const AABB scene = block_reduce_aabb<NT>(s, mine);
+    for (int k = threadIdx.x; k < kSeg; k += NT) {
+        const uint32_t key = (k < B) ? morton30(s.scratch.centre[k], scene) : 0xFFFFFFFFu;
+        s.keys[0][k] = key; s.ids[0][k] = (uint16_t)k;
+        if (p.tlasMortonPre) p.tlasMortonPre[k] = key;
+    }
+    __syncthreads();
+    block_build_segment<NT>(s, B, p.tlasMorton, p.tlasReorderIdx, p.tlasNodes);
+}
+
+// ---- one CTA per batch ----
+template <int NT>
+__global__ void __launch_bounds__(NT) k_build_blas(const BuildParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SegSmem& s = *reinterpret_cast<SegSmem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
+    const uint32_t b = blockIdx.x;
+    const uint32_t base = b * kSeg;
+    const uint32_t count = (b == p.numBatches - 1) ? (p.numTris - kSeg * (p.numBatches - 1)) : (uint32_t)kSeg;  // src/init.cu:129-130
+    const uint32_t active = (count + 3u) & ~3u;     // src/updateGeometry.cuh:93 : threads own 4 items each
+
+    // ---- gather + Triangle emit: 8 lanes per triangle, one 16-byte row each -> 512 contiguous bytes per warp store.
+    // rows: 0..2 = v1..v3, 3 = v4 (unused), 4..6 = n1..n3, 7 = n4 (unused)          src/updateGeometry.cuh:131-137
+    const int sub = lane & 7, grp = lane >> 3;
+    float4* tri4 = reinterpret_cast<float4*>(p.triangles + base);
+    AABB mine = aabb_empty();
+#pragma unroll 4
+    for (int it = 0; it < kSeg / (NW * 4); ++it) {
+        const uint32_t i = (uint32_t)(it * NW + warp) * 4u + grp;          // batch-local item
+        const uint32_t g = base + i;
+        const bool on = i < active;
+        Float3 val{0.0f, 0.0f, 0.0f};
+        if (on && (sub & 3) != 3) {
+            const uint32_t vid = (g < p.numTris) ? __ldg(p.idx + 3 * (size_t)g + (sub & 3)) : 0u;   // pad indices are 0 (src/init.cu:103-115)
+            val = ld3(sub < 4 ? p.pos : p.nrm, vid);
+        }
+        if (on) tri4[(size_t)i * 8 + sub] = make_float4(val.x, val.y, val.z, 0.0f);
+        const int l0 = lane & ~7;
+        const Float3 v1{__shfl_sync(0xffffffffu, val.x, l0), __shfl_sync(0xffffffffu, val.y, l0), __shfl_sync(0xffffffffu, val.z, l0)};
+        const Float3 v2{__shfl_sync(0xffffffffu, val.x, l0 + 1), __shfl_sync(0xffffffffu, val.y, l0 + 1), __shfl_sync(0xffffffffu, val.z, l0 + 1)};
+        const Float3 v3{__shfl_sync(0xffffffffu, val.x, l0 + 2), __shfl_sync(0xffffffffu, val.y, l0 + 2), __shfl_sync(0xffffffffu, val.z, l0 + 2)};
+        if (on && sub == 0) {
+            AABB bx;                                                                          // :172-177
+            bx.min.x = sel_min(v1.x, sel_min(v2.x, v3.x)); bx.min.y = sel_min(v1.y, sel_min(v2.y, v3.y)); bx.min.z = sel_min(v1.z, sel_min(v2.z, v3.z));
+            bx.max.x = sel_max(v1.x, sel_max(v2.x, v3.x)); bx.max.y = sel_max(v1.y, sel_max(v2.y, v3.y)); bx.max.z = sel_max(v1.z, sel_max(v2.z, v3.z));
+            const float eps = 1.1920928955078125e-07f;                                        // MachineEpsilon()
+            bx.max.x = bx.min.x + sel_max(bx.max.x - bx.min.x, eps * bx.max.x);
+            bx.max.y = bx.min.y + sel_max(bx.max.y - bx.min.y, eps * bx.max.y);
+            bx.max.z = bx.min.z + sel_max(bx.max.z - bx.min.z, eps * bx.max.z);
+            s.leafBox[i] = bx;
+            s.scratch.centre[i] = Float3{((v1.x + v2.x) + v3.x) / 3.0f, ((v1.y + v2.y) + v3.y) / 3.0f, ((v1.z + v2.z) + v3.z) / 3.0f};  // :180
+            aabb_grow(mine, bx);
+        }
+    }
+    const AABB batchBox = block_reduce_aabb<NT>(s, mine);     // barriers inside also publish leafBox/centre
+
+    // ---- per-item AABB array (24 KB contiguous per batch) + Morton keys ----
+    {
+        const float* lb = reinterpret_cast<const float*>(s.leafBox);
+        float* ga = reinterpret_cast<float*>(p.aabbs + base);
+        for (uint32_t e = tid; e < active * 6u; e += NT) ga[e] = lb[e];
+    }
+    for (int i = tid; i < kSeg; i += NT) {
+        const uint32_t key = ((uint32_t)i < active) ? morton30(s.scratch.centre[i], batchBox) : 0xFFFFFFFFu;  // src/kernel.cu:279
+        s.keys[0][i] = key; s.ids[0][i] = (uint16_t)i;
+        if (p.mortonPre) p.mortonPre[base + i] = key;
+    }
+    __syncthreads();
+
+    block_build_segment<NT>(s, (int)count, p.morton + base, p.reorderIdx + base, p.nodes + base);
+
+    // ---- fused TLAS: last CTA to retire builds the top level in the same launch ----
+    if (p.fuseTlas) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s.misc[0] = atomicAdd(p.ticket, 1u);
+        __syncthreads();
+        if (s.misc[0] == p.numBatches - 1) {
+            __threadfence();
+            tlas_build_block<NT>(s, p);
+        }
+    }
+}
+
+template <int NT>
+__global__ void __launch_bounds__(NT) k_build_tlas(const BuildParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    tlas_build_block<NT>(*reinterpret_cast<SegSmem*>(smem_raw), p);
+}
+
+// ------------------------------------------------------------------------------------------------
+int launch_build_bvh(Context& c) {
+    if (c.numTris == 0) return c.fail(RTRT_ERR_STATE, "rtrt_build_bvh: no mesh set");
+    BuildParams p{};
+    p.pos = c.dPos; p.nrm = c.dNrm; p.idx = c.dIdx; p.numTris = c.numTris; p.numBatches = c.numBatches;
+    p.triangles = c.dTriangles; p.aabbs = c.dAabbs; p.morton = c.dMorton; p.reorderIdx = c.dReorderIdx; p.nodes = c.dNodes;
+    p.mortonPre = c.keepPresortMorton ? c.dMortonPre : nullptr;
+    p.tlasAabbs = c.dTlasAabbs; p.tlasMorton = c.dTlasMorton; p.tlasReorderIdx = c.dTlasReorderIdx; p.tlasNodes = c.dTlasNodes;
+    p.tlasMortonPre = c.keepPresortMorton ? c.dTlasMortonPre : nullptr;
+    p.ticket = c.dTicket;
+    p.fuseTlas = (c.numBatches <= (uint32_t)kSeg) ? 1 : 0;
+
+    static bool attrSet = false;
+    const size_t smem = sizeof(SegSmem);
+    if (!attrSet) {
+        RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RTRT_CUDA(c, cudaFuncSetAttribute(k_build_tlas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attrSet = true;
+    }
+    RTRT_CUDA(c, cudaMemsetAsync(c.dTicket, 0, sizeof(uint32_t), c.stream));
+    k_build_blas<kBuildThreads><<<c.numBatches, kBuildThreads, smem, c.stream>>>(p);
+    c.launches += 1;
+    if (!p.fuseTlas) {
+        int rc = launch_build_tlas_global(c);     // B > 1024: multi-CTA top level (bvh_tlas_global.cu)
+        if (rc) return rc;
+    }
+    RTRT_CUDA(c, cudaGetLastError());
+    return RTRT_OK;
+}
+
+}  // namespace rtrt

@@ -1,0 +1,109 @@
+"""GPU parity tests, stage 1 (LBVH build) — CUDA path through the C ABI vs the CPU oracle, bit-exact on
+every observation point of src/bvh.cu (triangles, aabbs, morton pre/post sort, reorderIdx, bvhNodes, TLAS_*)."""
+import numpy as np
+import pytest
+
+from helpers import assert_bvh_equal, read_all_stage1, tree_leaves
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rt(pkg):
+    r = pkg.RayTracer(256, 256).init()
+    r.set_option("keep_presort_morton", 1)
+    yield r
+    r.cleanup()
+
+
+@pytest.mark.parametrize("n_tris", [1, 2, 3, 4, 5, 1023, 1024, 1025, 2049, 5000, 10240])
+def test_build_matches_oracle_small(rt, pkg, orc, n_tris):
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=3)
+    idx = idx[:n_tris]
+    rt.set_mesh(pos, idx, nrm)
+    rt.build_bvh()
+    ob = orc.build_bvh(pos, nrm, idx)
+    assert rt.counts() == (ob.num_tris, ob.num_batches, ob.num_batches_padded)
+    assert_bvh_equal(read_all_stage1(rt, pkg, presort=True), ob, pkg)
+
+
+def test_build_is_deterministic_and_repeatable(rt, pkg):
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=9)
+    rt.set_mesh(pos, idx, nrm)
+    rt.build_bvh()
+    a = read_all_stage1(rt, pkg)
+    for _ in range(3):
+        rt.build_bvh()           # per-frame rebuild (src/kernel.cu:330-331)
+    b = read_all_stage1(rt, pkg)
+    for k in a:
+        assert a[k].tobytes() == b[k].tobytes()
+
+
+def test_duplicate_keys(rt, pkg, orc):
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    nrm = np.tile(np.array([[0, 0, 1]], np.float32), (3, 1))
+    idx = np.tile(np.array([[0, 1, 2]], np.uint32), (2048, 1))
+    rt.set_mesh(pos, idx, nrm)
+    rt.build_bvh()
+    ob = orc.build_bvh(pos, nrm, idx)
+    bufs = read_all_stage1(rt, pkg, presort=True)
+    assert_bvh_equal(bufs, ob, pkg)
+    assert sorted(tree_leaves(bufs[pkg.BUF_BVH_NODES][:1024], 1024)) == list(range(1024))
+
+
+def test_flat_axis_nan_morton(rt, pkg, orc):
+    # flat z=0 grid (cf. resources/models/test.bin): (c-min)/(max-min) = 0/0 on z -> cvt.rzi.u32.f32(NaN) = 0
+    g = 32
+    xs, ys = np.meshgrid(np.linspace(-1, 1, g + 1, dtype=np.float32), np.linspace(-1, 1, g + 1, dtype=np.float32), indexing="ij")
+    pos = np.stack([xs, ys, np.zeros_like(xs)], -1).reshape(-1, 3)
+    nrm = np.tile(np.array([[0, 0, 1]], np.float32), (pos.shape[0], 1))
+    ii, jj = np.meshgrid(np.arange(g), np.arange(g), indexing="ij")
+    v00 = ii * (g + 1) + jj
+    idx = np.stack([np.stack([v00, v00 + g + 1, v00 + g + 2], -1), np.stack([v00, v00 + g + 2, v00 + 1], -1)], 2).reshape(-1, 3).astype(np.uint32)
+    rt.set_mesh(pos, idx, nrm)
+    rt.build_bvh()
+    ob = orc.build_bvh(pos, nrm, idx)
+    assert_bvh_equal(read_all_stage1(rt, pkg, presort=True), ob, pkg)
+
+
+def test_build_1m_triangles(rt, pkg, orc):
+    """BASELINE config 2 geometry: 1 047 552 triangles = 1023 batches (largest the reference accepts)."""
+    gx, gz = pkg.scenes.TERRAIN_SIZES["C2ref"]
+    pos, nrm, idx = pkg.scenes.terrain(gx, gz, seed=1)
+    rt.set_mesh(pos, idx, nrm)
+    rt.build_bvh()
+    ob = orc.build_bvh(pos, nrm, idx)
+    bufs = read_all_stage1(rt, pkg, presort=True)
+    assert_bvh_equal(bufs, ob, pkg)
+    # size-independent properties
+    m = bufs[pkg.BUF_MORTON].reshape(-1, 1024)
+    assert np.all(m[:, :-1] <= m[:, 1:])
+    ro = np.sort(bufs[pkg.BUF_REORDER_IDX].reshape(-1, 1024), axis=1)
+    assert np.all(ro == np.arange(1024)[None, :])
+    assert sorted(tree_leaves(bufs[pkg.BUF_TLAS_BVH_NODES], 1023)) == list(range(1023))
+
+
+def test_device_resident_mesh(pkg, orc):
+    import torch
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=4)
+    dp = torch.from_numpy(pos).cuda(); dn = torch.from_numpy(nrm).cuda(); di = torch.from_numpy(idx.astype(np.int32)).cuda()
+    with pkg.RayTracer(64, 64) as r:
+        r.set_mesh_device(dp.data_ptr(), dn.data_ptr(), di.data_ptr(), pos.shape[0], idx.shape[0])
+        torch.cuda.synchronize()
+        r.build_bvh()
+        assert_bvh_equal(read_all_stage1(r, pkg), orc.build_bvh(pos, nrm, idx), pkg)
+        # animate the vertex buffer in place and rebuild (dynamic geometry, BASELINE config 3 pattern)
+        dp[:, 1] += 0.5 * torch.sin(0.3 * dp[:, 0] + 1.0)
+        torch.cuda.synchronize()
+        r.build_bvh()
+        assert_bvh_equal(read_all_stage1(r, pkg), orc.build_bvh(dp.cpu().numpy(), nrm, idx), pkg)
+
+
+def test_errors(pkg):
+    with pkg.RayTracer(64, 64) as r:
+        with pytest.raises(pkg.RtrtError) as e:
+            r.build_bvh()
+        assert e.value.code == -4        # RTRT_ERR_STATE: no mesh
+        with pytest.raises(pkg.RtrtError) as e:
+            r.set_mesh(np.zeros((3, 3), np.float32), np.array([[0, 1, 7]], np.uint32), np.zeros((3, 3), np.float32))
+        assert e.value.code == -1        # index out of range
