@@ -85,8 +85,39 @@ typedef enum rtrt_buffer {
     RTRT_BUF_TLAS_MORTON,        /* uint32[Bp]                    (TLAS_morton2.csv)          */
     RTRT_BUF_TLAS_REORDER_IDX,   /* uint32[Bp]                    (TLAS_reorderIdx.csv)       */
     RTRT_BUF_TLAS_BVH_NODES,     /* BVHNode[Bp]                   (TLAS_bvhNodes.csv)         */
-    RTRT_BUF_COUNT_STAGE1
+    RTRT_BUF_COUNT_STAGE1,
+    /* Buffer2DName surfaces of the path (src/kernel.cuh:286-330), linear, row-major, W x H unless noted */
+    RTRT_BUF_RENDER_COLOR = 32,  /* half3 colour (demodulated radiance) + uint16 material mask, 8 B/px  */
+    RTRT_BUF_NORMAL,             /* half4, 8 B/px                                                       */
+    RTRT_BUF_ALBEDO,             /* half4, 8 B/px                                                       */
+    RTRT_BUF_DEPTH,              /* half, 2 B/px (RayMax stores as +inf)                                */
+    RTRT_BUF_MOTION_VECTOR,      /* half2, 4 B/px (history uv - uv + 0.5)                               */
+    RTRT_BUF_ACCUMULATION_COLOR, /* half3+u16, history of the spatially filtered colour                 */
+    RTRT_BUF_HISTORY_COLOR,      /* half3+u16, history of the final colour                              */
+    RTRT_BUF_HISTORY_DEPTH,      /* half                                                                */
+    RTRT_BUF_NOISE_LEVEL,        /* half, ceil(W/8) x ceil(H/8)                                         */
+    RTRT_BUF_NOISE_LEVEL_16,     /* half, ceil(W/16) x ceil(H/16)                                       */
+    RTRT_BUF_SKY,                /* float4[512*256]  (SkyBuffer)                                        */
+    RTRT_BUF_SKY_CDF,            /* float[512*256]   inclusive luminance CDF                            */
+    RTRT_BUF_SUN,                /* float4[32*32]    (SunBuffer)                                        */
+    RTRT_BUF_SUN_CDF             /* float[32*32]                                                        */
 } rtrt_buffer;
+
+/* SkyParams (src/settingParams.h:26-46), same defaults. */
+typedef struct rtrt_sky_params { float timeOfDay, sunAxisAngle, skyScalar, sunScalar, sunAngle; } rtrt_sky_params;
+/* DenoisingParams (src/settingParams.h:118-157), same defaults. */
+typedef struct rtrt_denoise_params {
+    float local_denoise_sigma_normal, local_denoise_sigma_depth, local_denoise_sigma_material;
+    float large_denoise_sigma_normal, large_denoise_sigma_depth, large_denoise_sigma_material;
+    float temporal_denoise_sigma_normal, temporal_denoise_sigma_depth, temporal_denoise_sigma_material;
+    float noise_threshold_local, noise_threshold_large;
+} rtrt_denoise_params;
+/* the denoiser toggles of RenderPassSettings (src/settingParams.h:66-99) */
+typedef struct rtrt_pass_settings {
+    int32_t enableTemporalDenoising, enableLocalSpatialFilter, enableWideSpatialFilter, enableTemporalDenoising2;
+} rtrt_pass_settings;
+/* SurfaceMaterial (src/kernel.cuh:182-196), 32 bytes; type = SurfaceMaterialType (src/kernel.cuh:172-180) */
+typedef struct rtrt_material { float albedo[3]; uint32_t type; float F0[3]; float alpha; } rtrt_material;
 
 /* ---- lifetime: RayTracer::RayTracer / init / cleanup (src/kernel.cuh:435-449, src/init.cu:53, :601-663) ---- */
 int rtrt_create(const rtrt_config* cfg_or_null, int device, rtrt_ctx** out);
@@ -130,6 +161,37 @@ int rtrt_build_bvh(rtrt_ctx* ctx);
 int rtrt_traverse(rtrt_ctx* ctx, const rtrt_ray* d_rays, uint32_t n, rtrt_hit* d_hits, int any_hit);
 /* Same through HOST buffers (H2D of rays, traversal, D2H of hits, synchronous). */
 int rtrt_traverse_host(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_hit* h_hits, int any_hit);
+
+/* ---- frame inputs -------------------------------------------------------------------------------
+ * Camera: the raw `Camera` struct of src/kernel.cuh:78-101 (176 bytes), which is also the camera.bin file format
+ * written by SaveCameraToFile (src/inputControl.cu:115-150); derived fields must be filled (Camera::update()).
+ * The first rtrt_pathtrace after rtrt_set_camera(..., reset_history=1) uses the same camera as history camera
+ * (src/kernel.cu:131-135); afterwards the history camera is the previous frame's (src/kernel.cu:357). */
+int rtrt_set_camera(rtrt_ctx* ctx, const void* camera_blob, size_t bytes, int reset_history);
+int rtrt_load_camera_file(rtrt_ctx* ctx, const char* path);          /* LoadCameraFromFile src/inputControl.cu:133-150 */
+int rtrt_save_camera_file(rtrt_ctx* ctx, const char* path);          /* SaveCameraToFile   src/inputControl.cu:115-131 */
+int rtrt_set_render_size(rtrt_ctx* ctx, int32_t width, int32_t height);
+int rtrt_set_frame_number(rtrt_ctx* ctx, int32_t frame_num);         /* cbo.frameNum (seeds the blue-noise sample index) */
+int rtrt_set_sky_params(rtrt_ctx* ctx, const rtrt_sky_params* p);    /* NULL = defaults; sky maps regenerate lazily (src/kernel.cu:289-308) */
+int rtrt_get_sun(rtrt_ctx* ctx, float* sun_dir3, float* sun_angle_cos_theta_max);
+int rtrt_set_denoise_params(rtrt_ctx* ctx, const rtrt_denoise_params* p, const rtrt_pass_settings* passes);
+/* materials[num_materials] + per-triangle material index (NULL/0 = the reference scene: 10 materials, every
+ * triangle -> material 3 = Lambert 0.9, src/init.cu:215-265) */
+int rtrt_set_materials(rtrt_ctx* ctx, const rtrt_material* materials, int32_t num_materials,
+                       const int32_t* materials_idx, uint32_t num_idx);
+/* texture atlas slot 0 = albedo+AO, 1 = normal+roughness (src/texture.h:5-12): 16-bit RGBA, w x h, mip chain is
+ * generated with the 2x2 box rule of MipmapGen (src/mipgen.cu:121-139).  Default: constant textures. */
+int rtrt_set_texture(rtrt_ctx* ctx, int32_t slot, int32_t width, int32_t height, const uint16_t* rgba16);
+/* rows [begin,end) of the frame this context traces and denoises (multi-GPU row bands); default: all rows */
+int rtrt_set_row_range(rtrt_ctx* ctx, int32_t row_begin, int32_t row_end);
+int rtrt_set_data_dir(rtrt_ctx* ctx, const char* dir);               /* where blue_noise_4spp.bin / hosek_sky.bin live */
+
+/* ---- stage 2: the PathTrace launch of RayTracer::draw (src/kernel.cu:336-357, src/pathtrace.cuh:11-128) ---- */
+int rtrt_pathtrace(rtrt_ctx* ctx);
+/* ---- stage 3: RayTracer::TemporalSpatialDenoising (src/denoising.cu:5-188) ---- */
+int rtrt_denoise(rtrt_ctx* ctx);
+/* ---- the three stages in draw() order, then frameNum++ (src/kernel.cu:259-362) ---- */
+int rtrt_render_frame(rtrt_ctx* ctx);
 
 /* ---- observation points: GetBuffer2D (src/kernel.cuh:455) + the DebugPrintFile dumps (src/bvh.cu) ---- */
 int rtrt_get_buffer(rtrt_ctx* ctx, int which /* rtrt_buffer */, void** dptr, size_t* bytes);

@@ -99,3 +99,139 @@ def traverse(bvh, rays, any_hit=False, stack_size=16, max_loop=1024, threads=Non
     if counters is not None:
         counters[:] = cnt
     return hits
+
+
+# --------------------------------------------------------------------------------------------------
+# stage 2: environment inputs + path trace
+# --------------------------------------------------------------------------------------------------
+DATA_DIR = os.path.join(os.path.dirname(HERE), "real-time-ray-tracing_b200", "data")
+
+
+def load_tables():
+    bn = np.fromfile(os.path.join(DATA_DIR, "blue_noise_4spp.bin"), np.uint8)
+    hosek = np.fromfile(os.path.join(DATA_DIR, "hosek_sky.bin"), np.float32)
+    assert bn.size == 65536 + 2 * 131072 and hosek.size == 2460
+    return bn, hosek
+
+
+def sun_dir(time_of_day=0.25, sun_axis_angle=45.0):
+    lib = load()
+    out = np.zeros(3, np.float32)
+    lib.orc_sun_dir(C.c_float(time_of_day), C.c_float(sun_axis_angle), _p(out))
+    return out
+
+
+class Sky:
+    pass
+
+
+def sky_generate(sun_direction, time_of_day=0.25, sun_axis_angle=45.0, sky_scalar=0.01, sun_scalar=0.01, sun_angle=0.6):
+    lib = load()
+    _, hosek = load_tables()
+    s = Sky()
+    s.sky = np.zeros((256 * 512, 4), np.float32); s.sky_cdf = np.zeros(256 * 512, np.float32)
+    s.sun = np.zeros((32 * 32, 4), np.float32); s.sun_cdf = np.zeros(32 * 32, np.float32)
+    params = np.array([time_of_day, sun_axis_angle, sky_scalar, sun_scalar, sun_angle], np.float32)
+    cosmax = C.c_float()
+    sd = np.ascontiguousarray(sun_direction, np.float32)
+    lib.orc_sky_generate(_p(params), _p(sd), _p(hosek), _p(s.sky), _p(s.sky_cdf), _p(s.sun), _p(s.sun_cdf), C.byref(cosmax))
+    s.sun_dir = sd; s.cos_theta_max = np.float32(cosmax.value)
+    return s
+
+
+def mip_chain(rgba16, levels=11):
+    """2x2 box mip chain with the truncating store of MipmapGen (src/mipgen.cu:121-139); levels past 1x1 alias the last."""
+    a = np.ascontiguousarray(rgba16, np.uint16)
+    out = [a]
+    while (out[-1].shape[0] != 1 or out[-1].shape[1] != 1) and len(out) < levels:
+        p = out[-1].astype(np.uint32)
+        h, w = p.shape[:2]
+        nh, nw = max(1, h // 2), max(1, w // 2)
+        ys = np.minimum(np.arange(nh) * 2, h - 1); ys1 = np.minimum(ys + 1, h - 1)
+        xs = np.minimum(np.arange(nw) * 2, w - 1); xs1 = np.minimum(xs + 1, w - 1)
+        s = p[ys][:, xs] + p[ys][:, xs1] + p[ys1][:, xs] + p[ys1][:, xs1]
+        out.append(np.ascontiguousarray((s // 4).astype(np.uint16)))
+    while len(out) < levels:
+        out.append(out[-1])
+    return out
+
+
+DEFAULT_TEX = [np.array([[[32768, 32768, 32768, 65535]]], np.uint16), np.array([[[32768, 32768, 65535, 65535]]], np.uint16)]
+
+MATERIAL_DTYPE = np.dtype([("albedo", "<f4", 3), ("type", "<u4"), ("F0", "<f4", 3), ("alpha", "<f4")])
+
+
+def default_materials():
+    """src/init.cu:215-251"""
+    m = np.zeros(10, MATERIAL_DTYPE)
+    m["albedo"] = 0.8; m["type"] = 1; m["F0"] = (0.56, 0.57, 0.58); m["alpha"] = 0.05
+    m["type"][0] = 4; m["albedo"][0] = (0.1, 0.2, 0.9)
+    m["type"][1] = 2
+    m["type"][2] = 4; m["albedo"][2] = (0.9, 0.2, 0.1)
+    m["type"][3] = 0; m["albedo"][3] = 0.9
+    m["type"][4] = 3; m["albedo"][4] = 0.9
+    m["type"][5] = 1
+    m["type"][6] = 0
+    m["type"][7] = 0; m["albedo"][7] = (0.9, 0.2, 0.1)
+    m["type"][8] = 0; m["albedo"][8] = (0.2, 0.9, 0.1)
+    m["type"][9] = 0; m["albedo"][9] = (0.1, 0.2, 0.9)
+    return m
+
+
+class _PtArgs(C.Structure):
+    _fields_ = [
+        ("triangles", C.c_void_p), ("nodes", C.c_void_p), ("tlas", C.c_void_p), ("numBatches", C.c_uint32),
+        ("stackSize", C.c_int), ("maxLoop", C.c_int),
+        ("materials", C.c_void_p), ("materialsIdx", C.c_void_p), ("numMaterials", C.c_int), ("numMaterialsIdx", C.c_int),
+        ("camera", C.c_void_p), ("historyCamera", C.c_void_p),
+        ("sky", C.c_void_p), ("skyCdf", C.c_void_p), ("sun", C.c_void_p), ("sunCdf", C.c_void_p),
+        ("sunDir", C.c_float * 3), ("sunAngleCosThetaMax", C.c_float),
+        ("blueNoise", C.c_void_p),
+        ("tex", (C.c_void_p * 11) * 2), ("texW", (C.c_int * 11) * 2), ("texH", (C.c_int * 11) * 2), ("texMaxLod", C.c_int * 2),
+        ("frameNum", C.c_int), ("width", C.c_int), ("height", C.c_int),
+        ("color", C.c_void_p), ("mask", C.c_void_p), ("normal", C.c_void_p), ("albedo", C.c_void_p), ("depth", C.c_void_p),
+        ("motion", C.c_void_p), ("counters", C.c_void_p), ("threads", C.c_int), ("rowBegin", C.c_int), ("rowEnd", C.c_int)]
+
+
+class Frame:
+    pass
+
+
+def pathtrace(bvh, camera, width, height, frame_num, sky, history_camera=None, materials=None, materials_idx=None,
+              textures=None, stack_size=16, max_loop=1024, threads=None, rows=None):
+    """One PathTrace launch on the CPU.  Returns float32 G-buffers (values before the half stores)."""
+    lib = load()
+    bn, _ = load_tables()
+    cam = np.ascontiguousarray(camera, np.float32); hcam = np.ascontiguousarray(camera if history_camera is None else history_camera, np.float32)
+    assert cam.nbytes == 176 and hcam.nbytes == 176
+    mats = np.ascontiguousarray(default_materials() if materials is None else materials, MATERIAL_DTYPE)
+    midx = np.ascontiguousarray(np.full(bvh.num_tris, 3, np.int32) if materials_idx is None else materials_idx, np.int32)
+    tex = [mip_chain(t) for t in (DEFAULT_TEX if textures is None else textures)]
+    f = Frame()
+    n = width * height
+    f.color = np.zeros((n, 3), np.float32); f.mask = np.zeros(n, np.uint16); f.normal = np.zeros((n, 3), np.float32)
+    f.albedo = np.zeros((n, 3), np.float32); f.depth = np.zeros(n, np.float32); f.motion = np.zeros((n, 2), np.float32)
+    f.counters = np.zeros(3, np.uint64)
+    a = _PtArgs()
+    a.triangles, a.nodes, a.tlas, a.numBatches = _p(bvh.triangles).value, _p(bvh.nodes).value, _p(bvh.tlas_nodes).value, bvh.num_batches
+    a.stackSize, a.maxLoop = stack_size, max_loop
+    a.materials, a.materialsIdx, a.numMaterials, a.numMaterialsIdx = _p(mats).value, _p(midx).value, mats.shape[0], midx.shape[0]
+    a.camera, a.historyCamera = _p(cam).value, _p(hcam).value
+    a.sky, a.skyCdf, a.sun, a.sunCdf = _p(sky.sky).value, _p(sky.sky_cdf).value, _p(sky.sun).value, _p(sky.sun_cdf).value
+    for k in range(3):
+        a.sunDir[k] = float(sky.sun_dir[k])
+    a.sunAngleCosThetaMax = float(sky.cos_theta_max)
+    a.blueNoise = _p(bn).value
+    for t in range(2):
+        for l in range(11):
+            a.tex[t][l] = _p(tex[t][l]).value; a.texW[t][l] = tex[t][l].shape[1]; a.texH[t][l] = tex[t][l].shape[0]
+        a.texMaxLod[t] = 10
+    a.frameNum, a.width, a.height = frame_num, width, height
+    a.color, a.mask, a.normal, a.albedo = _p(f.color).value, _p(f.mask).value, _p(f.normal).value, _p(f.albedo).value
+    a.depth, a.motion, a.counters = _p(f.depth).value, _p(f.motion).value, _p(f.counters).value
+    a.threads = threads or default_threads()
+    a.rowBegin, a.rowEnd = (0, height) if rows is None else rows
+    rc = lib.orc_pathtrace(C.byref(a))
+    if rc:
+        raise RuntimeError(f"orc_pathtrace failed: {rc}")
+    return f

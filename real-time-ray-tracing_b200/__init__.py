@@ -7,7 +7,8 @@ The directory name is not a Python identifier; import it with
 """
 from . import _lib  # noqa: F401
 from .api import (RayTracer, RtrtError, load_config, config_defaults, TRIANGLE_DTYPE, AABB_DTYPE, BVHNODE_DTYPE,
-                  RAY_DTYPE, HIT_DTYPE, RAY_MAX)  # noqa: F401
+                  RAY_DTYPE, HIT_DTYPE, RAY_MAX, MATERIAL_DTYPE, COLOR_DTYPE)  # noqa: F401
+from ._lib import *  # noqa: F401,F403  (BUF_* ids, ctypes structs)
 from . import scenes  # noqa: F401
 from ._lib import (BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES,
                    BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX,

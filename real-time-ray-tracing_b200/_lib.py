@@ -16,6 +16,8 @@ STATUS_NAMES = {0: "RTRT_OK", -1: "RTRT_ERR_ARG", -2: "RTRT_ERR_CUDA", -3: "RTRT
 # rtrt_buffer
 BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES, \
     BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES = range(11)
+BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCUMULATION_COLOR, BUF_HISTORY_COLOR, \
+    BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF = range(32, 46)
 
 
 class Config(C.Structure):
@@ -39,6 +41,24 @@ class Timings(C.Structure):
                 ("denoise_ms", C.c_float), ("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64)]
 
 
+class SkyParams(C.Structure):      # src/settingParams.h:41-45
+    _fields_ = [("timeOfDay", C.c_float), ("sunAxisAngle", C.c_float), ("skyScalar", C.c_float),
+                ("sunScalar", C.c_float), ("sunAngle", C.c_float)]
+
+
+class DenoiseParams(C.Structure):  # src/settingParams.h:144-157
+    _fields_ = [(n, C.c_float) for n in (
+        "local_denoise_sigma_normal", "local_denoise_sigma_depth", "local_denoise_sigma_material",
+        "large_denoise_sigma_normal", "large_denoise_sigma_depth", "large_denoise_sigma_material",
+        "temporal_denoise_sigma_normal", "temporal_denoise_sigma_depth", "temporal_denoise_sigma_material",
+        "noise_threshold_local", "noise_threshold_large")]
+
+
+class PassSettings(C.Structure):   # src/settingParams.h:87-91
+    _fields_ = [(n, C.c_int32) for n in ("enableTemporalDenoising", "enableLocalSpatialFilter",
+                                         "enableWideSpatialFilter", "enableTemporalDenoising2")]
+
+
 # every symbol include/rtrt.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "rtrt_abi_version": (C.c_int, []),
@@ -60,6 +80,21 @@ SYMBOLS = {
     "rtrt_sync": (C.c_int, [C.c_void_p]),
     "rtrt_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "rtrt_get_stream": (C.c_void_p, [C.c_void_p]),
+    "rtrt_set_camera": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
+    "rtrt_load_camera_file": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_save_camera_file": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_set_render_size": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "rtrt_set_frame_number": (C.c_int, [C.c_void_p, C.c_int32]),
+    "rtrt_set_sky_params": (C.c_int, [C.c_void_p, C.POINTER(SkyParams)]),
+    "rtrt_get_sun": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "rtrt_set_denoise_params": (C.c_int, [C.c_void_p, C.POINTER(DenoiseParams), C.POINTER(PassSettings)]),
+    "rtrt_set_materials": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32]),
+    "rtrt_set_texture": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
+    "rtrt_set_row_range": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "rtrt_set_data_dir": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_pathtrace": (C.c_int, [C.c_void_p]),
+    "rtrt_denoise": (C.c_int, [C.c_void_p]),
+    "rtrt_render_frame": (C.c_int, [C.c_void_p]),
 }
 
 _lib = None

@@ -32,6 +32,17 @@ BUFFER_DTYPES = {
     L.BUF_TLAS_REORDER_IDX: np.dtype("<u4"), L.BUF_TLAS_BVH_NODES: BVHNODE_DTYPE,
 }
 
+MATERIAL_DTYPE = np.dtype([("albedo", "<f4", 3), ("type", "<u4"), ("F0", "<f4", 3), ("alpha", "<f4")])   # src/kernel.cuh:182-196
+COLOR_DTYPE = np.dtype([("rgb", "<f2", 3), ("mask", "<u2")])      # Load2DHalf3Ushort1 layout, src/sampler.cuh:91-128
+for _b, _dt in ((L.BUF_RENDER_COLOR, COLOR_DTYPE), (L.BUF_NORMAL, np.dtype(("<f2", 4))), (L.BUF_ALBEDO, np.dtype(("<f2", 4))),
+                (L.BUF_DEPTH, np.dtype("<f2")), (L.BUF_MOTION_VECTOR, np.dtype(("<f2", 2))),
+                (L.BUF_ACCUMULATION_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_DEPTH, np.dtype("<f2")),
+                (L.BUF_NOISE_LEVEL, np.dtype("<f2")), (L.BUF_NOISE_LEVEL_16, np.dtype("<f2")),
+                (L.BUF_SKY, np.dtype(("<f4", 4))), (L.BUF_SKY_CDF, np.dtype("<f4")), (L.BUF_SUN, np.dtype(("<f4", 4))),
+                (L.BUF_SUN_CDF, np.dtype("<f4"))):
+    BUFFER_DTYPES[_b] = _dt
+MAT_LAMBERTIAN_DIFFUSE, MAT_PERFECT_REFLECTION, MAT_GLASS, MAT_MICROFACET_REFLECTION, MAT_EMISSIVE, MAT_SKY = range(6)
+
 RAY_MAX = np.float32(10e10)
 
 
@@ -139,6 +150,66 @@ class RayTracer:
 
     def traverse_device(self, d_rays, n, d_hits, any_hit=False):
         self._check(self._lib.rtrt_traverse(self._h, C.c_void_p(d_rays), n, C.c_void_p(d_hits), int(any_hit)))
+
+    # -- frame inputs ------------------------------------------------------------------------
+    def set_camera(self, cam, reset_history=False):
+        """cam: 44 float32 = the raw Camera struct (src/kernel.cuh:78-101), see scenes.make_camera."""
+        cam = np.ascontiguousarray(cam, dtype=np.float32)
+        self._check(self._lib.rtrt_set_camera(self._h, _ptr(cam), cam.nbytes, int(reset_history)))
+
+    def LoadCameraFromFile(self, path):
+        self._check(self._lib.rtrt_load_camera_file(self._h, str(path).encode()))
+
+    def SaveCameraToFile(self, path):
+        self._check(self._lib.rtrt_save_camera_file(self._h, str(path).encode()))
+
+    def set_render_size(self, w, h):
+        self._check(self._lib.rtrt_set_render_size(self._h, w, h))
+
+    def set_frame_number(self, n):
+        self._check(self._lib.rtrt_set_frame_number(self._h, n))
+
+    def set_sky_params(self, **kw):
+        p = L.SkyParams(0.25, 45.0, 0.01, 0.01, 0.6)
+        for k, v in kw.items():
+            setattr(p, k, v)
+        self._check(self._lib.rtrt_set_sky_params(self._h, C.byref(p)))
+
+    def get_sun(self):
+        d = (C.c_float * 3)(); c = C.c_float()
+        self._check(self._lib.rtrt_get_sun(self._h, d, C.byref(c)))
+        return np.array(list(d), np.float32), np.float32(c.value)
+
+    def set_denoise_params(self, params=None, passes=None):
+        self._check(self._lib.rtrt_set_denoise_params(self._h, C.byref(params) if params is not None else None,
+                                                      C.byref(passes) if passes is not None else None))
+
+    def set_materials(self, materials=None, materials_idx=None):
+        m = np.ascontiguousarray(materials, dtype=MATERIAL_DTYPE) if materials is not None else None
+        i = np.ascontiguousarray(materials_idx, dtype=np.int32) if materials_idx is not None else None
+        self._check(self._lib.rtrt_set_materials(self._h, _ptr(m) if m is not None else None, 0 if m is None else m.shape[0],
+                                                 _ptr(i) if i is not None else None, 0 if i is None else i.shape[0]))
+
+    def set_texture(self, slot, rgba16):
+        a = np.ascontiguousarray(rgba16, dtype=np.uint16)
+        assert a.ndim == 3 and a.shape[2] == 4
+        self._check(self._lib.rtrt_set_texture(self._h, slot, a.shape[1], a.shape[0], _ptr(a)))
+
+    def set_row_range(self, begin, end):
+        self._check(self._lib.rtrt_set_row_range(self._h, begin, end))
+
+    # -- stages 2, 3 ------------------------------------------------------------------------------
+    def pathtrace(self):
+        """The PathTrace launch of RayTracer::draw (src/kernel.cu:336-357)."""
+        self._check(self._lib.rtrt_pathtrace(self._h))
+
+    def denoise(self):
+        """TemporalSpatialDenoising (src/denoising.cu:5-188)."""
+        self._check(self._lib.rtrt_denoise(self._h))
+
+    def draw(self):
+        """RayTracer::draw for the hot path: BuildBvhLevel1/2 -> PathTrace -> denoise, frameNum++ (src/kernel.cu:259-362)."""
+        self._check(self._lib.rtrt_render_frame(self._h))
 
     # -- observation points -------------------------------------------------------------------
     def counts(self):

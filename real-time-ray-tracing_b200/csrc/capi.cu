@@ -93,6 +93,24 @@ static int ensure_ray_stage(Context& c, uint32_t n) {
 
 #define CTX_OR_FAIL(ctx) do { if (!(ctx)) return RTRT_ERR_ARG; } while (0)
 
+static void rtrt_set_sky_params_defaults(rtrt_sky_params* p) {       // src/settingParams.h:41-45
+    p->timeOfDay = 0.25f; p->sunAxisAngle = 45.0f; p->skyScalar = 0.01f; p->sunScalar = 0.01f; p->sunAngle = 0.6f;
+}
+static void rtrt_set_denoise_defaults(rtrt_denoise_params* d, rtrt_pass_settings* s) {   // src/settingParams.h:144-157, 87-91
+    d->local_denoise_sigma_normal = 100.0f; d->local_denoise_sigma_depth = 0.1f; d->local_denoise_sigma_material = 100.0f;
+    d->large_denoise_sigma_normal = 100.0f; d->large_denoise_sigma_depth = 0.01f; d->large_denoise_sigma_material = 100.0f;
+    d->temporal_denoise_sigma_normal = 100.0f; d->temporal_denoise_sigma_depth = 0.1f; d->temporal_denoise_sigma_material = 100.0f;
+    d->noise_threshold_local = 0.001f; d->noise_threshold_large = 0.001f;
+    s->enableTemporalDenoising = 1; s->enableLocalSpatialFilter = 1; s->enableWideSpatialFilter = 1; s->enableTemporalDenoising2 = 1;
+}
+
+static HistoryCamera history_setup(const Camera& cam) {                // HistoryCamera::Setup src/kernel.cuh:137-142
+    HistoryCamera h;
+    h.invCamMat = Mat3{cam.left.x, cam.up.x, cam.dir.x, cam.left.y, cam.up.y, cam.dir.y, cam.left.z, cam.up.z, cam.dir.z};
+    h.pos = cam.pos;
+    return h;
+}
+
 extern "C" {
 
 int rtrt_abi_version(void) { return RTRT_ABI_VERSION; }
@@ -108,9 +126,12 @@ int rtrt_create(const rtrt_config* cfg, int device, rtrt_ctx** out) {
     Context& c = h->c;
     c.device = device;
     if (cfg) c.cfg = *cfg; else rtrt_config_defaults(&c.cfg);
+    c.width = c.cfg.width; c.height = c.cfg.height;
+    rtrt_set_sky_params_defaults(&c.skyParams);
+    rtrt_set_denoise_defaults(&c.denoiseParams, &c.passSettings);
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     if (cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
-    cudaEventCreate(&c.evA); cudaEventCreate(&c.evB);
+    for (auto& e : c.ev) { cudaEventCreate(&e[0]); cudaEventCreate(&e[1]); }
     if (cudaMalloc((void**)&c.dTicket, 64) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     *out = h;
     return RTRT_OK;
@@ -122,9 +143,9 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     cudaSetDevice(c.device);
     cudaStreamSynchronize(c.stream);
     free_mesh(c);
+    free_frame_resources(c);
     dfree(c.dRayStage); dfree(c.dHitStage); dfree(c.dTicket);
-    if (c.evA) cudaEventDestroy(c.evA);
-    if (c.evB) cudaEventDestroy(c.evB);
+    for (auto& e : c.ev) { if (e[0]) cudaEventDestroy(e[0]); if (e[1]) cudaEventDestroy(e[1]); }
     if (c.stream) cudaStreamDestroy(c.stream);
     delete ctx;
     return RTRT_OK;
@@ -214,12 +235,12 @@ int rtrt_build_bvh(rtrt_ctx* ctx) {
     CTX_OR_FAIL(ctx);
     Context& c = ctx->c;
     RTRT_CUDA(c, cudaSetDevice(c.device));
-    RTRT_CUDA(c, cudaEventRecord(c.evA, c.stream));
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_BUILD][0], c.stream));
     int rc = launch_build_bvh(c);
     if (rc) return rc;
-    RTRT_CUDA(c, cudaEventRecord(c.evB, c.stream));
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_BUILD][1], c.stream));
     c.bvhValid = true;
-    c.timings.build_bvh_ms = -1.0f;     // resolved lazily in rtrt_get_timings
+    c.evPending[STAGE_BUILD] = true;    // resolved lazily in rtrt_get_timings
     return RTRT_OK;
 }
 
@@ -228,8 +249,13 @@ int rtrt_traverse(rtrt_ctx* ctx, const rtrt_ray* d_rays, uint32_t n, rtrt_hit* d
     Context& c = ctx->c;
     if ((!d_rays || !d_hits) && n) return c.fail(RTRT_ERR_ARG, "rtrt_traverse: null buffer");
     RTRT_CUDA(c, cudaSetDevice(c.device));
-    c.timings.rays_traced = n;
-    return launch_traverse(c, reinterpret_cast<const Ray*>(d_rays), n, reinterpret_cast<Hit*>(d_hits), any_hit, nullptr);
+    c.timings.rays_traced = n; c.raysOnDevice = false;
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_TRAVERSE][0], c.stream));
+    int rc = launch_traverse(c, reinterpret_cast<const Ray*>(d_rays), n, reinterpret_cast<Hit*>(d_hits), any_hit, nullptr);
+    if (rc) return rc;
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_TRAVERSE][1], c.stream));
+    c.evPending[STAGE_TRAVERSE] = true;
+    return RTRT_OK;
 }
 
 int rtrt_traverse_host(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_hit* h_hits, int any_hit) {
@@ -245,7 +271,7 @@ int rtrt_traverse_host(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_h
     if (rc) return rc;
     RTRT_CUDA(c, cudaMemcpyAsync(h_hits, c.dHitStage, (size_t)n * sizeof(Hit), cudaMemcpyDeviceToHost, c.stream));
     RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
-    c.timings.rays_traced = n;
+    c.timings.rays_traced = n; c.raysOnDevice = false;
     return RTRT_OK;
 }
 
@@ -253,7 +279,11 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
     CTX_OR_FAIL(ctx);
     Context& c = ctx->c;
     if (!dptr || !bytes) return c.fail(RTRT_ERR_ARG, "rtrt_get_buffer: null out pointer");
-    const size_t n = (size_t)c.numBatches * kBatchSize, bp = c.numBatchesPadded;
+    if (which >= RTRT_BUF_SKY && which <= RTRT_BUF_SUN_CDF && (c.skyDirty || !c.dSky)) {   // lazy regeneration, src/kernel.cu:289
+        int rc = ensure_frame_resources(c);
+        if (rc) return rc;
+    }
+    const size_t n = (size_t)c.numBatches * kBatchSize, bp = c.numBatchesPadded, px = (size_t)c.gbufW * c.gbufH;
     void* p = nullptr; size_t b = 0;
     switch (which) {
         case RTRT_BUF_TRIANGLES: p = c.dTriangles; b = n * sizeof(Triangle); break;
@@ -267,9 +297,23 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         case RTRT_BUF_TLAS_MORTON: p = c.dTlasMorton; b = bp * 4; break;
         case RTRT_BUF_TLAS_REORDER_IDX: p = c.dTlasReorderIdx; b = bp * 4; break;
         case RTRT_BUF_TLAS_BVH_NODES: p = c.dTlasNodes; b = bp * sizeof(BVHNode); break;
+        case RTRT_BUF_RENDER_COLOR: p = c.dColor; b = px * 8; break;
+        case RTRT_BUF_NORMAL: p = c.dNormal; b = px * 8; break;
+        case RTRT_BUF_ALBEDO: p = c.dAlbedo; b = px * 8; break;
+        case RTRT_BUF_DEPTH: p = c.dDepth; b = px * 2; break;
+        case RTRT_BUF_MOTION_VECTOR: p = c.dMotion; b = px * 4; break;
+        case RTRT_BUF_ACCUMULATION_COLOR: p = c.dAccum; b = px * 8; break;
+        case RTRT_BUF_HISTORY_COLOR: p = c.dHistoryColor; b = px * 8; break;
+        case RTRT_BUF_HISTORY_DEPTH: p = c.dHistoryDepth; b = px * 2; break;
+        case RTRT_BUF_NOISE_LEVEL: p = c.dNoise; b = (size_t)((c.gbufW + 7) / 8) * ((c.gbufH + 7) / 8) * 2; break;
+        case RTRT_BUF_NOISE_LEVEL_16: p = c.dNoise16; b = (size_t)((c.gbufW + 15) / 16) * ((c.gbufH + 15) / 16) * 2; break;
+        case RTRT_BUF_SKY: p = c.dSky; b = sizeof(float) * 4 * kSkySize; break;
+        case RTRT_BUF_SKY_CDF: p = c.dSkyCdf; b = sizeof(float) * kSkySize; break;
+        case RTRT_BUF_SUN: p = c.dSun; b = sizeof(float) * 4 * kSunSize; break;
+        case RTRT_BUF_SUN_CDF: p = c.dSunCdf; b = sizeof(float) * kSunSize; break;
         default: return c.fail(RTRT_ERR_ARG, "rtrt_get_buffer: unknown buffer");
     }
-    if (!p) return c.fail(RTRT_ERR_STATE, "rtrt_get_buffer: buffer not allocated (no mesh set?)");
+    if (!p) return c.fail(RTRT_ERR_STATE, "rtrt_get_buffer: buffer not allocated yet (no mesh set / no frame rendered?)");
     *dptr = p; *bytes = b;
     return RTRT_OK;
 }
@@ -309,9 +353,17 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
     if (!out) return c.fail(RTRT_ERR_ARG, "rtrt_get_timings: null out");
     RTRT_CUDA(c, cudaSetDevice(c.device));
     RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
-    if (c.timings.build_bvh_ms < 0.0f) {
-        float ms = 0.0f;
-        if (cudaEventElapsedTime(&ms, c.evA, c.evB) == cudaSuccess) c.timings.build_bvh_ms = ms; else c.timings.build_bvh_ms = 0.0f;
+    float* slots[4] = {&c.timings.build_bvh_ms, &c.timings.traverse_ms, &c.timings.pathtrace_ms, &c.timings.denoise_ms};
+    for (int s = 0; s < 4; ++s)
+        if (c.evPending[s]) {
+            float ms = 0.0f;
+            *slots[s] = (cudaEventElapsedTime(&ms, c.ev[s][0], c.ev[s][1]) == cudaSuccess) ? ms : 0.0f;
+            c.evPending[s] = false;
+        }
+    if (c.raysOnDevice && c.dRayCounter) {
+        unsigned long long r = 0;
+        RTRT_CUDA(c, cudaMemcpy(&r, c.dRayCounter, sizeof(r), cudaMemcpyDeviceToHost));
+        c.timings.rays_traced = r; c.raysOnDevice = false;
     }
     c.timings.kernel_launches = c.launches;
     *out = c.timings;
@@ -319,5 +371,141 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
 }
 
 void* rtrt_get_stream(rtrt_ctx* ctx) { return ctx ? (void*)ctx->c.stream : nullptr; }
+
+// ---------------------------------------------------------------------------------- frame inputs
+int rtrt_set_camera(rtrt_ctx* ctx, const void* blob, size_t bytes, int reset_history) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (!blob || bytes != sizeof(Camera)) return c.fail(RTRT_ERR_ARG, "rtrt_set_camera: blob must be sizeof(Camera) = 176 bytes");
+    std::memcpy(&c.camera, blob, sizeof(Camera));
+    if (reset_history || !c.cameraSet) c.historyCamera = history_setup(c.camera);      // src/kernel.cu:131-135
+    c.cameraSet = true;
+    return RTRT_OK;
+}
+
+int rtrt_load_camera_file(rtrt_ctx* ctx, const char* path) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    Camera cam;
+    FILE* f = path ? fopen(path, "rb") : nullptr;
+    if (!f) return c.fail(RTRT_ERR_IO, "rtrt_load_camera_file: cannot open file");
+    const size_t n = fread(&cam, 1, sizeof(cam), f);
+    fclose(f);
+    if (n != sizeof(cam)) return c.fail(RTRT_ERR_IO, "rtrt_load_camera_file: short file");
+    return rtrt_set_camera(ctx, &cam, sizeof(cam), 1);
+}
+
+int rtrt_save_camera_file(rtrt_ctx* ctx, const char* path) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (!c.cameraSet) return c.fail(RTRT_ERR_STATE, "rtrt_save_camera_file: no camera set");
+    FILE* f = path ? fopen(path, "wb") : nullptr;
+    if (!f) return c.fail(RTRT_ERR_IO, "rtrt_save_camera_file: cannot open file");
+    const size_t n = fwrite(&c.camera, 1, sizeof(Camera), f);
+    fclose(f);
+    return n == sizeof(Camera) ? RTRT_OK : c.fail(RTRT_ERR_IO, "rtrt_save_camera_file: short write");
+}
+
+int rtrt_set_render_size(rtrt_ctx* ctx, int32_t w, int32_t h) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (w < 8 || h < 8 || w > 16384 || h > 16384) return c.fail(RTRT_ERR_ARG, "rtrt_set_render_size: size out of range");
+    c.width = w; c.height = h; c.rowBegin = 0; c.rowEnd = h;
+    return RTRT_OK;
+}
+
+int rtrt_set_frame_number(rtrt_ctx* ctx, int32_t n) { CTX_OR_FAIL(ctx); ctx->c.frameNum = n; return RTRT_OK; }
+
+int rtrt_set_sky_params(rtrt_ctx* ctx, const rtrt_sky_params* p) {
+    CTX_OR_FAIL(ctx);
+    if (p) ctx->c.skyParams = *p; else rtrt_set_sky_params_defaults(&ctx->c.skyParams);
+    ctx->c.skyDirty = true;
+    return RTRT_OK;
+}
+
+int rtrt_get_sun(rtrt_ctx* ctx, float* d3, float* cosMax) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (c.skyDirty || !c.dSky) { int rc = ensure_frame_resources(c); if (rc) return rc; }
+    if (d3) { d3[0] = c.sunDir.x; d3[1] = c.sunDir.y; d3[2] = c.sunDir.z; }
+    if (cosMax) *cosMax = c.sunAngleCosThetaMax;
+    return RTRT_OK;
+}
+
+int rtrt_set_denoise_params(rtrt_ctx* ctx, const rtrt_denoise_params* p, const rtrt_pass_settings* s) {
+    CTX_OR_FAIL(ctx);
+    rtrt_denoise_params d; rtrt_pass_settings ps;
+    rtrt_set_denoise_defaults(&d, &ps);
+    ctx->c.denoiseParams = p ? *p : d;
+    ctx->c.passSettings = s ? *s : ps;
+    return RTRT_OK;
+}
+
+int rtrt_set_materials(rtrt_ctx* ctx, const rtrt_material* m, int32_t nm, const int32_t* idx, uint32_t nidx) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (m && nm <= 0) return c.fail(RTRT_ERR_ARG, "rtrt_set_materials: bad count");
+    static_assert(sizeof(rtrt_material) == sizeof(SurfaceMaterial), "material layout");
+    c.materialsUser = (m != nullptr) || (idx != nullptr);
+    return set_materials(c, m, nm, idx, (int)nidx);
+}
+
+int rtrt_set_texture(rtrt_ctx* ctx, int32_t slot, int32_t w, int32_t h, const uint16_t* rgba) {
+    CTX_OR_FAIL(ctx);
+    return set_texture(ctx->c, slot, w, h, rgba);
+}
+
+int rtrt_set_row_range(rtrt_ctx* ctx, int32_t b, int32_t e) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (b < 0 || e <= b || e > c.height) return c.fail(RTRT_ERR_ARG, "rtrt_set_row_range: bad range");
+    c.rowBegin = b; c.rowEnd = e;
+    return RTRT_OK;
+}
+
+int rtrt_set_data_dir(rtrt_ctx* ctx, const char* dir) {
+    CTX_OR_FAIL(ctx);
+    if (!dir) return ctx->c.fail(RTRT_ERR_ARG, "rtrt_set_data_dir: null");
+    ctx->c.dataDir = dir;
+    return RTRT_OK;
+}
+
+// ---------------------------------------------------------------------------------- stages 2 and 3
+int rtrt_pathtrace(rtrt_ctx* ctx) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_PATHTRACE][0], c.stream));
+    int rc = launch_pathtrace(c);
+    if (rc) return rc;
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_PATHTRACE][1], c.stream));
+    c.evPending[STAGE_PATHTRACE] = true; c.raysOnDevice = true;
+    c.historyCamera = history_setup(c.camera);                         // src/kernel.cu:357
+    return RTRT_OK;
+}
+
+int rtrt_denoise(rtrt_ctx* ctx) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_DENOISE][0], c.stream));
+    int rc = launch_denoise(c);
+    if (rc) return rc;
+    RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_DENOISE][1], c.stream));
+    c.evPending[STAGE_DENOISE] = true;
+    return RTRT_OK;
+}
+
+int rtrt_render_frame(rtrt_ctx* ctx) {
+    CTX_OR_FAIL(ctx);
+    int rc = rtrt_build_bvh(ctx);            // src/kernel.cu:330-331
+    if (rc) return rc;
+    rc = rtrt_pathtrace(ctx);                // :336-357
+    if (rc) return rc;
+    rc = rtrt_denoise(ctx);                  // :360
+    if (rc) return rc;
+    ctx->c.frameNum++;                       // UpdateFrame of the next draw (src/kernel.cu:61-63)
+    return RTRT_OK;
+}
 
 }  // extern "C"

@@ -4,6 +4,7 @@
 #pragma once
 #include "../../include/rtrt.h"
 #include "rtrt_types.h"
+#include "shading.cuh"
 #include <cuda_runtime.h>
 #include <string>
 #include <cstdio>
@@ -36,9 +37,35 @@ struct Context {
     int stackSize = 16;      // src/traverse.h:28
     int maxLoop = 1024;      // src/traverse.h:132
 
+    // ---- frame state: ConstBuffer (src/kernel.cuh:211-231) + Buffer2DManager (src/init.cu:441-584) ----
+    int width = 0, height = 0;               // render size
+    int rowBegin = 0, rowEnd = 0;            // rows this GPU traces / denoises (multi-GPU row bands); default = whole frame
+    int frameNum = 1;                        // src/kernel.cu:61-63 (first frame is 1)
+    bool cameraSet = false;
+    Camera camera{}; Camera prevCamera{}; HistoryCamera historyCamera{};
+    rtrt_sky_params skyParams{}; bool skyDirty = true;
+    Float3 sunDir{0, 1, 0}; float sunAngleCosThetaMax = 1.0f;
+    std::string dataDir;
+    float* dHosek = nullptr;                 // Hosek-Wilkie coefficient sets (2460 floats)
+    uint8_t* dBlueNoise = nullptr;           // sobol | scramble | rank
+    float* dSky = nullptr; float* dSkyPdf = nullptr; float* dSkyCdf = nullptr;
+    float* dSun = nullptr; float* dSunPdf = nullptr; float* dSunCdf = nullptr;
+    SurfaceMaterial* dMaterials = nullptr; int* dMaterialsIdx = nullptr; int numMaterials = 0, numMaterialsIdx = 0;
+    bool materialsUser = false;
+    MipTex tex[2]{}; void* dTexMem[2] = {nullptr, nullptr};
+    // G-buffers, linear, reference formats (src/init.cu:473-500)
+    void* dColor = nullptr; void* dNormal = nullptr; void* dAlbedo = nullptr; void* dDepth = nullptr; void* dMotion = nullptr;
+    void* dAccum = nullptr; void* dHistoryColor = nullptr; void* dHistoryDepth = nullptr; void* dHistoryAlbedo = nullptr;
+    void* dNoise = nullptr; void* dNoise16 = nullptr; void* dColorTmp = nullptr;
+    int gbufW = 0, gbufH = 0;
+    unsigned long long* dRayCounter = nullptr;
+    rtrt_denoise_params denoiseParams{}; rtrt_pass_settings passSettings{};
+
     // ---- bookkeeping ----
     unsigned long long launches = 0;                     // kernels launched by this library
-    cudaEvent_t evA = nullptr, evB = nullptr;
+    cudaEvent_t ev[4][2] = {};                           // [build, traverse, pathtrace, denoise][begin, end]
+    bool evPending[4] = {false, false, false, false};
+    bool raysOnDevice = false;                           // rays_traced of the last pathtrace still in dRayCounter
     rtrt_timings timings{};
 
     int fail(int code, const char* msg) { lastError = msg; return code; }
@@ -50,6 +77,8 @@ struct Context {
     }
 };
 
+enum { STAGE_BUILD = 0, STAGE_TRAVERSE = 1, STAGE_PATHTRACE = 2, STAGE_DENOISE = 3 };
+
 #define RTRT_CUDA(ctx, call)                                                         \
     do {                                                                             \
         cudaError_t _e = (call);                                                     \
@@ -60,5 +89,11 @@ struct Context {
 int launch_build_bvh(Context& c);
 int launch_build_tlas_global(Context& c);
 int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int anyHit, unsigned long long* dCounters);
+int launch_pathtrace(Context& c);
+int launch_denoise(Context& c);
+int ensure_frame_resources(Context& c);      // frame.cu: G-buffers, tables, default materials/textures, sky regeneration
+void free_frame_resources(Context& c);
+int set_texture(Context& c, int slot, int w, int h, const uint16_t* rgba);
+int set_materials(Context& c, const void* materials, int numMaterials, const int* materialsIdx, int numIdx);
 
 }  // namespace rtrt

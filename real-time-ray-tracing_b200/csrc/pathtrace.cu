@@ -1,0 +1,311 @@
+// Stage 2 — unidirectional path tracer for sm_100a (rtrt_pathtrace).
+//
+// Semantics restated from src/pathtrace.cuh:11-128 (fixed 5-segment path: primary, <= 2 specular bounces, two
+// diffuse/MIS interactions, environment lookup), src/raygen.cuh, src/traverse.cuh (RaySceneIntersect,
+// UpdateMaterial), src/surfaceInteraction.cuh (Glossy/DiffuseSurfaceInteraction) and src/light.cuh:275-305.
+// Same blue-noise indexing (sampleIdx = frameNum*4 + k, dims 0..3) so every pixel draws the reference's samples.
+// Outputs are the reference's G-buffers (src/pathtrace.cuh:123-127, formats src/init.cu:473-500) as LINEAR
+// device buffers: colour half3 + u16 material mask, normal half4, albedo half4, depth half, motion half2.
+#include "shading_bsdf.cuh"
+#include "traverse.cuh"
+#include "context.h"
+#include <cuda_fp16.h>
+
+namespace rtrt {
+
+constexpr int kPtBlockX = 8, kPtBlockY = 8;       // src/kernel.cu:336: 8x8 pixel tiles (a warp covers 8x4 pixels)
+constexpr int kPtThreads = kPtBlockX * kPtBlockY;
+
+struct PathTraceParams {
+    SceneView sc;
+    const SurfaceMaterial* __restrict__ materials; const int* __restrict__ materialsIdx; int numMaterials, numMaterialsIdx;
+    Camera camera; HistoryCamera historyCamera;
+    EnvMaps env; BlueNoiseTables bn; MipTex tex[2];
+    int frameNum, width, height, rowBegin, rowEnd;
+    ushort4* color; ushort4* normal; ushort4* albedo; __half* depth; __half2* motion;
+    unsigned long long* rayCounter;
+};
+
+struct RayState {            // live subset of src/kernel.cuh:233-284
+    Float3 orig, dir, beta0, beta1, pos, normal, fakeNormal, albedo, centerRaydir;
+    int matId, matType, lightIdx, objectIdx;
+    float offset, normalDotRayDir, depth, rayConeWidth, rayConeSpread;
+    bool isRayIntoSurface, hitLight, hit, isDiffuse, isHitProcessed, isOccluded, isShadowRay;
+};
+
+// src/raygen.cuh:45-63
+VD float ray_cone_width(const Camera& cam, int ix, int iy) {
+    const Float2 pc = (Float2{(float)ix, (float)iy} + 0.5f) - Float2{cam.resolution.x, cam.resolution.y} / 2.0f;
+    const Float2 po{copysignf(0.5f, pc.x), copysignf(0.5f, pc.y)};
+    const Float2 uvNear = (pc - po) * cam.inversedResolution * 2.0f;
+    const Float2 uvFar = (pc + po) * cam.inversedResolution * 2.0f;
+    const Float2 hf{tanf(cam.fov.x / 2.0f), tanf(cam.fov.y / 2.0f)};
+    const Float2 n = uvNear * hf, f = uvFar * hf;
+    return atanf(sqrtf(f.x * f.x + f.y * f.y)) - atanf(sqrtf(n.x * n.x + n.y * n.y));
+}
+
+// src/raygen.cuh:7-38
+VD void generate_ray(Float3& orig, Float3& dir, Float3& centerDir, Float2& sampleUv, const Camera& cam, int ix, int iy, Float2 rp, Float2 ra) {
+    Float2 uv = (Float2{(float)ix, (float)iy} + rp) * cam.inversedResolution;
+    Float2 uvc = (Float2{(float)ix, (float)iy} + 0.5f) * cam.inversedResolution;
+    sampleUv = uv;
+    uv = uv * -2.0f + 1.0f;
+    uvc = uvc * -2.0f + 1.0f;
+    const Float3 p = cam.adjustedFront + cam.adjustedLeft * uv.x + cam.adjustedUp * uv.y;
+    const Float3 pc = cam.adjustedFront + cam.adjustedLeft * uvc.x + cam.adjustedUp * uvc.y;
+    const Float2 disk = concentric_sample_disk(ra);
+    const Float3 pa = disk.x * cam.apertureLeft + disk.y * cam.apertureUp;
+    orig = cam.pos + pa;
+    dir = normalize(p - pa);
+    centerDir = normalize(pc);
+}
+
+// src/traverse.cuh:9-56
+VD void update_material(const PathTraceParams& P, RayState& r) {
+    if (!r.hit) { r.matType = MAT_SKY; r.matId = 99999; }
+    else {
+        r.matId = (r.objectIdx >= 0 && r.objectIdx < P.numMaterialsIdx) ? __ldg(P.materialsIdx + r.objectIdx) : 6;   // SAFE_LOAD default 6
+        r.matType = (r.matId >= 0 && r.matId < P.numMaterials) ? (int)P.materials[r.matId].type : (int)PERFECT_REFLECTION;
+    }
+    if (r.isShadowRay) {
+        if ((r.matType == EMISSIVE && r.lightIdx == r.objectIdx) || (r.matType == MAT_SKY && r.lightIdx == kEnvLightId)) r.hitLight = true;
+        else r.isOccluded = true;
+    } else {
+        r.hitLight = r.matType == EMISSIVE || r.matType == MAT_SKY;
+    }
+    r.isDiffuse = (r.matType == LAMBERTIAN_DIFFUSE) || (r.matType == MICROFACET_REFLECTION);
+}
+
+// src/traverse.cuh:64-225 — guards, traversal, hit record (src/traverse.h:161-174), normal flipping, material
+VD void ray_scene_intersect(const PathTraceParams& P, const AABB& sceneBox, RayState& r, uint32_t* stackLink, float* stackT, uint32_t& rays) {
+    if (r.hitLight || !r.isHitProcessed || r.isOccluded) return;
+    r.isHitProcessed = false;
+    ++rays;
+    const RayPrep rp = prepare_ray(r.orig, r.dir, sceneBox);
+    const TraverseResult h = traverse_bvh<16, false>(P.sc, rp, 0, stackLink, stackT, kPtThreads);
+    r.objectIdx = h.tri;
+    r.offset = 1e-7f;
+    r.normal = f3(0.0f);
+    r.pos = f3(kRayMax);
+    if (h.tri >= 0) {
+        const float4* row = P.sc.triRows + (size_t)h.tri * 8;
+        const float4 q1 = __ldg(row), q2 = __ldg(row + 1), q3 = __ldg(row + 2);
+        const float4 m1 = __ldg(row + 4), m2 = __ldg(row + 5), m3 = __ldg(row + 6);
+        const Float3 v1{q1.x, q1.y, q1.z}, v2{q2.x, q2.y, q2.z}, v3{q3.x, q3.y, q3.z};
+        const Float3 n = normalize(cross(v2 - v1, v3 - v1));
+        const float errorT = (16 * 1.1920928955078125e-07f) / (1.0f - 16 * 1.1920928955078125e-07f) * fabsf(h.t);   // ErrGamma(16)*|t|
+        // GetRayPlaneIntersectPoint (src/geometry.cuh:252-262)
+        const Float3 p = r.orig + r.dir * h.t;
+        const Float3 pc = p - (dot(n, p) + (-dot(n, v1))) * n;
+        const float errorP = getmax3(abs3(pc)) * ((6 * 1.1920928955078125e-07f) / (1.0f - 6 * 1.1920928955078125e-07f));
+        r.normal = n; r.pos = pc; r.offset = errorT + errorP;
+        const Float3 n1 = normalize(Float3{m1.x, m1.y, m1.z}), n2 = normalize(Float3{m2.x, m2.y, m2.z}), n3 = normalize(Float3{m3.x, m3.y, m3.z});
+        r.fakeNormal = normalize(n3 * (1.0f - h.ua - h.va) + n1 * h.ua + n2 * h.va);
+    }
+    r.normalDotRayDir = dot(r.normal, r.dir);
+    r.isRayIntoSurface = r.normalDotRayDir < 0;
+    if (!r.isRayIntoSurface) { r.normal = -r.normal; r.normalDotRayDir = -r.normalDotRayDir; }
+    if (dot(r.fakeNormal, r.normal) < 0) r.fakeNormal = -r.fakeNormal;
+    r.hit = (h.t < kRayMax);
+    r.depth = h.t;
+    if (!r.hit) { r.normal = f3(0, -1, 0); r.fakeNormal = f3(0, -1, 0); }
+    else r.rayConeWidth += r.rayConeSpread * h.t;
+    update_material(P, r);
+}
+
+// src/surfaceInteraction.cuh:11-34
+VD void glossy_interaction(RayState& r, float rnd) {
+    if (r.hitLight || r.isDiffuse || r.isOccluded) return;
+    r.isHitProcessed = true;
+    if (r.matType == PERFECT_REFLECTION) {
+        r.dir = normalize(r.dir - r.normal * dot(r.dir, r.normal) * 2.0f);
+        r.orig = r.pos + r.offset * r.normal;
+    } else if (r.matType == PERFECT_FRESNEL_REFLECTION_REFRACTION) {
+        Float3 next; float off = r.offset;
+        perfect_reflection_refraction(1.0f, 1.33f, r.isRayIntoSurface, r.normal, r.normalDotRayDir, rnd, r.dir, next, off);
+        r.dir = next;
+        r.orig = r.pos + off * r.normal;
+    }
+}
+
+VD Float3 pow3f(Float3 v, float a) { return Float3{powf(v.x, a), powf(v.y, a), powf(v.z, a)}; }
+
+// one triplanar projection of src/surfaceInteraction.cuh:96-155
+VD void triplanar_axis(const PathTraceParams& P, Float2 uv, float lod, Float3 normal, Float3 w, Float3& albedo, Float3& nrm) {
+    uv = uv * 0.5f;
+    const Float4 c = sample_tex_lod(P.tex[0], uv, lod);
+    albedo = pow3f(xyz(c), 2.2f);
+    const Float4 c2 = sample_tex_lod(P.tex[1], uv, lod);
+    const Float3 n = xyz(c2) - 0.5f;
+    const Float3 u = cross(normal, w);
+    const Float3 v = cross(normal, u);
+    nrm = normalize(u * n.x + v * n.y + normal * n.z);
+}
+
+// src/surfaceInteraction.cuh:36-310
+VD void diffuse_interaction(int bounce, const PathTraceParams& P, RayState& r, Float3& beta, const Float4& rnd, const Float4& rnd2) {
+    if (r.hitLight || !r.isDiffuse || r.isOccluded) return;
+    r.lightIdx = kDefaultLightId;
+    r.isHitProcessed = true;
+    const SurfaceMaterial mat = P.materials[r.matId];
+    Float3 normal = r.fakeNormal;
+    const Float3 surfaceNormal = r.normal;
+    Float3 albedo;
+    {
+        const float tw = (float)P.tex[0].w[0], th = (float)P.tex[0].h[0];
+        const float lod = log2f(r.rayConeWidth * 0.5f * sqrtf(tw * tw + th * th));
+        Float3 aX, aY, aZ, nX, nY, nZ;
+        triplanar_axis(P, Float2{r.pos.y, r.pos.z}, lod, normal, fabsf(normal.y) > 0.999f ? f3(0, 0, 1) : f3(0, 1, 0), aX, nX);
+        triplanar_axis(P, Float2{r.pos.x, r.pos.z}, lod, normal, fabsf(normal.x) > 0.999f ? f3(0, 0, 1) : f3(1, 0, 0), aY, nY);
+        triplanar_axis(P, Float2{r.pos.x, r.pos.y}, lod, normal, fabsf(normal.y) > 0.999f ? f3(1, 0, 0) : f3(0, 1, 0), aZ, nZ);
+        const float wx = surfaceNormal.x * surfaceNormal.x, wy = surfaceNormal.y * surfaceNormal.y, wz = surfaceNormal.z * surfaceNormal.z;
+        albedo = aX * wx + aY * wy + aZ * wz;
+        normal = normalize(nX * wx + nY * wy + nZ * wz);
+        r.fakeNormal = normal;
+    }
+    if (bounce == 0) r.albedo = albedo * (1.0f + fabsf(dot(normal, r.centerRaydir)));
+    const Float3 rayDir = r.dir;
+    Float3 lightDir; float lightPdf = 1.0f; int lightIdx;
+    sample_light(P.env, lightDir, lightPdf, lightIdx, rnd2);
+    Float3 surfDir = f3(0.0f), sBsdf = f3(0.0f), lBsdf = f3(0.0f);
+    float sPdf = 0.0f, lPdf = 0.0f;
+    const Float2 r2{rnd.x, rnd.y}, r22{rnd.z, rnd.w};
+    if (r.matType == LAMBERTIAN_DIFFUSE) {
+        surfDir = lambertian_sample(r2, normal);
+        sBsdf = lambertian_bsdf(albedo); sPdf = lambertian_pdf(surfDir, normal);
+        lBsdf = lambertian_bsdf(albedo);
+    } else if (r.matType == MICROFACET_REFLECTION) {
+        microfacet_reflection_sample(r2, r22, rayDir, surfDir, normal, surfaceNormal, sBsdf, sPdf, mat.F0, albedo, mat.alpha);
+        microfacet_reflection(lBsdf, lPdf, normal, -rayDir, lightDir, mat.F0, albedo, mat.alpha);
+    }
+    if (isnan3(lBsdf)) lBsdf = f3(0.0f);                    // NAN_DETECTER src/surfaceInteraction.cuh:228-231
+    if (isnan3(sBsdf)) sBsdf = f3(0.0f);
+    if (sPdf != sPdf) sPdf = 0.0f;
+    if (lightPdf != lightPdf) lightPdf = 0.0f;
+    const float powerHeuristicSurface = (sPdf * sPdf) / (sPdf * sPdf + lightPdf * lightPdf);
+    const float minFinalPdf = 1e-5f;
+    if (rnd.w < powerHeuristicSurface) {
+        if (dot(r.normal, surfDir) < 0) { r.isOccluded = true; return; }
+        const float cosWi = sel_max(RTRT_SAFE_COSINE_EPSI, dot(surfDir, normal));
+        beta = sBsdf * cosWi / sel_max(sPdf, minFinalPdf);
+        r.dir = surfDir;
+    } else {
+        if (dot(r.normal, lightDir) < 0) { r.isOccluded = true; return; }
+        const float cosWi = sel_max(RTRT_SAFE_COSINE_EPSI, dot(lightDir, normal));
+        beta = lBsdf * cosWi / sel_max(lightPdf, minFinalPdf);
+        r.dir = lightDir;
+        r.lightIdx = lightIdx;
+        r.isShadowRay = true;
+    }
+    if (isnan3(beta)) beta = f3(0.0f);
+    r.orig = r.pos + r.offset * r.normal;
+}
+
+VD unsigned short f2h_bits(float f) { return __half_as_ushort(__float2half_rn(f)); }
+
+__global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams P) {
+    __shared__ uint32_t sLink[16 * kPtThreads];
+    __shared__ float sT[16 * kPtThreads];
+    __shared__ unsigned int sRays;
+    const int tid = threadIdx.y * kPtBlockX + threadIdx.x;
+    if (tid == 0) sRays = 0;
+    __syncthreads();
+    const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
+    const int iy = P.rowBegin + blockIdx.y * kPtBlockY + threadIdx.y;
+    uint32_t rays = 0;
+    if (ix < P.width && iy < P.rowEnd) {
+        const float4 a = __ldg(P.sc.tlasRows), b = __ldg(P.sc.tlasRows + 1), c = __ldg(P.sc.tlasRows + 2);
+        AABB sceneBox;
+        sceneBox.max = Float3{sel_max(a.x, c.x), sel_max(a.y, c.y), sel_max(a.z, c.z)};
+        sceneBox.min = Float3{sel_min(b.x, a.w), sel_min(b.y, b.w), sel_min(b.z, c.w)};
+        uint32_t* stL = sLink + tid; float* stT = sT + tid;
+
+        RayState r;
+        r.beta0 = f3(1.0f); r.beta1 = f3(1.0f);
+        r.hitLight = false; r.lightIdx = kDefaultLightId; r.isHitProcessed = true; r.isOccluded = false; r.isShadowRay = false;
+        r.isDiffuse = false; r.hit = false; r.matId = 0; r.matType = 0; r.objectIdx = -1;
+        r.normal = f3(0, -1, 0); r.fakeNormal = f3(0.0f); r.albedo = f3(1.0f); r.pos = f3(0.0f);
+        r.rayConeWidth = 0.0f; r.depth = 0.0f; r.offset = 0.0f; r.normalDotRayDir = 0.0f; r.isRayIntoSurface = false;
+        r.rayConeSpread = ray_cone_width(P.camera, ix, iy);
+        Float4 rnd[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int si = P.frameNum * 4 + k;                                  // src/pathtrace.cuh:53-62
+            rnd[k] = Float4{blue_rand(P.bn, ix, iy, si, 0), blue_rand(P.bn, ix, iy, si, 1), blue_rand(P.bn, ix, iy, si, 2), blue_rand(P.bn, ix, iy, si, 3)};
+        }
+        Float2 sampleUv;
+        generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd[0].x, rnd[0].y}, Float2{rnd[0].z, rnd[0].w});
+        ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        float outDepth = r.depth;
+        const unsigned short mask = (unsigned short)r.matId;
+        Float2 motion{0.0f, 0.0f};
+        if (r.hit) {                                                            // HistoryCamera::WorldToScreenSpace src/kernel.cuh:144-151
+            const Float3 v = mul(P.historyCamera.invCamMat, r.pos - P.historyCamera.pos);
+            const Float2 ndc = (Float2{v.x, v.y} / v.z) / P.camera.tanHalfFov;
+            motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
+        }
+        motion = motion + 0.5f;
+        glossy_interaction(r, rnd[0].x); ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        glossy_interaction(r, rnd[0].y); ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        glossy_interaction(r, rnd[0].z);
+        diffuse_interaction(0, P, r, r.beta1, rnd[0], rnd[1]);
+        Float3 outNormal = r.fakeNormal;
+        ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        glossy_interaction(r, rnd[0].w);
+        diffuse_interaction(1, P, r, r.beta0, rnd[2], rnd[3]);
+        ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        Float3 L0 = f3(0.0f);                                                   // GetLightSource src/light.cuh:275-305
+        if (r.hitLight && !r.isOccluded && r.matType == MAT_SKY) L0 = env_light(P.env, r.dir);
+        Float3 L2 = (L0 * r.beta0) * r.beta1;
+        if (isnan3(L2)) L2 = f3(0.0f);                                          // NAN_DETECTER src/pathtrace.cuh:113-117
+        if (isnan3(outNormal)) outNormal = f3(0.0f);
+        if (outDepth != outDepth) outDepth = 0.0f;
+        if (motion.x != motion.x || motion.y != motion.y) motion = Float2{0.0f, 0.0f};
+        L2 = Float3{clampf(L2.x, 0.0f, 10.0f), clampf(L2.y, 0.0f, 10.0f), clampf(L2.z, 0.0f, 10.0f)};
+        L2 = L2 / r.albedo;
+        const size_t i = (size_t)iy * P.width + ix;
+        P.color[i] = make_ushort4(f2h_bits(L2.x), f2h_bits(L2.y), f2h_bits(L2.z), mask);
+        P.normal[i] = make_ushort4(f2h_bits(outNormal.x), f2h_bits(outNormal.y), f2h_bits(outNormal.z), f2h_bits(0.0f));
+        P.albedo[i] = make_ushort4(f2h_bits(r.albedo.x), f2h_bits(r.albedo.y), f2h_bits(r.albedo.z), f2h_bits(0.0f));
+        P.depth[i] = __float2half_rn(outDepth);
+        P.motion[i] = __float22half2_rn(make_float2(motion.x, motion.y));
+    }
+    // rays traced: warp reduce -> one shared atomic per warp -> one global atomic per CTA
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
+    if ((tid & 31) == 0) atomicAdd(&sRays, rays);
+    __syncthreads();
+    if (tid == 0 && P.rayCounter) atomicAdd(P.rayCounter, (unsigned long long)sRays);
+}
+
+SceneView make_scene_view(const Context& c);   // traverse.cu
+
+int launch_pathtrace(Context& c) {
+    if (!c.bvhValid) return c.fail(RTRT_ERR_STATE, "rtrt_pathtrace: BVH not built");
+    if (!c.cameraSet) return c.fail(RTRT_ERR_STATE, "rtrt_pathtrace: camera not set");
+    int rc = ensure_frame_resources(c);       // G-buffers, blue noise, default materials / textures, sky
+    if (rc) return rc;
+    PathTraceParams P{};
+    P.sc = make_scene_view(c);
+    P.materials = c.dMaterials; P.materialsIdx = c.dMaterialsIdx; P.numMaterials = c.numMaterials; P.numMaterialsIdx = c.numMaterialsIdx;
+    P.camera = c.camera; P.historyCamera = c.historyCamera;
+    P.env.sky = reinterpret_cast<const float4*>(c.dSky); P.env.skyCdf = c.dSkyCdf;
+    P.env.sun = reinterpret_cast<const float4*>(c.dSun); P.env.sunCdf = c.dSunCdf;
+    P.env.sunDir = c.sunDir; P.env.sunAngleCosThetaMax = c.sunAngleCosThetaMax;
+    P.bn.sobol = c.dBlueNoise; P.bn.scramble = c.dBlueNoise + 65536; P.bn.rank = c.dBlueNoise + 65536 + 131072;
+    for (int t = 0; t < 2; ++t) P.tex[t] = c.tex[t];
+    P.frameNum = c.frameNum; P.width = c.width; P.height = c.height;
+    P.rowBegin = c.rowBegin; P.rowEnd = c.rowEnd;
+    P.color = reinterpret_cast<ushort4*>(c.dColor); P.normal = reinterpret_cast<ushort4*>(c.dNormal);
+    P.albedo = reinterpret_cast<ushort4*>(c.dAlbedo); P.depth = reinterpret_cast<__half*>(c.dDepth);
+    P.motion = reinterpret_cast<__half2*>(c.dMotion);
+    P.rayCounter = c.dRayCounter;
+    RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, sizeof(unsigned long long), c.stream));
+    const int rows = c.rowEnd - c.rowBegin;
+    const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
+    k_pathtrace<<<grid, block, 0, c.stream>>>(P);
+    c.launches += 1;
+    RTRT_CUDA(c, cudaGetLastError());
+    return RTRT_OK;
+}
+
+}  // namespace rtrt
