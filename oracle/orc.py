@@ -235,3 +235,38 @@ def pathtrace(bvh, camera, width, height, frame_num, sky, history_camera=None, m
     if rc:
         raise RuntimeError(f"orc_pathtrace failed: {rc}")
     return f
+
+
+# --------------------------------------------------------------------------------------------------
+# stage 3: denoise
+# --------------------------------------------------------------------------------------------------
+COLOR_DTYPE = np.dtype([("rgb", "<f2", 3), ("mask", "<u2")])
+DENOISE_DEFAULTS = np.array([100.0, 0.1, 100.0, 100.0, 0.01, 100.0, 100.0, 0.1, 100.0, 0.001, 0.001], np.float32)   # src/settingParams.h:144-157
+
+
+class DenoiseState:
+    """History carried from frame to frame (AccumulationColorBuffer, HistoryColorBuffer, HistoryDepthBuffer)."""
+
+    def __init__(self, width, height):
+        n = width * height
+        self.W, self.H = width, height
+        self.accum = np.zeros(n, COLOR_DTYPE); self.history_color = np.zeros(n, COLOR_DTYPE); self.history_depth = np.zeros(n, np.float16)
+        self.noise8 = np.zeros(((height + 7) // 8) * ((width + 7) // 8), np.float16)
+        self.noise16 = np.zeros(((height + 15) // 16) * ((width + 15) // 16), np.float16)
+
+
+def denoise(state, frame_num, color, normal, depth, motion, albedo, params=None, passes=(1, 1, 1, 1), threads=None):
+    """TemporalSpatialDenoising with ping-pong semantics.  color: COLOR_DTYPE[n]; normal/albedo: f2[n,4]; depth: f2[n];
+    motion: f2[n,2].  Returns the denoised colour (COLOR_DTYPE) and updates `state` in place."""
+    lib = load()
+    out = np.ascontiguousarray(color, COLOR_DTYPE).copy()
+    normal = np.ascontiguousarray(normal, np.float16); depth = np.ascontiguousarray(depth, np.float16)
+    motion = np.ascontiguousarray(motion, np.float16); albedo = np.ascontiguousarray(albedo, np.float16)
+    p = np.ascontiguousarray(DENOISE_DEFAULTS if params is None else params, np.float32)
+    ps = np.ascontiguousarray(passes, np.int32)
+    rc = lib.orc_denoise(C.c_int(state.W), C.c_int(state.H), C.c_int(frame_num), _p(p), _p(ps), _p(out), _p(normal), _p(depth), _p(motion),
+                         _p(albedo), _p(state.accum), _p(state.history_color), _p(state.history_depth), _p(state.noise8), _p(state.noise16),
+                         C.c_int(threads or default_threads()))
+    if rc:
+        raise RuntimeError(f"orc_denoise failed: {rc}")
+    return out

@@ -1,5 +1,428 @@
-// Stage 3 placeholder (replaced by the real denoiser below in this round).
+// Stage 3 — temporal + edge-aware spatial denoiser for sm_100a (rtrt_denoise).
+//
+// Restates RayTracer::TemporalSpatialDenoising (src/denoising.cu:5-188) and its kernels
+// (src/temporalDenoising.cuh: TemporalFilter :610-893, CalculateTileNoiseLevel :33-91, TileNoiseLevel8x8to16x16
+// :93-102, SpatialFilter7x7 :317-492, SpatialFilterGlobal5x5<3|6|12> :495-608, ApplyAlbedo :1127-1139,
+// TemporalFilter2 :896-1111, CopyToHistory* :142-170) with the same formulas, tap sets, thresholds and the same
+// half-precision store points, but
+//   * PING-PONG buffers instead of in-place filtering (the reference's in-place passes race across tiles, so its
+//     output is not even deterministic),
+//   * 6 launches instead of 12: the two noise-level kernels are folded into the pass that produces the colours
+//     they measure (tile statistics come out of shared memory, same shuffle order as WarpReduceSum), the
+//     accumulation copy is a second store of the 7x7 pass, ApplyAlbedo + TemporalFilter2 + the history copies
+//     are one pass.  Pass-wise traffic drops from 252 B/px to ~150 B/px.
+// Buffers are linear (8-byte pixels: half3 colour + u16 mask), read through the read-only path.
 #include "context.h"
+#include "rtrt_vec.cuh"
+#include <cuda_fp16.h>
+
 namespace rtrt {
-int launch_denoise(Context& c) { return c.fail(RTRT_ERR_STATE, "rtrt_denoise: not implemented yet"); }
+
+struct DnParams {
+    int W, H, frameNum;
+    float local_n, local_d, local_m, large_n, large_d, large_m, temp_n, temp_d, temp_m, thr_local, thr_large;
+    const ushort4* __restrict__ normal; const __half* __restrict__ depth; const __half2* __restrict__ motion;
+    const ushort4* __restrict__ albedo;
+    __half* noise8; __half* noise16;
+};
+
+__constant__ float cG3[9] = {0.0578968, 0.0921378, 0.0584323, 0.0921378, 0.146629, 0.09299, 0.0584322, 0.0929898, 0.0589727};
+__constant__ float cG5[25] = {0.00360466, 0.0144464, 0.0229902, 0.01458, 0.0036719, 0.0144464, 0.0578968, 0.0921378, 0.0584323, 0.0147159,
+                              0.0229902, 0.0921378, 0.146629, 0.09299, 0.023419, 0.01458, 0.0584322, 0.0929898, 0.0589727, 0.014852,
+                              0.00367191, 0.0147158, 0.0234191, 0.0148519, 0.0037404};
+__constant__ float cG7[49] = {3.47404e-05, 0.000353875, 0.00141822, 0.00225698, 0.00143134, 0.000360475, 3.57221e-05,
+                              0.000353875, 0.00360466, 0.0144464, 0.0229902, 0.01458, 0.0036719, 0.000363875,
+                              0.00141822, 0.0144464, 0.0578968, 0.0921378, 0.0584323, 0.0147159, 0.0014583,
+                              0.00225698, 0.0229902, 0.0921378, 0.146629, 0.09299, 0.023419, 0.00232076,
+                              0.00143134, 0.01458, 0.0584322, 0.0929898, 0.0589727, 0.014852, 0.00147179,
+                              0.000360475, 0.00367191, 0.0147158, 0.0234191, 0.0148519, 0.0037404, 0.000370662,
+                              3.57221e-05, 0.000363875, 0.0014583, 0.00232075, 0.00147179, 0.000370662, 3.67315e-05};
+
+VD float h2f(unsigned short b) { return __half2float(__ushort_as_half(b)); }
+VD unsigned short f2h(float f) { return __half_as_ushort(__float2half_rn(f)); }
+VD Float3 px_rgb(ushort4 p) { return Float3{h2f(p.x), h2f(p.y), h2f(p.z)}; }
+VD ushort4 px_pack(Float3 c, unsigned short w) { return make_ushort4(f2h(c.x), f2h(c.y), f2h(c.z), w); }
+VD Float3 min3f(Float3 a, Float3 b) { return Float3{sel_min(a.x, b.x), sel_min(a.y, b.y), sel_min(a.z, b.z)}; }
+VD Float3 rgb_to_ycocg(Float3 c) { const float t1 = c.x + c.z, t2 = c.y * 2.0f; return Float3{t1 + t2, (c.x - c.z) * 2.0f, t2 - t1}; }
+VD Float3 ycocg_to_rgb(Float3 y) { const float t = y.x - y.z; return Float3{t + y.y, y.x + y.z, t - y.y} * 0.25f; }
+VD ushort4 ld_px(const ushort4* __restrict__ img, int W, int H, int x, int y) {      // surface clamp addressing
+    x = clampi(x, 0, W - 1); y = clampi(y, 0, H - 1);
+    return __ldg(img + (size_t)y * W + x);
 }
+
+// SampleBicubicSmoothStep<Load2DFuncHalf3Ushort1>, default boundary (src/sampler.cuh:498-541)
+VD Float3 sample_history(const ushort4* __restrict__ img, int W, int H, Float2 uv) {
+    const BicubicTaps t = bicubic_taps(uv, W, H);
+    Float3 out = f3(0.0f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) out = out + px_rgb(ld_px(img, W, H, t.x0 + (i & 1), t.y0 + (i >> 1))) * t.w[i];
+    return out / t.sum;
+}
+
+// blend tail shared by TemporalFilter (:861-889) and TemporalFilter2 (:1079-1107)
+VD Float3 temporal_blend(Float3 colorValue, Float3 hist, float lumaHistory, float lumaMin, float lumaMax, float lumaCurrent, float base) {
+    float blend = base;
+    blend *= 0.2f + 0.8f * clampf(0.5f * sel_min(fabsf(lumaHistory - lumaMin), fabsf(lumaHistory - lumaMax)) / sel_max(sel_max(lumaHistory, lumaCurrent), 1e-4f));
+    float wA = blend * sel_max(0.0001f, 1.0f / (lumaCurrent + 4.0f));
+    float wB = (1.0f - blend) * sel_max(0.0001f, 1.0f / (lumaHistory + 4.0f));
+    const float s = wA + wB;
+    const float ws = 1.0f / ((fabsf(s) > 1e-20f) ? s : copysignf(1e-20f, s));            // SafeDivide
+    wA *= ws; wB *= ws;
+    return colorValue * wA + hist * wB;
+}
+
+// ---- tile noise statistics out of shared memory: CalculateTileNoiseLevel (:33-91) + 8x8 -> 16x16 (:93-102) ----
+// sOut = the 16x16 block's output colours (half-rounded, as stored); sDepth = its depths.  Warps 0..3 take one 8x8
+// tile each with the reference's lane mapping and shfl_down tree; thread 0 then averages to the 16x16 level.
+__device__ __forceinline__ void block_noise_levels(const DnParams& P, const ushort4* sOut, const unsigned short* sDepth, float* sN8, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int gw = (P.W + 7) / 8, gh = (P.H + 7) / 8;
+    if (warp < 4) {
+        const int t8x = blockIdx.x * 2 + (warp & 1), t8y = blockIdx.y * 2 + (warp >> 1);
+        const int tx = lane & 7, ty = lane >> 3;
+        float l1, l2, b1, b2;
+        {
+            // pixel coordinates are clamped to the image like the surface reads, then made block-local
+            const int gx = min(t8x * 8 + tx, P.W - 1) - blockIdx.x * 16;
+            const int gy1 = min(t8y * 8 + 2 * ty, P.H - 1) - blockIdx.y * 16, gy2 = min(t8y * 8 + 2 * ty + 1, P.H - 1) - blockIdx.y * 16;
+            const bool in = gx >= 0 && gx < 16 && gy1 >= 0 && gy1 < 16 && gy2 >= 0 && gy2 < 16;   // false only for tiles fully outside the image
+            const ushort4 p1 = in ? sOut[gy1 * 16 + gx] : make_ushort4(0, 0, 0, 0), p2 = in ? sOut[gy2 * 16 + gx] : make_ushort4(0, 0, 0, 0);
+            l1 = getmax3(px_rgb(p1)); l2 = getmax3(px_rgb(p2));
+            b1 = (in && h2f(sDepth[gy1 * 16 + gx]) >= kRayMax) ? 1.0f : 0.0f;
+            b2 = (in && h2f(sDepth[gy2 * 16 + gx]) >= kRayMax) ? 1.0f : 0.0f;
+        }
+        float l12 = l1 * l1, l22 = l2 * l2;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            b1 += __shfl_down_sync(0xffffffffu, b1, o); b2 += __shfl_down_sync(0xffffffffu, b2, o);
+            l1 += __shfl_down_sync(0xffffffffu, l1, o); l12 += __shfl_down_sync(0xffffffffu, l12, o);
+            l2 += __shfl_down_sync(0xffffffffu, l2, o); l22 += __shfl_down_sync(0xffffffffu, l22, o);
+        }
+        if (lane == 0) {
+            const float notSky = 1.0f - (b1 + b2) / 64.0f;
+            const float ave = (l1 + l2) / 64.0f, aveSq = ave * ave, sqAve = (l12 + l22) / 64.0f;
+            const float var = sel_max(1e-20f, sqAve - aveSq);
+            float noise = var / sel_max(aveSq, 1e-20f);
+            noise *= notSky;
+            const __half hn = __float2half_rn(noise);
+            sN8[warp] = __half2float(hn);
+            if (t8x < gw && t8y < gh) P.noise8[(size_t)t8y * gw + t8x] = hn;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        // tiles beyond the 8x8 grid read the clamped (= last valid) tile, like the surface read in :97-100
+        const bool xo = blockIdx.x * 2 + 1 >= gw, yo = blockIdx.y * 2 + 1 >= gh;
+        const float v1 = sN8[0], v2 = sN8[xo ? 0 : 1], v3 = sN8[yo ? 0 : 2], v4 = sN8[(yo ? 0 : 2) + (xo ? 0 : 1)];
+        P.noise16[(size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x] = __float2half_rn((v1 + v2 + v3 + v4) / 4);
+    }
+}
+
+// edge-stopping weight shared by the three bilateral filters
+VD float bilateral_weight(Float3 n0, Float3 n1, float d0, float d1, bool maskDiffers, float sigN, float sigD, float sigM, float floorDot, float g) {
+    float w = 1.0f;
+    w *= powf(sel_max(dot(n0, n1), floorDot), sigN);
+    const float dd = (d0 - d1) / sigD;
+    w *= expf(-0.5f * dd * dd);
+    w *= maskDiffers ? 1.0f / sigM : 1.0f;
+    w *= g;
+    return w;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Pass A: TemporalFilter (+ tile noise of its output).  16x16 pixels per CTA, 18x18 staged tile.
+// -------------------------------------------------------------------------------------------------------------------
+template <bool FILTER>
+__global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ushort4* __restrict__ in, const ushort4* __restrict__ accum, ushort4* __restrict__ out) {
+    constexpr int T = 18;
+    __shared__ ushort4 sC[T * T];
+    __shared__ ushort4 sG[T * T];            // normal.xyz (half) + depth (half)
+    __shared__ ushort4 sOut[256];
+    __shared__ unsigned short sDepth[256];
+    __shared__ float sN8[4];
+    const int tid = threadIdx.y * 16 + threadIdx.x;
+    const int x0 = blockIdx.x * 16 - 1, y0 = blockIdx.y * 16 - 1;
+    for (int i = tid; i < T * T; i += 256) {
+        const int gx = clampi(x0 + i % T, 0, P.W - 1), gy = clampi(y0 + i / T, 0, P.H - 1);
+        const size_t g = (size_t)gy * P.W + gx;
+        sC[i] = __ldg(in + g);
+        ushort4 n = __ldg(P.normal + g);
+        n.w = __half_as_ushort(__ldg(P.depth + g));
+        sG[i] = n;
+    }
+    __syncthreads();
+    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const int ci = (threadIdx.y + 1) * T + threadIdx.x + 1;
+    ushort4 result = sC[ci];
+    const ushort4 cg = sG[ci];
+    if (FILTER && x < P.W && y < P.H) {
+        const Float3 colorValue = px_rgb(result), normalValue = px_rgb(cg);
+        const float depthValue = h2f(cg.w);
+        const unsigned short maskValue = result.w;
+        if (!(depthValue >= kRayMax)) {
+            Float3 nMax = rgb_to_ycocg(colorValue), nMin = nMax, filtered = f3(0.0f);
+            float wsum = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 9; ++j) {
+                const int xo = j % 3, yo = j / 3;
+                const int si = (threadIdx.y + yo) * T + threadIdx.x + xo;
+                const ushort4 q = sC[si], g = sG[si];
+                const Float3 color = px_rgb(q);
+                const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, P.temp_n, P.temp_d, P.temp_m, 0.0f, cG3[j]);
+                filtered = filtered + color * w; wsum += w;
+                const Float3 nc = rgb_to_ycocg(color);
+                nMax = max3f(nMax, nc); nMin = min3f(nMin, nc);
+            }
+            if (wsum > 0.0f) filtered = filtered / wsum; else filtered = f3(0.0f);
+            if (isnan3(filtered)) filtered = f3(0.0f);
+            const float2 mv = __half22float2(__ldg(P.motion + (size_t)y * P.W + x));
+            const Float2 huv = (Float2{(float)x, (float)y} + 0.5f) * Float2{1.0f / (float)P.W, 1.0f / (float)P.H} + (Float2{mv.x, mv.y} - 0.5f);
+            if (huv.x < 0 || huv.y < 0 || huv.x > 1.0f || huv.y > 1.0f) {
+                result = px_pack(filtered, maskValue);
+            } else {
+                Float3 hist = sample_history(accum, P.W, P.H, huv);
+                Float3 hy = rgb_to_ycocg(hist);
+                hy = Float3{clampf(hy.x, nMin.x, nMax.x), clampf(hy.y, nMin.y, nMax.y), clampf(hy.z, nMin.z, nMax.z)};
+                hist = ycocg_to_rgb(hy);
+                const float lumaCurrent = rgb_to_ycocg(colorValue).x;
+                float discard = 0.0f;
+                const int hx = (int)floorf(huv.x * P.W), hyy = (int)floorf(huv.y * P.H);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) discard += (maskValue != ld_px(accum, P.W, P.H, hx + (i & 1), hyy + (i >> 1)).w) ? 1.0f : 0.0f;
+                discard /= 4.0f;
+                hist = hist * (1.0f - discard) + filtered * discard;
+                const float lumaHistory = rgb_to_ycocg(hist).x;
+                if (isnan3(hist)) hist = f3(0.0f);
+                Float3 o = temporal_blend(colorValue, hist, lumaHistory, nMin.x, nMax.x, lumaCurrent, 1.0f / 8.0f);
+                if (isnan3(o)) o = f3(0.0f);
+                result = px_pack(o, maskValue);
+            }
+        }
+    }
+    if (FILTER && x < P.W && y < P.H) out[(size_t)y * P.W + x] = result;
+    sOut[tid] = result; sDepth[tid] = cg.w;
+    __syncthreads();
+    block_noise_levels(P, sOut, sDepth, sN8, tid);
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Pass B: SpatialFilter7x7 (24 of 49 taps, parity-alternating) + accumulation copy + tile noise of its output.
+// 16x16 pixels per CTA, 22x22 staged tile.  gate16 = noise level of the INPUT (written by the previous pass).
+// -------------------------------------------------------------------------------------------------------------------
+template <bool FILTER>
+__global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, ushort4* __restrict__ accumOut,
+                                                     const __half* __restrict__ gate16, int wantNoise) {
+    constexpr int T = 22;
+    __shared__ ushort4 sC[T * T];
+    __shared__ ushort4 sG[T * T];
+    __shared__ ushort4 sOut[256];
+    __shared__ unsigned short sDepth[256];
+    __shared__ float sN8[4];
+    const int tid = threadIdx.y * 16 + threadIdx.x;
+    const int x0 = blockIdx.x * 16 - 3, y0 = blockIdx.y * 16 - 3;
+    bool active = FILTER;
+    if (FILTER) active = !(__half2float(__ldg(gate16 + (size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_local);
+    const int lo = active ? 0 : 3, hi = active ? T : T - 3;          // gated tiles only need their own 16x16 pixels
+    for (int i = tid; i < T * T; i += 256) {
+        const int lx = i % T, ly = i / T;
+        if (lx < lo || lx >= hi || ly < lo || ly >= hi) continue;
+        const int gx = clampi(x0 + lx, 0, P.W - 1), gy = clampi(y0 + ly, 0, P.H - 1);
+        const size_t g = (size_t)gy * P.W + gx;
+        sC[i] = __ldg(in + g);
+        ushort4 n = __ldg(P.normal + g);
+        n.w = __half_as_ushort(__ldg(P.depth + g));
+        sG[i] = n;
+    }
+    __syncthreads();
+    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const int ci = (threadIdx.y + 3) * T + threadIdx.x + 3;
+    ushort4 result = sC[ci];
+    const ushort4 cg = sG[ci];
+    if (active && x < P.W && y < P.H) {
+        const Float3 normalValue = px_rgb(cg);
+        const float depthValue = h2f(cg.w);
+        const unsigned short maskValue = result.w;
+        if (!(depthValue >= kRayMax)) {
+            Float3 sumC = f3(0.0f); float sumW = 0.0f;
+            int j = P.frameNum % 2;
+#pragma unroll 4
+            for (int i = 0; i < 24; ++i) {
+                const int xo = j % 7, yo = j / 7;
+                const int si = (threadIdx.y + yo) * T + threadIdx.x + xo;
+                const ushort4 q = sC[si], g = sG[si];
+                const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, P.local_n, P.local_d, P.local_m, 0.0001f, cG7[j]);
+                sumC = sumC + px_rgb(q) * w; sumW += w;
+                j += 2;
+            }
+            if (isnan3(sumC)) sumC = f3(0.0f);
+            if (sumW != sumW) sumW = 0.0f;
+            Float3 fin = (sumW == 0.0f) ? f3(0.0f) : sumC / sumW;
+            if (isnan3(fin)) fin = f3(0.0f);
+            result = px_pack(fin, maskValue);
+        }
+    }
+    if (x < P.W && y < P.H) {
+        if (FILTER) out[(size_t)y * P.W + x] = result;
+        if (accumOut) accumOut[(size_t)y * P.W + x] = result;        // CopyToHistoryColorBuffer (:159-170)
+    }
+    if (wantNoise) {
+        sOut[tid] = result; sDepth[tid] = cg.w;
+        __syncthreads();
+        block_noise_levels(P, sOut, sDepth, sN8, tid);
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Pass C: SpatialFilterGlobal5x5<S>, S = 3, 6, 12 — dilated taps straight from global memory (L1/L2 resident).
+// -------------------------------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, const __half* __restrict__ gate16) {
+    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    if (x >= P.W || y >= P.H) return;
+    const size_t c = (size_t)y * P.W + x;
+    ushort4 result = __ldg(in + c);
+    const bool active = !(__half2float(__ldg(gate16 + (size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_large);
+    if (active) {
+        const Float3 normalValue = px_rgb(__ldg(P.normal + c));
+        const float depthValue = __half2float(__ldg(P.depth + c));
+        const unsigned short maskValue = result.w;
+        if (!(depthValue >= 10e9f)) {
+            Float3 sumC = f3(0.0f); float sumW = 0.0f;
+#pragma unroll 5
+            for (int k = 0; k < 25; ++k) {
+                const int i = k % 5, j = k / 5;
+                const int sx = clampi(x + (i - 2) * S, 0, P.W - 1), sy = clampi(y + (j - 2) * S, 0, P.H - 1);
+                const size_t g = (size_t)sy * P.W + sx;
+                const ushort4 q = __ldg(in + g);
+                Float3 color = px_rgb(q);
+                float w = bilateral_weight(normalValue, px_rgb(__ldg(P.normal + g)), depthValue, __half2float(__ldg(P.depth + g)), maskValue != q.w,
+                                           P.large_n, P.large_d, P.large_m, 0.0f, cG5[k]);
+                if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
+                sumC = sumC + color * w; sumW += w;
+            }
+            if (isnan3(sumC)) sumC = f3(0.0f);
+            if (sumW != sumW) sumW = 0.0f;
+            Float3 fin = (sumW == 0.0f) ? f3(0.0f) : sumC / sumW;
+            if (isnan3(fin)) fin = f3(0.0f);
+            result = px_pack(fin, maskValue);
+        }
+    }
+    out[c] = result;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Pass D: ApplyAlbedo (:1127-1139) + TemporalFilter2 (:896-1111) + CopyToHistoryColorDepthBuffer (:142-157).
+// The remodulated colour (half-rounded, mask channel = half(1.0) like the reference's Store2DHalf4) is staged in an
+// 18x18 tile as YCoCg; the history of the previous frame is read from histPrev, this frame's goes to histNext.
+// -------------------------------------------------------------------------------------------------------------------
+template <bool TF2>
+__global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out,
+                                                  const ushort4* __restrict__ histPrev, ushort4* __restrict__ histNext, __half* __restrict__ histDepth) {
+    constexpr int T = 18;
+    __shared__ Float3 sY[T * T];
+    const int tid = threadIdx.y * 16 + threadIdx.x;
+    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const unsigned short kOne = 0x3C00;                                   // half(1.0): what ApplyAlbedo leaves in the mask channel
+    auto remodulated = [&](int gx, int gy) {
+        const size_t g = (size_t)clampi(gy, 0, P.H - 1) * P.W + clampi(gx, 0, P.W - 1);
+        const Float3 c = px_rgb(__ldg(in + g)) * px_rgb(__ldg(P.albedo + g));
+        return px_pack(c, kOne);
+    };
+    ushort4 result;
+    if (TF2) {
+        const int x0 = blockIdx.x * 16 - 1, y0 = blockIdx.y * 16 - 1;
+        for (int i = tid; i < T * T; i += 256) sY[i] = rgb_to_ycocg(px_rgb(remodulated(x0 + i % T, y0 + i / T)));
+        __syncthreads();
+        if (x >= P.W || y >= P.H) return;
+        const Float3 centerY = sY[(threadIdx.y + 1) * T + threadIdx.x + 1];
+        const Float3 colorValue = ycocg_to_rgb(centerY);
+        result = remodulated(x, y);
+        // all masks equal half(1.0) after ApplyAlbedo, so every tap takes part in the min/max
+        Float3 nMax = f3(1.175494351e-38f), nMin = f3(3.402823466e+38f), nMax2 = nMax, nMin2 = nMin;     // Float3(FLT_MIN) / Float3(FLT_MAX), :968-972
+#pragma unroll
+        for (int j = 0; j < 9; ++j) {
+            const int xo = j % 3, yo = j / 3;
+            const Float3 color = sY[(threadIdx.y + yo) * T + threadIdx.x + xo];
+            nMax = max3f(nMax, color); nMin = min3f(nMin, color);
+            if (abs(xo - 1) + abs(yo - 1) <= 1) { nMax2 = max3f(nMax2, color); nMin2 = min3f(nMin2, color); }
+        }
+        nMax = (nMax + nMax2) / 2.0f; nMin = (nMin + nMin2) / 2.0f;
+        const float2 mv = __half22float2(__ldg(P.motion + (size_t)y * P.W + x));
+        const Float2 huv = (Float2{(float)x, (float)y} + 0.5f) * Float2{1.0f / (float)P.W, 1.0f / (float)P.H} + (Float2{mv.x, mv.y} - 0.5f);
+        if (!(huv.x < 0 || huv.y < 0 || huv.x > 1.0f || huv.y > 1.0f)) {
+            Float3 ch = sample_history(histPrev, P.W, P.H, huv);
+            Float3 hy = rgb_to_ycocg(ch);
+            hy = Float3{clampf(hy.x, nMin.x, nMax.x), clampf(hy.y, nMin.y, nMax.y), clampf(hy.z, nMin.z, nMax.z)};
+            ch = ycocg_to_rgb(hy);
+            const float lumaCurrent = rgb_to_ycocg(colorValue).x;
+            float discard = 0.0f;
+            const int hx = (int)floorf(huv.x * P.W), hyy = (int)floorf(huv.y * P.H);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) discard += (kOne != ld_px(histPrev, P.W, P.H, hx + (i & 1), hyy + (i >> 1)).w) ? 1.0f : 0.0f;
+            discard /= 4.0f;
+            if (discard != 1.0f) {
+                ch = ch * (1.0f - discard) + colorValue * discard;
+                const float lumaHistory = rgb_to_ycocg(ch).x;
+                Float3 o = temporal_blend(colorValue, ch, lumaHistory, nMin.x, nMax.x, lumaCurrent, 3.0f / 4.0f);
+                if (isnan3(o)) o = f3(0.0f);
+                result = px_pack(o, kOne);
+            }
+        }
+    } else {
+        if (x >= P.W || y >= P.H) return;
+        result = remodulated(x, y);
+    }
+    const size_t c = (size_t)y * P.W + x;
+    out[c] = result;
+    if (histNext) { histNext[c] = result; histDepth[c] = __ldg(P.depth + c); }
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+int launch_denoise(Context& c) {
+    if (!c.dColor || c.gbufW != c.width || c.gbufH != c.height) return c.fail(RTRT_ERR_STATE, "rtrt_denoise: no path-traced frame to denoise");
+    DnParams P{};
+    P.W = c.width; P.H = c.height; P.frameNum = c.frameNum;
+    const rtrt_denoise_params& d = c.denoiseParams;
+    P.local_n = d.local_denoise_sigma_normal; P.local_d = d.local_denoise_sigma_depth; P.local_m = d.local_denoise_sigma_material;
+    P.large_n = d.large_denoise_sigma_normal; P.large_d = d.large_denoise_sigma_depth; P.large_m = d.large_denoise_sigma_material;
+    P.temp_n = d.temporal_denoise_sigma_normal; P.temp_d = d.temporal_denoise_sigma_depth; P.temp_m = d.temporal_denoise_sigma_material;
+    P.thr_local = d.noise_threshold_local; P.thr_large = d.noise_threshold_large;
+    P.normal = reinterpret_cast<const ushort4*>(c.dNormal); P.depth = reinterpret_cast<const __half*>(c.dDepth);
+    P.motion = reinterpret_cast<const __half2*>(c.dMotion); P.albedo = reinterpret_cast<const ushort4*>(c.dAlbedo);
+    P.noise8 = reinterpret_cast<__half*>(c.dNoise); P.noise16 = reinterpret_cast<__half*>(c.dNoise16);
+    const rtrt_pass_settings& ps = c.passSettings;
+    const bool temporal = ps.enableTemporalDenoising != 0, local = ps.enableLocalSpatialFilter != 0, wide = ps.enableWideSpatialFilter != 0,
+               tf2 = ps.enableTemporalDenoising2 != 0, notFirst = c.frameNum != 1;
+    const dim3 grid((c.width + 15) / 16, (c.height + 15) / 16), block(16, 16);
+    ushort4* cur = reinterpret_cast<ushort4*>(c.dColor); ushort4* oth = reinterpret_cast<ushort4*>(c.dColorTmp);
+    ushort4* accum = reinterpret_cast<ushort4*>(c.dAccum);
+    const __half* n16 = reinterpret_cast<const __half*>(c.dNoise16);
+    auto swap = [&]() { ushort4* t = cur; cur = oth; oth = t; };
+    const size_t bytes = (size_t)c.width * c.height * sizeof(ushort4);
+
+    // TemporalFilter (src/denoising.cu:49-64) [+ noise level of its output, :68-76]
+    if (temporal && notFirst) { k_dn_temporal<true><<<grid, block, 0, c.stream>>>(P, cur, accum, oth); swap(); c.launches++; }
+    else if (local) { k_dn_temporal<false><<<grid, block, 0, c.stream>>>(P, cur, accum, oth); c.launches++; }
+    // SpatialFilter7x7 (:90-98) + CopyToHistoryColorBuffer (:100-106) [+ noise level for the wide passes, :110-118]
+    if (local) { k_dn_spatial7<true><<<grid, block, 0, c.stream>>>(P, cur, oth, temporal ? accum : nullptr, n16, wide ? 1 : 0); swap(); c.launches++; }
+    else if (temporal || wide) { k_dn_spatial7<false><<<grid, block, 0, c.stream>>>(P, cur, oth, temporal ? accum : nullptr, n16, wide ? 1 : 0); c.launches++; }
+    // SpatialFilterGlobal5x5<3|6|12> (:132-157)
+    if (wide) {
+        k_dn_spatial5<3><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        k_dn_spatial5<6><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        k_dn_spatial5<12><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        c.launches += 3;
+    }
+    // ApplyAlbedo (:160-163) + TemporalFilter2 (:165-179) + CopyToHistoryColorDepthBuffer (:180-186)
+    ushort4* histPrev = reinterpret_cast<ushort4*>(c.dHistoryColor); ushort4* histNext = reinterpret_cast<ushort4*>(c.dHistoryAlbedo);
+    if (tf2 && notFirst) k_dn_final<true><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, histNext, reinterpret_cast<__half*>(c.dHistoryDepth));
+    else k_dn_final<false><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, tf2 ? histNext : nullptr, reinterpret_cast<__half*>(c.dHistoryDepth));
+    swap(); c.launches++;
+    if (tf2) { void* t = c.dHistoryColor; c.dHistoryColor = c.dHistoryAlbedo; c.dHistoryAlbedo = t; }       // history ping-pong
+    (void)bytes;
+    c.dColor = cur; c.dColorTmp = oth;          // RTRT_BUF_RENDER_COLOR now names the denoised frame
+    RTRT_CUDA(c, cudaGetLastError());
+    return RTRT_OK;
+}
+
+}  // namespace rtrt
