@@ -1,15 +1,21 @@
 #!/usr/bin/env python
 """bench.py — one JSON line for BASELINE.json's metric on BASELINE config 2.
 
-A "step" is one frame of the hot path on the 1 047 552-triangle procedural terrain at 1920x1080:
-  LBVH rebuild (rtrt_build_bvh) -> ray traversal of the frame's rays (rtrt_traverse; the path-trace and
-  denoise stages are added to the step as they land).
-`value`  : Mrays/s, device-resident inputs, CUDA events per step on the library's stream, max over ranks.
-`e2e`    : same metric through the host-buffer entry point (rays H2D + hits D2H inside the timed region).
-N > 1    : the frame is partitioned BY SAMPLE — every rank renders the same view with its own sample index,
-           BVH rebuilt redundantly per GPU (no data-path collective) -> "scaling": "weak".
-`--impl reference` : the reference has no CPU path and does not build here; the reference arm times the CPU
-           oracle (oracle/, the multithreaded C++ restatement) on a bounded sample of the same workload.
+A "step" is ONE FRAME of the hot path (RayTracer::draw, src/kernel.cu:259-362) on the 1 047 552-triangle procedural
+terrain at 1920x1080, 1 spp:
+    LBVH rebuild (rtrt_build_bvh) -> path trace (rtrt_pathtrace: blue-noise sampler, BSDF + one-sample MIS, sky/sun
+    CDF sampling, <= 5 TraverseBvh calls per pixel) -> temporal + a-trous denoise (rtrt_denoise).
+`value`  : Mrays/s = TraverseBvh calls executed (device counter) / whole-step device time, inputs resident in HBM,
+           CUDA events on the library's stream, L2 flushed between steps, max over ranks.
+`e2e`    : same metric through the C ABI with HOST buffers: every step uploads the animated vertex + normal buffers
+           from pinned host memory (rtrt_update_vertices), renders the frame (rtrt_render_frame) and reads the
+           denoised frame back to pinned host memory (rtrt_read_buffer) inside the timed region.
+N > 1    : one process per GPU, the frame is partitioned BY SAMPLE (north_star: "by tile or by sample"): every rank
+           renders the same view with its own sample index (frame number), BVH rebuilt redundantly per GPU, and the
+           denoised frames are averaged with one NCCL all-reduce (the framebuffer combine) inside the timed region
+           -> per-GPU work fixed -> "scaling": "weak".  `--mode rows` shards ONE frame by row bands instead (strong).
+`--impl reference` : the reference has no CPU path and does not build on Linux; this tier's reference arm times the CPU
+           oracle (oracle/, multithreaded C++ restatement) with all host threads on a bounded sample of the workload.
 """
 import argparse
 import importlib
@@ -27,9 +33,15 @@ sys.path.insert(0, ROOT)
 PKG = "real-time-ray-tracing_b200"
 
 WIDTH, HEIGHT = 1920, 1080
-WORKLOAD = "C2: 1080p frame, 1 047 552-tri procedural terrain (1023 batches), two-level LBVH rebuild + traversal"
+SCENE = "C2ref"
+WORKLOAD = ("C2: 1080p 1 spp frame, 1 047 552-tri procedural terrain (1023 batches), per-frame two-level LBVH rebuild + "
+            "path trace (blue noise, Lambert BSDF + MIS, sky/sun) + temporal/a-trous denoise")
 CAMERA = dict(pos=(0, 30, -60), yaw=0.0, pitch=-0.4)
-BUILD_BYTES_PER_TRI = 248          # SURVEY.md §8(d) / BASELINE.md §4
+BUILD_BYTES_PER_TRI = 248          # SURVEY.md §8(d) / BASELINE.md §4 / DESIGN.md
+DENOISE_BYTES_PER_PX = 252         # reference pass sequence; fused lower bound 74
+GBUF_BYTES_PER_PX = 30             # path-trace outputs: colour 8 + normal 8 + albedo 8 + depth 2 + motion 4
+NODE_BYTES, TRI_BYTES = 64, 128    # reference layout bytes per node visit / leaf test (SURVEY §8d "secondary")
+CPU_ROWS = 540                     # rows of the frame the CPU baseline path-traces and denoises (1/2 of 1080)
 
 
 def peaks():
@@ -61,74 +73,115 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.05)
 
     def summary(self):
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons)}
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
 def make_scene(pkg):
-    gx, gz = pkg.scenes.TERRAIN_SIZES["C2ref"]
+    gx, gz = pkg.scenes.TERRAIN_SIZES[SCENE]
     pos, nrm, idx = pkg.scenes.terrain(gx, gz, seed=1)
     cam = pkg.scenes.make_camera(CAMERA["pos"], CAMERA["yaw"], CAMERA["pitch"], WIDTH, HEIGHT)
     return pos, nrm, idx, cam
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (oracle/ — test infrastructure; executed here only as the timed CPU baseline / reference arm)
+# ------------------------------------------------------------------------------------------------------------------
+class CpuArm:
+    """Bounded sample of the step on the host cores: FULL LBVH build + path trace + denoise of CPU_ROWS rows
+    (5 bands of 27 rows spread over the frame).  Whole-frame time is estimated as build + (H / CPU_ROWS) * (pt + dn)."""
+
+    def __init__(self, pkg):
+        from oracle import orc
+        orc.build()
+        self.orc, self.pkg = orc, pkg
+        self.cores = orc.default_threads()
+        self.pos, self.nrm, self.idx, self.cam = make_scene(pkg)
+        self.sky = orc.sky_generate(orc.sun_dir())
+        nb = 5
+        h = CPU_ROWS // nb
+        self.bands = [(int((k + 0.5) * HEIGHT / nb) - h // 2, int((k + 0.5) * HEIGHT / nb) - h // 2 + h) for k in range(nb)]
+        self.state = orc.DenoiseState(WIDTH, h * nb)
+        self.sample = (f"full LBVH build of {self.idx.shape[0]} tris + path trace + denoise of {h * nb}/{HEIGHT} rows "
+                       f"({nb} bands of {h} rows); frame time = build + {HEIGHT}/{h * nb} x (pt + dn)")
+
+    def step(self, frame):
+        orc = self.orc
+        t0 = time.perf_counter()
+        ob = orc.build_bvh(self.pos, self.nrm, self.idx, threads=self.cores)
+        t1 = time.perf_counter()
+        rays = 0
+        parts = []
+        for (b, e) in self.bands:
+            f = orc.pathtrace(ob, self.cam, WIDTH, HEIGHT, frame, self.sky, threads=self.cores, rows=(b, e))
+            rays += int(f.counters[0])
+            parts.append((f, b, e))
+        t2 = time.perf_counter()
+        sl = np.concatenate([np.arange(b * WIDTH, e * WIDTH) for (_, b, e) in parts])
+        f = parts[0][0]
+        def cat(name):
+            return np.concatenate([getattr(p, name)[b * WIDTH:e * WIDTH] for (p, b, e) in parts])
+        n = sl.shape[0]
+        color = np.zeros(n, orc.COLOR_DTYPE)
+        color["rgb"] = cat("color").astype(np.float16); color["mask"] = cat("mask")
+        nrm4 = np.zeros((n, 4), np.float16); nrm4[:, :3] = cat("normal")
+        alb4 = np.zeros((n, 4), np.float16); alb4[:, :3] = cat("albedo")
+        with np.errstate(over="ignore"):
+            depth = cat("depth").astype(np.float16)
+        motion = cat("motion").astype(np.float16)
+        t3 = time.perf_counter()
+        orc.denoise(self.state, frame, color, nrm4, depth, motion, alb4, threads=self.cores)
+        t4 = time.perf_counter()
+        scale = HEIGHT / float(n // WIDTH)
+        build_s, pt_s, dn_s = t1 - t0, t2 - t1, t4 - t3
+        frame_s = build_s + scale * (pt_s + dn_s)
+        return {"rays": rays, "sample_s": build_s + pt_s + dn_s, "frame_s": frame_s, "frame_rays": rays * scale,
+                "build_ms": 1e3 * build_s, "pathtrace_ms_frame": 1e3 * scale * pt_s, "denoise_ms_frame": 1e3 * scale * dn_s}
+
+    def baseline(self, steps=1, warmup=0):
+        rs = [self.step(2 + s) for s in range(warmup + steps)][warmup:]
+        frame_s = float(np.mean([r["frame_s"] for r in rs])); frame_rays = float(np.mean([r["frame_rays"] for r in rs]))
+        val = frame_rays / frame_s / 1e6
+        return val, 1e3 * frame_s, {"value": val, "unit": "Mrays/s", "cores": self.cores, "kind": "port", "sample": self.sample,
+                                    "build_ms": float(np.mean([r["build_ms"] for r in rs])),
+                                    "pathtrace_ms_per_frame": float(np.mean([r["pathtrace_ms_frame"] for r in rs])),
+                                    "denoise_ms_per_frame": float(np.mean([r["denoise_ms_frame"] for r in rs])),
+                                    "pathtrace_mrays_s": float(np.mean([r["frame_rays"] / (r["pathtrace_ms_frame"] * 1e-3) / 1e6 for r in rs]))}
+
+
 def run_reference(args, rank, world):
-    """Reference arm: CPU oracle, all host threads, bounded sample of the same workload."""
+    """Reference arm (this tier): CPU oracle, all host threads, bounded sample of the same workload; rank 0 only."""
     if rank != 0:
         return
     pkg = importlib.import_module(PKG)
-    from oracle import orc
-    orc.build()
-    pos, nrm, idx, cam = make_scene(pkg)
-    rays = pkg.scenes.primary_rays(cam, WIDTH, HEIGHT)
-    rows = 135                                            # 1/8 of the frame's rows, spread over the image
-    sel = rays.reshape(HEIGHT, WIDTH)[::HEIGHT // rows][:rows].reshape(-1).copy()
-    cores = orc.default_threads()
-    times = []
-    for s in range(args.warmup + args.steps):
-        t0 = time.perf_counter()
-        ob = orc.build_bvh(pos, nrm, idx, threads=cores)
-        orc.traverse(ob, sel, threads=cores)
-        dt = time.perf_counter() - t0
-        if s >= args.warmup:
-            times.append(dt)
-    ms = 1e3 * float(np.mean(times))
-    val = sel.shape[0] / (ms * 1e-3) / 1e6
-    sample = f"full LBVH build of 1 047 552 tris + {rows}/{HEIGHT} rows ({sel.shape[0]} rays) of the 1080p frame"
+    arm = CpuArm(pkg)
+    val, ms, cb = arm.baseline(steps=args.steps, warmup=min(args.warmup, 1))
     line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
-            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": arm.sample},
+            "cpu_baseline": cb, "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def cpu_baseline(pkg, pos, nrm, idx, rays):
-    from oracle import orc
-    orc.build()
-    cores = orc.default_threads()
-    rows = 135
-    sel = rays.reshape(HEIGHT, WIDTH)[::HEIGHT // rows][:rows].reshape(-1).copy()
-    t0 = time.perf_counter()
-    ob = orc.build_bvh(pos, nrm, idx, threads=cores)
-    t1 = time.perf_counter()
-    orc.traverse(ob, sel, threads=cores)
-    t2 = time.perf_counter()
-    return {"value": sel.shape[0] / (t2 - t0) / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
-            "sample": f"full LBVH build of {idx.shape[0]} tris + {rows}/{HEIGHT} rows ({sel.shape[0]} rays) of the 1080p frame",
-            "build_ms": 1e3 * (t1 - t0), "traverse_mrays_s": sel.shape[0] / (t2 - t1) / 1e6}
+class DevView:
+    """A borrowed device buffer as a __cuda_array_interface__ object (so torch / NCCL can address it)."""
+
+    def __init__(self, ptr, nbytes, typestr="<f2", itemsize=2):
+        self.__cuda_array_interface__ = {"shape": (nbytes // itemsize,), "typestr": typestr, "data": (ptr, False), "version": 3,
+                                         "strides": None}
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
+    ap.add_argument("--mode", default="samples", choices=["samples", "rows"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -147,90 +200,145 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = importlib.import_module(PKG)        # raises if librtrt.so is missing: no fallback
     pos, nrm, idx, cam = make_scene(pkg)
-    rays = pkg.scenes.primary_rays(cam, WIDTH, HEIGHT)
-    n_rays = rays.shape[0]
+    n_tris, n_px = int(idx.shape[0]), WIDTH * HEIGHT
     hbm_peak, peak_kind = peaks()
 
     rt = pkg.RayTracer(WIDTH, HEIGHT, device=local).init()
     rt.set_mesh(pos, idx, nrm)
+    rt.set_camera(cam, reset_history=True)
+    rows = (0, HEIGHT)
+    if args.mode == "rows" and world > 1:                      # strong scaling: one frame, contiguous row bands
+        rows = (HEIGHT * rank // world, HEIGHT * (rank + 1) // world)
+        rt.set_row_range(*rows)
     stream = torch.cuda.ExternalStream(rt.stream, device=torch.device("cuda", local))
-    d_rays = torch.from_numpy(rays.view(np.uint8).reshape(-1)).cuda()
-    d_hits = torch.empty(n_rays * 16, dtype=torch.uint8, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
-    h_rays = torch.from_numpy(rays.view(np.uint8).reshape(-1).copy()).pin_memory()
-    h_hits = torch.empty(n_rays * 16, dtype=torch.uint8).pin_memory()
+    h_pos = torch.from_numpy(pos.reshape(-1).copy()).pin_memory()
+    h_nrm = torch.from_numpy(nrm.reshape(-1).copy()).pin_memory()
+    h_out = torch.empty(n_px * 8, dtype=torch.uint8).pin_memory()
     torch.cuda.synchronize()
+    frame_no = [1 + (rank if args.mode == "samples" else 0)]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(step_fn, steps, warmup, sub_events=False):
+    def combine():
+        """framebuffer combine across ranks (NCCL over NVLink), on the library's stream"""
+        if world == 1:
+            return
+        ptr, nbytes = rt.get_buffer(pkg.BUF_RENDER_COLOR)
+        with torch.cuda.stream(stream):
+            if args.mode == "samples":
+                t = torch.as_tensor(DevView(ptr, nbytes), device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.AVG)
+            else:
+                t = torch.as_tensor(DevView(ptr, nbytes, "|u1", 1), device="cuda")
+                parts = [t[HEIGHT * r // world * WIDTH * 8: HEIGHT * (r + 1) // world * WIDTH * 8] for r in range(world)]
+                dist.all_gather(parts, parts[rank].clone())
+
+    def step_device(e):
+        rt.set_frame_number(frame_no[0]); frame_no[0] += world if args.mode == "samples" else 1
+        if e: e[0].record(stream)
+        rt.build_bvh()
+        if e: e[1].record(stream)
+        rt.pathtrace()
+        if e: e[2].record(stream)
+        rt.denoise()
+        if e: e[3].record(stream)
+        combine()
+        if e: e[4].record(stream)
+
+    def step_e2e(e):
+        rt.set_frame_number(frame_no[0]); frame_no[0] += world if args.mode == "samples" else 1
+        if e: e[0].record(stream)
+        rt.update_vertices(h_pos.data_ptr(), h_nrm.data_ptr())             # H2D, pinned
+        rt.build_bvh(); rt.pathtrace(); rt.denoise()
+        combine()
+        rt.read_buffer_into(pkg.BUF_RENDER_COLOR, h_out.data_ptr(), h_out.numel())   # D2H + stream sync
+        if e: e[4].record(stream)
+
+    def timed(step_fn, steps, warmup):
         for _ in range(warmup):
             step_fn(None)
         barrier()
         lbefore = rt.timings()["kernel_launches"]
-        evs = []
+        evs, rays = [], 0
         for _ in range(steps):
             with torch.cuda.stream(stream):
                 flush.zero_()                                            # L2 flush, outside the event pair
-            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
             step_fn(e)
             evs.append(e)
+            rays += rt.timings()["rays_traced"]                          # synchronises the stream (outside the event pair)
         barrier()
-        tot = [e[0].elapsed_time(e[2]) for e in evs]
-        first = [e[0].elapsed_time(e[1]) for e in evs]
         nl = rt.timings()["kernel_launches"] - lbefore
-        return float(np.sum(tot)), float(np.mean(first)), float(np.mean(tot) - np.mean(first)), int(nl)
-
-    def step_device(e):
-        if e: e[0].record(stream)
-        rt.build_bvh()
-        if e: e[1].record(stream)
-        rt.traverse_device(d_rays.data_ptr(), n_rays, d_hits.data_ptr())
-        if e: e[2].record(stream)
-
-    def step_e2e(e):
-        if e: e[0].record(stream)
-        rt.build_bvh()
-        if e: e[1].record(stream)
-        rt._check(rt._lib.rtrt_traverse_host(rt._h, h_rays.data_ptr(), n_rays, h_hits.data_ptr(), 0))
-        if e: e[2].record(stream)
+        tot = float(np.sum([e[0].elapsed_time(e[4]) for e in evs]))
+        stages = None
+        if step_fn is step_device:
+            stages = [float(np.mean([e[k].elapsed_time(e[k + 1]) for e in evs])) for k in range(4)]
+        return tot, stages, int(nl), int(rays)
 
     sampler = ClockSampler(local); sampler.start()
-    total_ms, build_ms, trav_ms, launches = timed(step_device, args.steps, args.warmup)
+    total_ms, stages, launches, rays = timed(step_device, args.steps, args.warmup)
     sampler.stop_flag = True; sampler.join()
-    e2e_ms, _, _, _ = timed(step_e2e, max(3, args.steps // 2), 3)
     e2e_steps = max(3, args.steps // 2)
+    e2e_ms, _, _, e2e_rays = timed(step_e2e, e2e_steps, 3)
 
-    t = torch.tensor([total_ms, e2e_ms, build_ms, trav_ms], dtype=torch.float64, device="cuda")
+    # untimed: one frame with the visit counters on -> algorithmic bytes of the traversal
+    rt.set_option("count_visits", 1)
+    rt.set_frame_number(2); rt.pathtrace()
+    tm = rt.timings()
+    node_visits, leaf_tests, rays_cnt = tm["node_visits"], tm["leaf_tests"], tm["rays_traced"]
+    rt.set_option("count_visits", 0)
+
+    t = torch.tensor([total_ms, e2e_ms] + stages, dtype=torch.float64, device="cuda")
+    r = torch.tensor([rays, e2e_rays], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms, build_ms, trav_ms = t.tolist()
+        dist.all_reduce(r, op=dist.ReduceOp.SUM)
+    total_ms, e2e_ms, build_ms, pt_ms, dn_ms, comb_ms = t.tolist()
+    rays, e2e_rays = r.tolist()
     ms_step = total_ms / args.steps
-    value = world * n_rays / (ms_step * 1e-3) / 1e6
-    e2e_val = world * n_rays / (e2e_ms / e2e_steps * 1e-3) / 1e6
+    value = rays / (total_ms * 1e-3) / 1e6
+    e2e_val = e2e_rays / (e2e_ms * 1e-3) / 1e6
 
     if rank == 0:
-        n_tris = idx.shape[0]
+        rows_n = rows[1] - rows[0]
         build_gbs = BUILD_BYTES_PER_TRI * n_tris / (build_ms * 1e-3) / 1e9
+        dn_gbs = DENOISE_BYTES_PER_PX * WIDTH * rows_n / (dn_ms * 1e-3) / 1e9
+        pt_bytes = node_visits * NODE_BYTES + leaf_tests * TRI_BYTES + GBUF_BYTES_PER_PX * WIDTH * rows_n
+        pt_gbs = pt_bytes / (pt_ms * 1e-3) / 1e9
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "width": WIDTH, "height": HEIGHT, "triangles": int(n_tris), "rays_per_step": int(n_rays),
-                       "parallelism": f"sample-partitioned x{world}, BVH rebuilt per GPU", "l2": "flushed between steps (256 MiB memset, outside the event pairs)",
-                       "stages": {"build_bvh_ms": build_ms, "traverse_ms": trav_ms}},
-            "roofline": {"kernel": "k_build_blas (LBVH build, fused gather+sort+emit+refit+TLAS)", "bound": "hbm",
-                         "achieved": build_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": build_gbs / hbm_peak, "traffic": None,
-                         "peak_kind": peak_kind, "algorithmic_bytes_per_launch": BUILD_BYTES_PER_TRI * int(n_tris)},
-            "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": int(n_rays * 32), "d2h_bytes_per_step": int(n_rays * 16)},
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if args.mode == "samples" else "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "width": WIDTH, "height": HEIGHT, "triangles": n_tris, "spp": 1,
+                       "rays_per_step": rays / args.steps,
+                       "parallelism": (f"sample-partitioned x{world}, BVH rebuilt per GPU, NCCL all-reduce of the frame" if args.mode == "samples"
+                                       else f"row bands x{world}, BVH rebuilt per GPU, NCCL all-gather of the frame"),
+                       "l2": "flushed between steps (256 MiB memset, outside the event pairs)",
+                       "stages_ms": {"build_bvh": build_ms, "pathtrace": pt_ms, "denoise": dn_ms, "combine": comb_ms},
+                       "pathtrace_mrays_s": rays / args.steps / (pt_ms * 1e-3) / 1e6,
+                       "build_mtris_s": n_tris / (build_ms * 1e-3) / 1e6},
+            "roofline": {"kernel": "k_pathtrace (dominant: %.0f%% of the step)" % (100 * pt_ms / max(ms_step, 1e-9)), "bound": "hbm",
+                         "achieved": pt_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pt_gbs / hbm_peak, "traffic": None,
+                         "peak_kind": peak_kind, "algorithmic_bytes_per_launch": int(pt_bytes),
+                         "note": "latency/divergence-bound traversal (no RT cores); bytes = node visits x 64 + leaf tests x 128 + 30 B/px G-buffer",
+                         "node_visits_per_ray": node_visits / max(rays_cnt, 1), "leaf_tests_per_ray": leaf_tests / max(rays_cnt, 1)},
+            "roofline_build": {"kernel": "k_build_blas (gather+AABB+Morton+sort+Karras+refit+TLAS, one launch)", "bound": "hbm",
+                               "achieved": build_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": build_gbs / hbm_peak,
+                               "algorithmic_bytes_per_launch": BUILD_BYTES_PER_TRI * n_tris},
+            "roofline_denoise": {"kernel": "k_dn_* (6 launches)", "bound": "hbm", "achieved": dn_gbs, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": dn_gbs / hbm_peak, "algorithmic_bytes_per_step": DENOISE_BYTES_PER_PX * WIDTH * rows_n,
+                                 "note": "252 B/px = the reference's pass-wise traffic; fused lower bound 74 B/px"},
+            "e2e": {"value": e2e_val, "unit": "Mrays/s", "ms_per_step": e2e_ms / e2e_steps,
+                    "h2d_bytes_per_step": int(h_pos.numel() * 4 + h_nrm.numel() * 4), "d2h_bytes_per_step": int(h_out.numel())},
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
         }
-        if not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(pkg, pos, nrm, idx, rays)
+        if not args.no_cpu_baseline and world == 1:
+            _, _, line["cpu_baseline"] = CpuArm(pkg).baseline(steps=1, warmup=0)
         print(json.dumps(line), flush=True)
     rt.cleanup()
     if world > 1:

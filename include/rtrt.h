@@ -68,6 +68,8 @@ typedef struct rtrt_timings {
     float build_bvh_ms, traverse_ms, pathtrace_ms, denoise_ms;
     uint64_t kernel_launches;     /* kernels launched by this library since rtrt_create */
     uint64_t rays_traced;         /* TraverseBvh calls executed by the last pathtrace / traverse */
+    uint64_t node_visits;         /* inner-node visits / leaf (triangle) tests of the last pathtrace; only counted  */
+    uint64_t leaf_tests;          /* when option "count_visits" = 1 (adds register pressure, off by default)        */
 } rtrt_timings;
 
 /* Buffers observable through rtrt_get_buffer.  The first block are the DebugPrintFile observation
@@ -144,12 +146,18 @@ int rtrt_set_mesh_device(rtrt_ctx* ctx, const float* d_pos, const float* d_nrm, 
 /* Mesh file of LoadScene-era format `uint32 triCount; Triangle[triCount]` (src/init.cu:28-50,
  * tool/meshProcessor.cpp:204-208), 128-byte triangles. */
 int rtrt_set_mesh_bin(rtrt_ctx* ctx, const char* path);
+/* Per-frame vertex animation from HOST arrays: replaces the contents of the vertex (and, if non-NULL, normal)
+ * buffer of the current mesh, V x 3 floats each, asynchronously on the context stream (pinned memory makes the
+ * copy overlap).  Topology is unchanged; call rtrt_build_bvh / rtrt_render_frame afterwards.  This is the
+ * host-fed equivalent of MeshDisplace writing vertexBuffer every frame (src/kernel.cu:139-226, :324). */
+int rtrt_update_vertices(rtrt_ctx* ctx, const float* pos, const float* nrm_or_null, uint32_t num_vertices);
 
 /* ---- options ---- */
 int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
  *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
- *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)                      */
+ *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)
+ *   "count_visits"        0/1  : rtrt_pathtrace also counts node visits / leaf tests (rtrt_timings)         */
 
 /* ---- stage 1: RayTracer::BuildBvhLevel1 + BuildBvhLevel2 (src/bvh.cu:7-97) ---- */
 int rtrt_build_bvh(rtrt_ctx* ctx);

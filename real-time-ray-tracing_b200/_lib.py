@@ -38,7 +38,8 @@ class Config(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [("build_bvh_ms", C.c_float), ("traverse_ms", C.c_float), ("pathtrace_ms", C.c_float),
-                ("denoise_ms", C.c_float), ("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64)]
+                ("denoise_ms", C.c_float), ("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64),
+                ("node_visits", C.c_uint64), ("leaf_tests", C.c_uint64)]
 
 
 class SkyParams(C.Structure):      # src/settingParams.h:41-45
@@ -70,6 +71,7 @@ SYMBOLS = {
     "rtrt_set_mesh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
     "rtrt_set_mesh_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
     "rtrt_set_mesh_bin": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_update_vertices": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "rtrt_set_option_i": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "rtrt_build_bvh": (C.c_int, [C.c_void_p]),
     "rtrt_traverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int]),

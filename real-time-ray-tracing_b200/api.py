@@ -124,11 +124,22 @@ class RayTracer:
             assert nrm.shape == pos.shape
         self._check(self._lib.rtrt_set_mesh(self._h, _ptr(pos), _ptr(nrm) if nrm is not None else None, _ptr(idx),
                                             pos.shape[0], idx.shape[0]))
+        self._nverts = pos.shape[0]
 
     def set_mesh_device(self, d_pos, d_nrm, d_idx, num_vertices, num_triangles):
         """Device-resident inputs (ints = device addresses, e.g. torch_tensor.data_ptr()); borrowed."""
         self._check(self._lib.rtrt_set_mesh_device(self._h, C.c_void_p(d_pos), C.c_void_p(d_nrm), C.c_void_p(d_idx),
                                                    num_vertices, num_triangles))
+
+    def update_vertices(self, pos, nrm=None):
+        """Per-frame vertex animation (MeshDisplace, src/kernel.cu:139-226): host arrays or raw host addresses."""
+        if isinstance(pos, int):
+            self._check(self._lib.rtrt_update_vertices(self._h, C.c_void_p(pos), C.c_void_p(nrm) if nrm else None, self._nverts))
+            return
+        pos = np.ascontiguousarray(pos, dtype=np.float32).reshape(-1, 3)
+        if nrm is not None:
+            nrm = np.ascontiguousarray(nrm, dtype=np.float32).reshape(-1, 3)
+        self._check(self._lib.rtrt_update_vertices(self._h, _ptr(pos), _ptr(nrm) if nrm is not None else None, pos.shape[0]))
 
     def set_mesh_bin(self, path):
         self._check(self._lib.rtrt_set_mesh_bin(self._h, str(path).encode()))
@@ -228,6 +239,10 @@ class RayTracer:
         out = np.empty(nbytes // dt.itemsize, dtype=dt)
         self._check(self._lib.rtrt_read_buffer(self._h, which, _ptr(out), nbytes))
         return out
+
+    def read_buffer_into(self, which, host_ptr, nbytes):
+        """Synchronous copy of a buffer into caller-owned (ideally pinned) host memory at address `host_ptr`."""
+        self._check(self._lib.rtrt_read_buffer(self._h, which, C.c_void_p(host_ptr), nbytes))
 
     def sync(self):
         self._check(self._lib.rtrt_sync(self._h))

@@ -221,12 +221,27 @@ int rtrt_set_mesh_bin(rtrt_ctx* ctx, const char* path) {
     return rtrt_set_mesh(ctx, pos.data(), nrm.data(), idx.data(), 3 * n, n);
 }
 
+int rtrt_update_vertices(rtrt_ctx* ctx, const float* pos, const float* nrm, uint32_t V) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (!pos) return c.fail(RTRT_ERR_ARG, "rtrt_update_vertices: null positions");
+    if (!c.dPos || c.numTris == 0) return c.fail(RTRT_ERR_STATE, "rtrt_update_vertices: no mesh set");
+    if (!c.ownsMesh) return c.fail(RTRT_ERR_STATE, "rtrt_update_vertices: mesh buffers are caller-owned (rtrt_set_mesh_device)");
+    if (V != c.numVerts) return c.fail(RTRT_ERR_ARG, "rtrt_update_vertices: vertex count differs from the mesh");
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    RTRT_CUDA(c, cudaMemcpyAsync(c.dPos, pos, (size_t)3 * V * sizeof(float), cudaMemcpyHostToDevice, c.stream));
+    if (nrm) RTRT_CUDA(c, cudaMemcpyAsync(c.dNrm, nrm, (size_t)3 * V * sizeof(float), cudaMemcpyHostToDevice, c.stream));
+    c.bvhValid = false;
+    return RTRT_OK;
+}
+
 int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     CTX_OR_FAIL(ctx);
     Context& c = ctx->c;
     if (!name) return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: null name");
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 32) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..32"); c.stackSize = (int)value; return RTRT_OK; }
+    if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }
     return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: unknown option");
 }
@@ -361,9 +376,9 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
             c.evPending[s] = false;
         }
     if (c.raysOnDevice && c.dRayCounter) {
-        unsigned long long r = 0;
-        RTRT_CUDA(c, cudaMemcpy(&r, c.dRayCounter, sizeof(r), cudaMemcpyDeviceToHost));
-        c.timings.rays_traced = r; c.raysOnDevice = false;
+        unsigned long long r[3] = {0, 0, 0};
+        RTRT_CUDA(c, cudaMemcpy(r, c.dRayCounter, sizeof(r), cudaMemcpyDeviceToHost));
+        c.timings.rays_traced = r[0]; c.timings.node_visits = r[1]; c.timings.leaf_tests = r[2]; c.raysOnDevice = false;
     }
     c.timings.kernel_launches = c.launches;
     *out = c.timings;

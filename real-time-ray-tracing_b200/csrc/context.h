@@ -36,6 +36,7 @@ struct Context {
     Ray* dRayStage = nullptr; Hit* dHitStage = nullptr; uint32_t rayStageCap = 0;
     int stackSize = 16;      // src/traverse.h:28
     int maxLoop = 1024;      // src/traverse.h:132
+    bool countVisits = false;
 
     // ---- frame state: ConstBuffer (src/kernel.cuh:211-231) + Buffer2DManager (src/init.cu:441-584) ----
     int width = 0, height = 0;               // render size

@@ -77,12 +77,15 @@ VD void update_material(const PathTraceParams& P, RayState& r) {
 }
 
 // src/traverse.cuh:64-225 — guards, traversal, hit record (src/traverse.h:161-174), normal flipping, material
-VD void ray_scene_intersect(const PathTraceParams& P, const AABB& sceneBox, RayState& r, uint32_t* stackLink, float* stackT, uint32_t& rays) {
+template <bool COUNT>
+VD void ray_scene_intersect(const PathTraceParams& P, const AABB& sceneBox, RayState& r, uint32_t* stackLink, float* stackT, uint32_t& rays,
+                            uint32_t& nodeVisits, uint32_t& leafTests) {
     if (r.hitLight || !r.isHitProcessed || r.isOccluded) return;
     r.isHitProcessed = false;
     ++rays;
     const RayPrep rp = prepare_ray(r.orig, r.dir, sceneBox);
-    const TraverseResult h = traverse_bvh<16, false>(P.sc, rp, 0, stackLink, stackT, kPtThreads);
+    const TraverseResult h = traverse_bvh<16, COUNT>(P.sc, rp, 0, stackLink, stackT, kPtThreads);
+    if (COUNT) { nodeVisits += h.nodeVisits; leafTests += h.leafTests; }
     r.objectIdx = h.tri;
     r.offset = 1e-7f;
     r.normal = f3(0.0f);
@@ -203,6 +206,7 @@ VD void diffuse_interaction(int bounce, const PathTraceParams& P, RayState& r, F
 
 VD unsigned short f2h_bits(float f) { return __half_as_ushort(__float2half_rn(f)); }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams P) {
     __shared__ uint32_t sLink[16 * kPtThreads];
     __shared__ float sT[16 * kPtThreads];
@@ -212,7 +216,7 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
     __syncthreads();
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
     const int iy = P.rowBegin + blockIdx.y * kPtBlockY + threadIdx.y;
-    uint32_t rays = 0;
+    uint32_t rays = 0, nodeVisits = 0, leafTests = 0;
     if (ix < P.width && iy < P.rowEnd) {
         const float4 a = __ldg(P.sc.tlasRows), b = __ldg(P.sc.tlasRows + 1), c = __ldg(P.sc.tlasRows + 2);
         AABB sceneBox;
@@ -235,7 +239,7 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
         }
         Float2 sampleUv;
         generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd[0].x, rnd[0].y}, Float2{rnd[0].z, rnd[0].w});
-        ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
         float outDepth = r.depth;
         const unsigned short mask = (unsigned short)r.matId;
         Float2 motion{0.0f, 0.0f};
@@ -245,15 +249,15 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
             motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
         }
         motion = motion + 0.5f;
-        glossy_interaction(r, rnd[0].x); ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
-        glossy_interaction(r, rnd[0].y); ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        glossy_interaction(r, rnd[0].x); ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
+        glossy_interaction(r, rnd[0].y); ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
         glossy_interaction(r, rnd[0].z);
         diffuse_interaction(0, P, r, r.beta1, rnd[0], rnd[1]);
         Float3 outNormal = r.fakeNormal;
-        ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
         glossy_interaction(r, rnd[0].w);
         diffuse_interaction(1, P, r, r.beta0, rnd[2], rnd[3]);
-        ray_scene_intersect(P, sceneBox, r, stL, stT, rays);
+        ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
         Float3 L0 = f3(0.0f);                                                   // GetLightSource src/light.cuh:275-305
         if (r.hitLight && !r.isOccluded && r.matType == MAT_SKY) L0 = env_light(P.env, r.dir);
         Float3 L2 = (L0 * r.beta0) * r.beta1;
@@ -275,6 +279,10 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
     if ((tid & 31) == 0) atomicAdd(&sRays, rays);
     __syncthreads();
     if (tid == 0 && P.rayCounter) atomicAdd(P.rayCounter, (unsigned long long)sRays);
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
+        if ((tid & 31) == 0 && P.rayCounter) { atomicAdd(P.rayCounter + 1, (unsigned long long)nodeVisits); atomicAdd(P.rayCounter + 2, (unsigned long long)leafTests); }
+    }
 }
 
 SceneView make_scene_view(const Context& c);   // traverse.cu
@@ -299,10 +307,11 @@ int launch_pathtrace(Context& c) {
     P.albedo = reinterpret_cast<ushort4*>(c.dAlbedo); P.depth = reinterpret_cast<__half*>(c.dDepth);
     P.motion = reinterpret_cast<__half2*>(c.dMotion);
     P.rayCounter = c.dRayCounter;
-    RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, sizeof(unsigned long long), c.stream));
+    RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));
     const int rows = c.rowEnd - c.rowBegin;
     const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
-    k_pathtrace<<<grid, block, 0, c.stream>>>(P);
+    if (c.countVisits) k_pathtrace<true><<<grid, block, 0, c.stream>>>(P);
+    else k_pathtrace<false><<<grid, block, 0, c.stream>>>(P);
     c.launches += 1;
     RTRT_CUDA(c, cudaGetLastError());
     return RTRT_OK;
