@@ -1,0 +1,116 @@
+#!/usr/bin/env python
+"""Recipe for oracle/_ref/librefcuda.so — the REFERENCE'S OWN CUDA kernels of the hot path, compiled for sm_100.
+
+TEST / BASELINE INFRASTRUCTURE, not product.  Runs only where /root/reference exists (this container); the GPU box
+uses the prebuilt .so (oracle/_ref/ is git-ignored, not gpurun-ignored).  No reference source is copied into the repo.
+
+The reference is Windows/MSVC-only: src/linearMath.h:252-256,400-405,508-519 and src/geometry.h:20-28,81-91 put members
+with constructors inside anonymous structs of unions and declare duplicate member names (z, w), which g++ and nvcc's EDG
+front end reject on Linux.  This recipe therefore
+  1. copies the reference headers the path needs into a scratch directory under /tmp,
+  2. applies the declaration-only patches in PATCHES below (type layout and every function body unchanged: the
+     anonymous-struct aliases `xy`, `xyz`, `zw`, `v0..v2`, `_v3`, `min/max`, `v1..v4` become layout-identical POD proxy
+     members or reference accessors),
+  3. compiles oracle/refcuda/harness.cu (ours: extern "C" launchers around the reference kernels) against them,
+  4. removes the scratch directory.
+Usage: python oracle/refcuda/build_ref.py [--fmad true|false] [--keep]
+"""
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("RTRT_REFERENCE", "/root/reference")
+OUT_DIR = os.path.join(os.path.dirname(HERE), "_ref")
+
+HEADERS = ["linearMath.h", "geometry.h", "geometry.cuh", "bvhNode.cuh", "precision.cuh", "debugUtil.h", "updateGeometry.cuh",
+           "radixSort.cuh", "buildBVH.cuh", "traverse.h", "blueNoiseRandGen.h", "blueNoiseRandGenData.h"]
+
+# POD proxies: same bytes as Float2/Float3, no constructors (so they may live in an anonymous struct), convertible.
+PROXIES = r'''
+struct Float2; struct Float3;
+struct RefPod2 { float x, y; __forceinline__ __host__ __device__ operator Float2() const; };
+struct RefPod3 { float x, y, z; __forceinline__ __host__ __device__ operator Float3() const;
+                 __forceinline__ __host__ __device__ RefPod3& operator=(const Float3& v); };
+'''
+PROXY_DEFS = r'''
+__forceinline__ __host__ __device__ RefPod2::operator Float2() const { return Float2(x, y); }
+__forceinline__ __host__ __device__ RefPod3::operator Float3() const { return Float3(x, y, z); }
+__forceinline__ __host__ __device__ RefPod3& RefPod3::operator=(const Float3& v) { x = v.x; y = v.y; z = v.z; return *this; }
+__forceinline__ __host__ __device__ Float3 operator-(const RefPod3& a) { return Float3(-a.x, -a.y, -a.z); }
+__forceinline__ __host__ __device__ Float3 operator-(const RefPod3& a, float b) { return Float3(a.x - b, a.y - b, a.z - b); }
+__forceinline__ __host__ __device__ Float2 operator/(const RefPod2& a, float b) { return Float2(a.x / b, a.y / b); }
+'''
+
+
+def sub1(text, pattern, repl, what, flags=re.S):
+    new, n = re.subn(pattern, repl, text, count=1, flags=flags)
+    if n != 1:
+        raise RuntimeError(f"patch did not apply: {what}")
+    return new
+
+
+def patch_linear_math(t):
+    t = sub1(t, r"(#pragma once)", r"\1\n#include <float.h>\n", "pragma")
+    # Float3: drop the duplicate-z alias; xy becomes a POD proxy
+    t = sub1(t, r"struct \{ float x, y, z; \};\s*struct \{ Float2 xy; float z; \};",
+             "struct { float x, y, z; };\n\t\tstruct { RefPod2 xy; float _z_alias; };", "Float3 union")
+    # Float4: xyz / xy / zw aliases become POD proxies
+    t = sub1(t, r"struct \{ float x, y, z, w; \};\s*struct \{ Float3 xyz; float w; \};\s*struct \{ Float2 xy; Float2 zw; \};",
+             "struct { float x, y, z, w; };\n\t\tstruct { RefPod3 xyz; float _w_alias; };\n\t\tstruct { RefPod2 xy; RefPod2 zw; };", "Float4 union")
+    # Mat3: column aliases
+    t = sub1(t, r"struct \{\s*Float3 v0, v1, v2;\s*\};\s*Float3 _v3\[3\];", "struct { RefPod3 v0, v1, v2; };\n\t\tRefPod3 _v3p[3];", "Mat3 union")
+    t = t.replace("Float3&       operator[](int i)       { return _v3[i]; }", "Float3&       operator[](int i)       { return *reinterpret_cast<Float3*>(&_v3p[i]); }")
+    t = t.replace("const Float3& operator[](int i) const { return _v3[i]; }", "const Float3& operator[](int i) const { return *reinterpret_cast<const Float3*>(&_v3p[i]); }")
+    # proxies declared before the first struct, defined after Float3
+    t = sub1(t, r"(struct Float2\s*\{)", PROXIES.replace("\\", "\\\\") + r"\n\1", "proxy decl")
+    t = sub1(t, r"(struct Int3\s*\{)", PROXY_DEFS.replace("\\", "\\\\") + r"\n\1", "proxy defs")
+    return t
+
+
+def patch_geometry_h(t):
+    # AABB: { Float3 min; Float3 max; } | float v[6]  ->  float v[6] storage + reference members
+    t = sub1(t, r"union\s*\{\s*struct\s*\{\s*Float3 min;\s*Float3 max;\s*\};\s*float v\[6\];\s*\};",
+             "Float3 min;\n\tFloat3 max;\n\t__host__ __device__ float vAt(int i) const { return (&min.x)[i]; }", "AABB union")
+    t = t.replace("__host__ __device__ float operator[](int i) const { return v[i]; }", "__host__ __device__ float operator[](int i) const { return vAt(i); }")
+    # Triangle: { v1 w1 .. v4 w4 } | Float4 vertices[4]  ->  plain members (vertices[] alias unused on the path)
+    t = sub1(t, r"union\s*\{\s*struct\s*\{\s*(Float3 v1; float w1;\s*Float3 v2; float w2;\s*Float3 v3; float w3;\s*Float3 v4; float w4;)\s*\};\s*Float4 vertices\[4\];\s*\};",
+             r"\1", "Triangle union")
+    return t
+
+
+def main():
+    fmad = "false"
+    if "--fmad" in sys.argv:
+        fmad = sys.argv[sys.argv.index("--fmad") + 1]
+    keep = "--keep" in sys.argv
+    if not os.path.isdir(os.path.join(REF, "src")):
+        print(f"build_ref: {REF}/src not present (GPU box?) — using the prebuilt oracle/_ref if any")
+        return 0
+    os.makedirs(OUT_DIR, exist_ok=True)
+    tmp = tempfile.mkdtemp(prefix="refcuda_")
+    try:
+        for h in HEADERS:
+            shutil.copy(os.path.join(REF, "src", h), os.path.join(tmp, h))
+        for name, fn in (("linearMath.h", patch_linear_math), ("geometry.h", patch_geometry_h)):
+            p = os.path.join(tmp, name)
+            open(p, "w").write(fn(open(p, encoding="utf-8", errors="replace").read()))
+        out = os.path.join(OUT_DIR, "librefcuda.so" if fmad == "false" else "librefcuda_fmad.so")
+        cmd = ["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100,code=sm_100", "-O3", "-lineinfo", f"--fmad={fmad}", "-std=c++17",
+               "-Xcompiler", "-fPIC", "-Xcompiler", "-w", "-w", "-shared", "-I", tmp, os.path.join(HERE, "harness.cu"), "-o", out, "-lcudart"]
+        print(" ".join(cmd), flush=True)
+        subprocess.check_call(cmd)
+        print("built", out)
+    finally:
+        if keep:
+            print("scratch kept at", tmp)
+        else:
+            shutil.rmtree(tmp, ignore_errors=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

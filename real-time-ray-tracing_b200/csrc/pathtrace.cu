@@ -131,14 +131,48 @@ VD void glossy_interaction(RayState& r, float rnd) {
     }
 }
 
-VD Float3 pow3f(Float3 v, float a) { return Float3{powf(v.x, a), powf(v.y, a), powf(v.z, a)}; }
+// powf is ~150 SASS instructions inlined; one out-of-line copy keeps the megakernel inside the instruction cache.
+__device__ __noinline__ float pow_ool(float v, float a) { return powf(v, a); }
+VD Float3 pow3f(Float3 v, float a) { return Float3{pow_ool(v.x, a), pow_ool(v.y, a), pow_ool(v.z, a)}; }
+
+// SampleBicubicSmoothStepLod (src/sampler.cuh:565-584) with the two mip levels as a rolled loop (code size)
+VD Float4 sample_tex_lod_rolled(const MipTex* texs, int t, Float2 uv, float lod) {
+    const float low = floorf(lod);
+    const float f = lod - low;
+    int lo = __float2int_rz(low);                 // cvt.rzi.s32.f32: saturating, NaN -> 0
+    int hi = (lo == 0x7fffffff) ? lo : lo + 1;
+    const int maxLod = texs[t].maxLod;
+    lo = clampi(lo, 0, maxLod); hi = clampi(hi, 0, maxLod);
+    Float4 acc{0, 0, 0, 0};
+#pragma unroll 1
+    for (int k = 0; k < 2; ++k) {
+        const int lv = k ? hi : lo;
+        const int w = texs[t].w[lv], h = texs[t].h[lv];
+        const ushort4* __restrict__ img = texs[t].mip[lv];
+        const BicubicTaps tp = bicubic_taps(uv, w, h);
+        Float4 out{0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int x = tp.x0 + (i & 1), y = tp.y0 + (i >> 1);
+            boundary_repeat(x, y, w, h);
+            out = out + load_ushort4(img, w, h, x, y) * tp.w[i];
+        }
+        out = out / tp.sum;
+        acc = k ? (acc + out * f) : (out * (1.0f - f));       // a * (1 - f) + b * f
+    }
+    return acc;
+}
 
 // one triplanar projection of src/surfaceInteraction.cuh:96-155
 VD void triplanar_axis(const PathTraceParams& P, Float2 uv, float lod, Float3 normal, Float3 w, Float3& albedo, Float3& nrm) {
     uv = uv * 0.5f;
-    const Float4 c = sample_tex_lod(P.tex[0], uv, lod);
+    Float4 c{0, 0, 0, 0}, c2{0, 0, 0, 0};
+#pragma unroll 1
+    for (int t = 0; t < 2; ++t) {
+        const Float4 v = sample_tex_lod_rolled(P.tex, t, uv, lod);
+        if (t == 0) c = v; else c2 = v;
+    }
     albedo = pow3f(xyz(c), 2.2f);
-    const Float4 c2 = sample_tex_lod(P.tex[1], uv, lod);
     const Float3 n = xyz(c2) - 0.5f;
     const Float3 u = cross(normal, w);
     const Float3 v = cross(normal, u);
@@ -157,13 +191,21 @@ VD void diffuse_interaction(int bounce, const PathTraceParams& P, RayState& r, F
     {
         const float tw = (float)P.tex[0].w[0], th = (float)P.tex[0].h[0];
         const float lod = log2f(r.rayConeWidth * 0.5f * sqrtf(tw * tw + th * th));
-        Float3 aX, aY, aZ, nX, nY, nZ;
-        triplanar_axis(P, Float2{r.pos.y, r.pos.z}, lod, normal, fabsf(normal.y) > 0.999f ? f3(0, 0, 1) : f3(0, 1, 0), aX, nX);
-        triplanar_axis(P, Float2{r.pos.x, r.pos.z}, lod, normal, fabsf(normal.x) > 0.999f ? f3(0, 0, 1) : f3(1, 0, 0), aY, nY);
-        triplanar_axis(P, Float2{r.pos.x, r.pos.y}, lod, normal, fabsf(normal.y) > 0.999f ? f3(1, 0, 0) : f3(0, 1, 0), aZ, nZ);
         const float wx = surfaceNormal.x * surfaceNormal.x, wy = surfaceNormal.y * surfaceNormal.y, wz = surfaceNormal.z * surfaceNormal.z;
-        albedo = aX * wx + aY * wy + aZ * wz;
-        normal = normalize(nX * wx + nY * wy + nZ * wz);
+        const Float3 shadingN = normal;
+        Float3 aSum = f3(0.0f), nSum = f3(0.0f);
+#pragma unroll 1
+        for (int ax = 0; ax < 3; ++ax) {                       // X, Y, Z projections; sums keep the reference's left-to-right order
+            const Float2 uv = ax == 0 ? Float2{r.pos.y, r.pos.z} : (ax == 1 ? Float2{r.pos.x, r.pos.z} : Float2{r.pos.x, r.pos.y});
+            const Float3 w = ax == 1 ? (fabsf(shadingN.x) > 0.999f ? f3(0, 0, 1) : f3(1, 0, 0))
+                                     : (fabsf(shadingN.y) > 0.999f ? (ax == 0 ? f3(0, 0, 1) : f3(1, 0, 0)) : f3(0, 1, 0));
+            const float wt = ax == 0 ? wx : (ax == 1 ? wy : wz);
+            Float3 a, n;
+            triplanar_axis(P, uv, lod, shadingN, w, a, n);
+            if (ax == 0) { aSum = a * wt; nSum = n * wt; } else { aSum = aSum + a * wt; nSum = nSum + n * wt; }
+        }
+        albedo = aSum;
+        normal = normalize(nSum);
         r.fakeNormal = normal;
     }
     if (bounce == 0) r.albedo = albedo * (1.0f + fabsf(dot(normal, r.centerRaydir)));
@@ -239,25 +281,34 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
         }
         Float2 sampleUv;
         generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd[0].x, rnd[0].y}, Float2{rnd[0].z, rnd[0].w});
-        ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
-        float outDepth = r.depth;
-        const unsigned short mask = (unsigned short)r.matId;
-        Float2 motion{0.0f, 0.0f};
-        if (r.hit) {                                                            // HistoryCamera::WorldToScreenSpace src/kernel.cuh:144-151
-            const Float3 v = mul(P.historyCamera.invCamMat, r.pos - P.historyCamera.pos);
-            const Float2 ndc = (Float2{v.x, v.y} / v.z) / P.camera.tanHalfFov;
-            motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
+        // The reference unrolls five RaySceneIntersect calls (src/pathtrace.cuh:67-105).  Here they are ONE loop body so the
+        // traversal and the diffuse interaction exist once in the instruction stream: the unrolled form is ~36 k SASS
+        // instructions (580 KB) and spent 62 % of its issue slots waiting on instruction fetch (profiles/r1b).
+        float outDepth = 0.0f; unsigned short mask = 0; Float2 motion{0.0f, 0.0f}; Float3 outNormal = f3(0.0f);
+#pragma unroll 1
+        for (int seg = 0; seg < 5; ++seg) {
+            ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
+            if (seg == 0) {
+                outDepth = r.depth;
+                mask = (unsigned short)r.matId;
+                if (r.hit) {                                                        // HistoryCamera::WorldToScreenSpace src/kernel.cuh:144-151
+                    const Float3 v = mul(P.historyCamera.invCamMat, r.pos - P.historyCamera.pos);
+                    const Float2 ndc = (Float2{v.x, v.y} / v.z) / P.camera.tanHalfFov;
+                    motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
+                }
+                motion = motion + 0.5f;
+            }
+            if (seg < 4) {
+                const float g = seg == 0 ? rnd[0].x : (seg == 1 ? rnd[0].y : (seg == 2 ? rnd[0].z : rnd[0].w));
+                glossy_interaction(r, g);
+            }
+            if (seg == 2 || seg == 3) {
+                const bool first = seg == 2;
+                Float3 beta = first ? r.beta1 : r.beta0;
+                diffuse_interaction(first ? 0 : 1, P, r, beta, first ? rnd[0] : rnd[2], first ? rnd[1] : rnd[3]);
+                if (first) { r.beta1 = beta; outNormal = r.fakeNormal; } else r.beta0 = beta;
+            }
         }
-        motion = motion + 0.5f;
-        glossy_interaction(r, rnd[0].x); ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
-        glossy_interaction(r, rnd[0].y); ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
-        glossy_interaction(r, rnd[0].z);
-        diffuse_interaction(0, P, r, r.beta1, rnd[0], rnd[1]);
-        Float3 outNormal = r.fakeNormal;
-        ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
-        glossy_interaction(r, rnd[0].w);
-        diffuse_interaction(1, P, r, r.beta0, rnd[2], rnd[3]);
-        ray_scene_intersect<COUNT>(P, sceneBox, r, stL, stT, rays, nodeVisits, leafTests);
         Float3 L0 = f3(0.0f);                                                   // GetLightSource src/light.cuh:275-305
         if (r.hitLight && !r.isOccluded && r.matType == MAT_SKY) L0 = env_light(P.env, r.dir);
         Float3 L2 = (L0 * r.beta0) * r.beta1;

@@ -1,0 +1,39 @@
+#!/usr/bin/env python
+"""Quick per-stage timing on the bench scene (not the bench contract): CUDA events, L2 flushed, median of N."""
+import importlib, os, sys, json
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+import torch
+pkg = importlib.import_module("real-time-ray-tracing_b200")
+W, H = (int(os.environ.get("W", 1920)), int(os.environ.get("H", 1080)))
+scene = os.environ.get("SCENE", "C2ref")
+N = int(os.environ.get("N", 10))
+gx, gz = pkg.scenes.TERRAIN_SIZES[scene]
+pos, nrm, idx = pkg.scenes.terrain(gx, gz, seed=1, order=os.environ.get("ORDER", "morton"))
+cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, W, H)
+rays = pkg.scenes.primary_rays(cam, W, H)
+rt = pkg.RayTracer(W, H).init(); rt.set_mesh(pos, idx, nrm); rt.set_camera(cam, reset_history=True)
+for k, v in [a.split("=") for a in sys.argv[1:]]:
+    rt.set_option(k, int(v))
+stream = torch.cuda.ExternalStream(rt.stream)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+d_rays = torch.from_numpy(rays.view(np.uint8).reshape(-1)).cuda(); d_hits = torch.empty(rays.shape[0] * 16, dtype=torch.uint8, device="cuda")
+def timeit(fn, n=N):
+    ts = []
+    for i in range(n + 2):
+        with torch.cuda.stream(stream): flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); fn(i); b.record(stream); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts[2:]))
+out = {"scene": scene, "tris": int(idx.shape[0]), "W": W, "H": H}
+out["build_ms"] = timeit(lambda i: rt.build_bvh())
+out["traverse_primary_ms"] = timeit(lambda i: rt.traverse_device(d_rays.data_ptr(), rays.shape[0], d_hits.data_ptr()))
+def pt(i): rt.set_frame_number(2 + i); rt.pathtrace()
+out["pathtrace_ms"] = timeit(pt)
+out["rays"] = rt.timings()["rays_traced"]
+def dn(i): rt.set_frame_number(2 + i); rt.denoise()
+out["denoise_ms"] = timeit(dn)
+out["pathtrace_mrays_s"] = out["rays"] / out["pathtrace_ms"] / 1e3
+out["primary_mrays_s"] = rays.shape[0] / out["traverse_primary_ms"] / 1e3
+print(json.dumps(out))
