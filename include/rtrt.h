@@ -157,6 +157,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
  *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
  *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)
+ *   "wavefront"           1/0  : path-trace driver: wavefront ray queues with persistent traversal (default) or one megakernel
  *   "count_visits"        0/1  : rtrt_pathtrace also counts node visits / leaf tests (rtrt_timings)         */
 
 /* ---- stage 1: RayTracer::BuildBvhLevel1 + BuildBvhLevel2 (src/bvh.cu:7-97) ---- */

@@ -241,6 +241,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!name) return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: null name");
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 32) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..32"); c.stackSize = (int)value; return RTRT_OK; }
+    if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }
     return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: unknown option");

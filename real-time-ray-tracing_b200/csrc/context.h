@@ -37,6 +37,8 @@ struct Context {
     int stackSize = 16;      // src/traverse.h:28
     int maxLoop = 1024;      // src/traverse.h:132
     bool countVisits = false;
+    bool wavefront = true;                 // path-trace driver: wavefront queues (default) or the single megakernel
+    void* dWf = nullptr; size_t wfBytes = 0;   // wavefront path state + queues (pathtrace_wf.cu)
 
     // ---- frame state: ConstBuffer (src/kernel.cuh:211-231) + Buffer2DManager (src/init.cu:441-584) ----
     int width = 0, height = 0;               // render size

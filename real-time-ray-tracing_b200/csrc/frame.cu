@@ -222,6 +222,7 @@ void free_frame_resources(Context& c) {
     dfree2(c.dMaterials); dfree2(c.dMaterialsIdx);
     for (int t = 0; t < 2; ++t) { if (c.dTexMem[t]) cudaFree(c.dTexMem[t]); c.dTexMem[t] = nullptr; }
     dfree2(c.dRayCounter);
+    if (c.dWf) { cudaFree(c.dWf); c.dWf = nullptr; c.wfBytes = 0; }
 }
 
 // Texture slot upload + mip chain (2x2 box in float, truncating store: MipmapGen src/mipgen.cu:121-139; init-time work)

@@ -1,0 +1,340 @@
+// Stage 2, wavefront driver (default): the reference's PathTrace megakernel (src/pathtrace.cuh:11-128) re-cut for a
+// GPU without RT cores.  Every path runs the SAME per-pixel sequence of operations as the megakernel (same blue-noise
+// samples, same guards, same five segments), but the work is split where the rays are:
+//
+//   k_pt_primary   one thread per pixel: sampler, thin-lens ray, primary TraverseBvh (coherent), then the path logic
+//                  up to the point where the next ray is needed; that ray + 80 B of path state go to HBM and the
+//                  pixel id is appended (warp-aggregated) to the round-0 queue.  Sky pixels finish here.
+//   k_pt_trace     persistent CTAs; each lane pulls a queued ray, traverses it with the shared trav_step(), writes
+//                  (t, tri, u, v) and immediately REFILLS from the queue when enough lanes of its warp have gone idle,
+//                  so the wildly varying lengths of incoherent bounce rays do not leave lanes empty.
+//   k_pt_logic     compacted: one thread per queued path applies the hit (normal, material, ray cone), runs the
+//                  glossy / diffuse interactions of its segment(s) and either queues the next ray or writes the pixel.
+//   (trace, logic) x 4 rounds = at most 5 rays per path like the reference; empty rounds cost one idle launch.
+//
+// Path state in HBM (per pixel, SoA float4): orig|coneWidth, dir|coneSpread, beta0|albedo.x, beta1|albedo.y,
+// albedo.z|lightIdx|flags|mask+seg  and the hit record t|ua|va|tri = 96 B/px, touched only for live paths.
+#include "pathtrace_common.cuh"
+
+namespace rtrt {
+
+constexpr int kTraceThreads = 128;
+constexpr int kLogicThreads = 128;
+constexpr int kRefillIdle = 8;        // refill a warp once this many of its lanes are idle
+
+struct WfBuffers {
+    float4* st0; float4* st1; float4* st2; float4* st3; float4* st4; float4* hit;
+    uint32_t* queue[2];
+    uint32_t* counters;      // [r] = entries in the queue consumed by round r (r = 0..3), [8 + r] = fetch cursor of k_pt_trace
+};
+
+enum : uint32_t { F_HITLIGHT = 1u, F_PROCESSED = 2u, F_OCCLUDED = 4u, F_SHADOW = 8u, F_DIFFUSE = 16u, F_HIT = 32u };
+
+VD void save_state(const WfBuffers& B, uint32_t pix, const RayState& r, int seg, unsigned short mask) {
+    B.st0[pix] = make_float4(r.orig.x, r.orig.y, r.orig.z, r.rayConeWidth);
+    B.st1[pix] = make_float4(r.dir.x, r.dir.y, r.dir.z, r.rayConeSpread);
+    B.st2[pix] = make_float4(r.beta0.x, r.beta0.y, r.beta0.z, r.albedo.x);
+    B.st3[pix] = make_float4(r.beta1.x, r.beta1.y, r.beta1.z, r.albedo.y);
+    const uint32_t flags = (r.hitLight ? F_HITLIGHT : 0u) | (r.isHitProcessed ? F_PROCESSED : 0u) | (r.isOccluded ? F_OCCLUDED : 0u) |
+                           (r.isShadowRay ? F_SHADOW : 0u) | (r.isDiffuse ? F_DIFFUSE : 0u) | (r.hit ? F_HIT : 0u) |
+                           ((uint32_t)r.matType << 8);
+    B.st4[pix] = make_float4(r.albedo.z, __int_as_float(r.lightIdx), __uint_as_float(flags), __uint_as_float((uint32_t)mask | ((uint32_t)seg << 16)));
+}
+
+VD void load_state(const WfBuffers& B, uint32_t pix, RayState& r, int& seg, unsigned short& mask) {
+    const float4 a = B.st0[pix], b = B.st1[pix], c = B.st2[pix], d = B.st3[pix], e = B.st4[pix];
+    r.orig = Float3{a.x, a.y, a.z}; r.rayConeWidth = a.w;
+    r.dir = Float3{b.x, b.y, b.z}; r.rayConeSpread = b.w;
+    r.beta0 = Float3{c.x, c.y, c.z}; r.beta1 = Float3{d.x, d.y, d.z};
+    r.albedo = Float3{c.w, d.w, e.x};
+    r.lightIdx = __float_as_int(e.y);
+    const uint32_t flags = __float_as_uint(e.z), ms = __float_as_uint(e.w);
+    r.hitLight = flags & F_HITLIGHT; r.isHitProcessed = flags & F_PROCESSED; r.isOccluded = flags & F_OCCLUDED;
+    r.isShadowRay = flags & F_SHADOW; r.isDiffuse = flags & F_DIFFUSE; r.hit = flags & F_HIT;
+    r.matType = (int)((flags >> 8) & 0xFFu);
+    mask = (unsigned short)(ms & 0xFFFFu); seg = (int)(ms >> 16);
+    r.matId = 0; r.objectIdx = -1; r.normal = f3(0, -1, 0); r.fakeNormal = f3(0.0f); r.pos = f3(0.0f);
+    r.depth = 0.0f; r.offset = 0.0f; r.normalDotRayDir = 0.0f; r.isRayIntoSurface = false;
+}
+
+VD Float4 blue_rand4(const PathTraceParams& P, int ix, int iy, int k) {                  // src/pathtrace.cuh:53-62
+    const int si = P.frameNum * 4 + k;
+    return Float4{blue_rand(P.bn, ix, iy, si, 0), blue_rand(P.bn, ix, iy, si, 1), blue_rand(P.bn, ix, iy, si, 2), blue_rand(P.bn, ix, iy, si, 3)};
+}
+
+VD Float3 center_ray_dir(const Camera& cam, int ix, int iy) {                            // the centre ray of GenerateRay (src/raygen.cuh:7-38)
+    Float2 uvc = (Float2{(float)ix, (float)iy} + 0.5f) * cam.inversedResolution;
+    uvc = uvc * -2.0f + 1.0f;
+    return normalize(cam.adjustedFront + cam.adjustedLeft * uvc.x + cam.adjustedUp * uvc.y);
+}
+
+// The interactions that follow RaySceneIntersect number `seg` (src/pathtrace.cuh:84-105), then advance through the
+// segments whose intersect is a guarded no-op.  Returns true when the path needs its next ray traced (state to be saved
+// with the returned seg), false when the path is complete (seg == 5).
+VD bool advance_path(const PathTraceParams& P, RayState& r, int& seg, int ix, int iy, ushort4* normalOut) {
+    while (true) {
+        if (seg < 4) {
+            const bool glossyActs = !(r.hitLight || r.isDiffuse || r.isOccluded);
+            float g = 0.0f;
+            if (glossyActs) g = blue_rand(P.bn, ix, iy, P.frameNum * 4, seg);             // rnd[0].{x,y,z,w} for seg 0..3
+            glossy_interaction(r, g);
+        }
+        if (seg == 2 || seg == 3) {
+            const bool first = seg == 2;
+            if (!(r.hitLight || !r.isDiffuse || r.isOccluded)) {
+                if (first) r.centerRaydir = center_ray_dir(P.camera, ix, iy);
+                Float3 beta = first ? r.beta1 : r.beta0;
+                const Float4 ra = blue_rand4(P, ix, iy, first ? 0 : 2), rb = blue_rand4(P, ix, iy, first ? 1 : 3);
+                diffuse_interaction(first ? 0 : 1, P, r, beta, ra, rb);
+                if (first) r.beta1 = beta; else r.beta0 = beta;
+            }
+            if (first) {
+                Float3 n = r.fakeNormal;
+                if (isnan3(n)) n = f3(0.0f);
+                normalOut[(size_t)iy * P.width + ix] = make_ushort4(f2h_bits(n.x), f2h_bits(n.y), f2h_bits(n.z), f2h_bits(0.0f));
+            }
+        }
+        ++seg;
+        if (seg >= 5) return false;
+        if (needs_ray(r)) return true;
+    }
+}
+
+VD void finalize_path(const PathTraceParams& P, const RayState& r, unsigned short mask, int ix, int iy) {
+    Float3 L0 = f3(0.0f);                                                               // GetLightSource src/light.cuh:275-305
+    if (r.hitLight && !r.isOccluded && r.matType == MAT_SKY) L0 = env_light(P.env, r.dir);
+    Float3 L2 = (L0 * r.beta0) * r.beta1;
+    if (isnan3(L2)) L2 = f3(0.0f);                                                      // NAN_DETECTER src/pathtrace.cuh:113-117
+    L2 = Float3{clampf(L2.x, 0.0f, 10.0f), clampf(L2.y, 0.0f, 10.0f), clampf(L2.z, 0.0f, 10.0f)};
+    L2 = L2 / r.albedo;
+    const size_t i = (size_t)iy * P.width + ix;
+    P.color[i] = make_ushort4(f2h_bits(L2.x), f2h_bits(L2.y), f2h_bits(L2.z), mask);
+    P.albedo[i] = make_ushort4(f2h_bits(r.albedo.x), f2h_bits(r.albedo.y), f2h_bits(r.albedo.z), f2h_bits(0.0f));
+}
+
+// warp-aggregated append of this lane's pixel to a queue; must be reached by every lane of the warp
+VD void queue_append(bool emit, uint32_t pix, uint32_t* queue, uint32_t* counter, int lane) {
+    const unsigned m = __ballot_sync(0xffffffffu, emit);
+    if (m == 0u) return;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (emit) queue[base + __popc(m & ((1u << lane) - 1u))] = pix;
+}
+
+VD AABB scene_box(const SceneView& sc) {                     // merged box of TLAS node 0 (src/traverse.h:127-129)
+    const float4 a = __ldg(sc.tlasRows), b = __ldg(sc.tlasRows + 1), c = __ldg(sc.tlasRows + 2);
+    AABB box;
+    box.max = Float3{sel_max(a.x, c.x), sel_max(a.y, c.y), sel_max(a.z, c.z)};
+    box.min = Float3{sel_min(b.x, a.w), sel_min(b.y, b.w), sel_min(b.z, c.w)};
+    return box;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// k_pt_primary: per pixel — sampler, camera ray, primary traversal, segment-0 outputs, path logic up to the next ray.
+// ---------------------------------------------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams P, const WfBuffers B) {
+    __shared__ uint32_t sLink[16 * kPtThreads];
+    __shared__ float sT[16 * kPtThreads];
+    const int tid = threadIdx.y * kPtBlockX + threadIdx.x, lane = tid & 31;
+    const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
+    const int iy = P.rowBegin + blockIdx.y * kPtBlockY + threadIdx.y;
+    bool emit = false;
+    uint32_t nodeVisits = 0, leafTests = 0;
+    if (ix < P.width && iy < P.rowEnd) {
+        const AABB sceneBox = scene_box(P.sc);
+        RayState r;
+        r.beta0 = f3(1.0f); r.beta1 = f3(1.0f);
+        r.hitLight = false; r.lightIdx = kDefaultLightId; r.isHitProcessed = false; r.isOccluded = false; r.isShadowRay = false;
+        r.isDiffuse = false; r.hit = false; r.matId = 0; r.matType = 0; r.objectIdx = -1;
+        r.normal = f3(0, -1, 0); r.fakeNormal = f3(0.0f); r.albedo = f3(1.0f); r.pos = f3(0.0f);
+        r.rayConeWidth = 0.0f; r.depth = 0.0f; r.offset = 0.0f; r.normalDotRayDir = 0.0f; r.isRayIntoSurface = false;
+        r.rayConeSpread = ray_cone_width(P.camera, ix, iy);
+        const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
+        Float2 sampleUv;
+        generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
+        {
+            const RayPrep rp = prepare_ray(r.orig, r.dir, sceneBox);
+            const TraverseResult h = traverse_bvh<16, COUNT>(P.sc, rp, 0, sLink + tid, sT + tid, kPtThreads);
+            if (COUNT) { nodeVisits = h.nodeVisits; leafTests = h.leafTests; }
+            apply_hit(P, r, h.t, h.tri, h.ua, h.va);
+        }
+        float outDepth = r.depth;
+        const unsigned short mask = (unsigned short)r.matId;
+        Float2 motion{0.0f, 0.0f};
+        if (r.hit) {                                                            // HistoryCamera::WorldToScreenSpace src/kernel.cuh:144-151
+            const Float3 v = mul(P.historyCamera.invCamMat, r.pos - P.historyCamera.pos);
+            const Float2 ndc = (Float2{v.x, v.y} / v.z) / P.camera.tanHalfFov;
+            motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
+        }
+        motion = motion + 0.5f;
+        if (outDepth != outDepth) outDepth = 0.0f;                              // NAN_DETECTER src/pathtrace.cuh:113-117
+        if (motion.x != motion.x || motion.y != motion.y) motion = Float2{0.0f, 0.0f};
+        const size_t i = (size_t)iy * P.width + ix;
+        P.depth[i] = __float2half_rn(outDepth);
+        P.motion[i] = __float22half2_rn(make_float2(motion.x, motion.y));
+        int seg = 0;
+        emit = advance_path(P, r, seg, ix, iy, P.normal);
+        if (emit) { r.isHitProcessed = false; save_state(B, (uint32_t)i, r, seg, mask); }
+        else finalize_path(P, r, mask, ix, iy);
+    }
+    queue_append(emit, (uint32_t)((size_t)iy * P.width + ix), B.queue[0], B.counters + 0, lane);
+    if (COUNT && P.rayCounter) {
+        for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
+        if (lane == 0) { atomicAdd(P.rayCounter + 1, (unsigned long long)nodeVisits); atomicAdd(P.rayCounter + 2, (unsigned long long)leafTests); }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// k_pt_trace: persistent wavefront traversal with lane refill.  Queue entries are pixel ids; rays come from st0/st1.
+// ---------------------------------------------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, const WfBuffers B, const uint32_t* __restrict__ queue,
+                                                            const uint32_t* __restrict__ countPtr, uint32_t* fetchPtr, unsigned long long* visitCounters) {
+    __shared__ uint32_t sLink[16 * kTraceThreads];
+    __shared__ float sT[16 * kTraceThreads];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t n = *countPtr;
+    if (n == 0u) return;
+    const AABB sceneBox = scene_box(sc);
+    const int cap = sc.stackSize < 16 ? sc.stackSize : 16;
+    const uint32_t numTri = sc.numBatches * kBatchSize;
+    const int maxLoop = sc.maxLoop;
+    uint32_t* stL = sLink + tid; float* stT = sT + tid;
+    bool active = false, exhausted = false;
+    uint32_t pix = 0;
+    RayPrep rp; TravState s;
+    uint32_t nodeVisits = 0, leafTests = 0;
+    trav_init(s);
+    rp = prepare_ray(Float3{0, 0, 0}, Float3{0, 1, 0}, sceneBox);
+    while (true) {
+        // ---- refill idle lanes from the queue ----
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (!exhausted && idle != 0u) {
+            const int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(fetchPtr, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active) {
+                const uint32_t q = base + __popc(idle & ((1u << lane) - 1u));
+                if (q < n) {
+                    pix = __ldg(queue + q);
+                    const float4 o = B.st0[pix], d = B.st1[pix];
+                    rp = prepare_ray(Float3{o.x, o.y, o.z}, Float3{d.x, d.y, d.z}, sceneBox);
+                    trav_init(s);
+                    active = true;
+                }
+            }
+            exhausted = base + (uint32_t)__popc(idle) >= n;
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+        // ---- traverse until enough lanes have finished to make a refill worthwhile ----
+        while (true) {
+            if (active) {
+                bool done = trav_step<COUNT>(sc, rp, s, 0, cap, numTri, stL, stT, kTraceThreads);
+                ++s.it;
+                if (done || s.it >= maxLoop) {
+                    B.hit[pix] = make_float4(s.t, s.ua, s.va, __int_as_float(s.tri));
+                    if (COUNT) { nodeVisits += s.nodeVisits; leafTests += s.leafTests; }
+                    active = false;
+                }
+            }
+            const unsigned live = __ballot_sync(0xffffffffu, active);
+            if (live == 0u) break;
+            if (!exhausted && 32 - __popc(live) >= kRefillIdle) break;
+        }
+    }
+    if (COUNT && visitCounters) {
+        for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
+        if (lane == 0) { atomicAdd(visitCounters + 1, (unsigned long long)nodeVisits); atomicAdd(visitCounters + 2, (unsigned long long)leafTests); }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// k_pt_logic: one thread per queued path (grid-stride over the device-side count): apply the hit of the ray just
+// traced, run the interactions of the segment(s), queue the next ray or write the pixel.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParams P, const WfBuffers B, const uint32_t* __restrict__ queueIn,
+                                                            const uint32_t* __restrict__ countIn, uint32_t* queueOut, uint32_t* countOut) {
+    const uint32_t n = *countIn;
+    const int lane = threadIdx.x & 31;
+    const uint32_t stride = gridDim.x * kLogicThreads;
+    // every lane of a warp runs the same number of iterations so that queue_append stays warp-converged
+    for (uint32_t q0 = blockIdx.x * kLogicThreads + (threadIdx.x & ~31u); q0 < n; q0 += stride) {
+        const uint32_t q = q0 + lane;
+        bool emit = false;
+        uint32_t pix = 0;
+        if (q < n) {
+            pix = __ldg(queueIn + q);
+            const int iy = (int)(pix / (uint32_t)P.width), ix = (int)(pix - (uint32_t)iy * (uint32_t)P.width);
+            RayState r; int seg; unsigned short mask;
+            load_state(B, pix, r, seg, mask);
+            const float4 h = B.hit[pix];
+            apply_hit(P, r, h.x, __float_as_int(h.w), h.y, h.z);
+            emit = advance_path(P, r, seg, ix, iy, P.normal);
+            if (emit) { r.isHitProcessed = false; save_state(B, pix, r, seg, mask); }
+            else finalize_path(P, r, mask, ix, iy);
+        }
+        queue_append(emit, pix, queueOut, countOut, lane);
+    }
+}
+
+// rays traced = pixels + every queued ray (src/traverse.cuh:64-72: one TraverseBvh per passed guard)
+__global__ void k_pt_count_rays(const uint32_t* __restrict__ counters, unsigned long long pixels, unsigned long long* out) {
+    out[0] = pixels + counters[0] + counters[1] + counters[2] + counters[3];
+}
+
+SceneView make_scene_view(const Context& c);   // traverse.cu
+
+static int ensure_wf_buffers(Context& c, WfBuffers& B) {
+    const size_t px = (size_t)c.width * c.height;
+    const size_t need = px * (6 * sizeof(float4) + 2 * sizeof(uint32_t)) + 256;
+    if (c.wfBytes < need) {
+        if (c.dWf) cudaFree(c.dWf);
+        c.dWf = nullptr; c.wfBytes = 0;
+        RTRT_CUDA(c, cudaMalloc(&c.dWf, need));
+        c.wfBytes = need;
+    }
+    char* p = reinterpret_cast<char*>(c.dWf);
+    B.counters = reinterpret_cast<uint32_t*>(p); p += 256;
+    float4** f4[6] = {&B.st0, &B.st1, &B.st2, &B.st3, &B.st4, &B.hit};
+    for (auto f : f4) { *f = reinterpret_cast<float4*>(p); p += px * sizeof(float4); }
+    B.queue[0] = reinterpret_cast<uint32_t*>(p); p += px * sizeof(uint32_t);
+    B.queue[1] = reinterpret_cast<uint32_t*>(p);
+    return RTRT_OK;
+}
+
+void fill_pathtrace_params(Context& c, PathTraceParams& P);   // pathtrace.cu
+
+int launch_pathtrace_wavefront(Context& c) {
+    PathTraceParams P{};
+    fill_pathtrace_params(c, P);
+    WfBuffers B{};
+    int rc = ensure_wf_buffers(c, B);
+    if (rc) return rc;
+    static int smCount = 0;
+    if (!smCount) { cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c.device); if (smCount <= 0) smCount = 148; }
+    RTRT_CUDA(c, cudaMemsetAsync(B.counters, 0, 256, c.stream));
+    RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));
+    const int rows = c.rowEnd - c.rowBegin;
+    const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
+    if (c.countVisits) k_pt_primary<true><<<grid, block, 0, c.stream>>>(P, B);
+    else k_pt_primary<false><<<grid, block, 0, c.stream>>>(P, B);
+    c.launches += 1;
+    const int traceGrid = smCount * 8, logicGrid = smCount * 8;
+    for (int round = 0; round < 4; ++round) {
+        uint32_t* qin = B.queue[round & 1]; uint32_t* qout = B.queue[(round + 1) & 1];
+        if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, qin, B.counters + round, B.counters + 8 + round, c.dRayCounter);
+        else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, qin, B.counters + round, B.counters + 8 + round, nullptr);
+        k_pt_logic<<<logicGrid, kLogicThreads, 0, c.stream>>>(P, B, qin, B.counters + round, qout, B.counters + round + 1);
+        c.launches += 2;
+    }
+    k_pt_count_rays<<<1, 1, 0, c.stream>>>(B.counters, (unsigned long long)c.width * rows, c.dRayCounter);
+    c.launches += 1;
+    RTRT_CUDA(c, cudaGetLastError());
+    return RTRT_OK;
+}
+
+}  // namespace rtrt

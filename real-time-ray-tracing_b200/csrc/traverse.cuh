@@ -162,78 +162,97 @@ struct TraverseResult {
     uint32_t nodeVisits, leafTests;
 };
 
+// One ray's traversal state.  `step` advances it by exactly one iteration of the reference loop (src/traverse.h:132-250):
+// one inner-node visit, one TLAS-leaf -> BLAS-root transition, or one triangle test (+ the pop that follows a leaf or a
+// double miss).  The same step function drives the plain per-thread loop (traverse_bvh) and the persistent wavefront
+// kernel with lane refill (pathtrace.cu), so both produce the reference's per-ray sequence.
+struct TravState {
+    uint32_t cur; float curT; int top; int it;
+    float t; int tri; float u, v, ua, va;
+    uint32_t nodeVisits, leafTests;
+};
+
+__device__ __forceinline__ void trav_init(TravState& s) {
+    s.cur = 0u; s.curT = -FLT_MAX; s.top = -1; s.it = 0;         // TLAS node 0
+    s.t = kRayMax; s.tri = -1; s.u = 0.0f; s.v = 0.0f; s.ua = 0.0f; s.va = 0.0f;
+    s.nodeVisits = 0; s.leafTests = 0;
+}
+
+// returns true when the traversal is finished (stack empty, or any-hit satisfied)
+template <bool COUNT>
+__device__ __forceinline__ bool trav_step(const SceneView& sc, const RayPrep& r, TravState& s, int anyHit, int cap, uint32_t numTri,
+                                          uint32_t* stackLink, float* stackT, const int stride) {
+    bool pop = false;
+    const uint32_t cur = s.cur;
+    if (cur & kLinkLeaf) {
+        if (cur & kLinkBlas) {
+            const uint32_t loadIdx = cur & 0x3FFFFFFFu;          // blasOffset*1024 + idx
+            float4 q1 = make_float4(0, 0, 0, 0), q2 = q1, q3 = q1;
+            if (loadIdx < numTri) {                               // SAFE_LOAD (src/traverse.h:155)
+                const float4* row = sc.triRows + (size_t)loadIdx * 8;
+                q1 = __ldg(row); q2 = __ldg(row + 1); q3 = __ldg(row + 2);
+            }
+            if (COUNT) s.leafTests++;
+            float tt, uu, vv;
+            if (ray_triangle(r, q1, q2, q3, s.t, tt, uu, vv)) {
+                s.u = uu; s.v = vv;
+                if (tt < s.t) {
+                    s.t = tt; s.tri = (int)loadIdx; s.ua = uu; s.va = vv;
+                    if (anyHit) return true;
+                }
+            }
+            pop = true;
+        } else {
+            // TLAS leaf -> root of that BLAS (src/traverse.h:191-197)
+            const uint32_t b = cur & 0x3FFFFFFFu;
+            s.cur = kLinkBlas | (b << 10);
+        }
+    } else {
+        float4 n0 = make_float4(0, 0, 0, 0), n1 = n0, n2 = n0, n3 = n0;
+        const uint32_t idx = cur & 0x3FFFFFFFu;
+        if (cur & kLinkBlas) {
+            if (idx < numTri) { const float4* row = sc.nodeRows + (size_t)idx * 4; n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
+        } else {
+            if (idx < sc.numBatches) { const float4* row = sc.tlasRows + (size_t)idx * 4; n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
+        }
+        if (COUNT) s.nodeVisits++;
+        float t1, t2;
+        const bool i1 = ray_box(r, n1.x, n1.y, n1.z, n0.x, n0.y, n0.z, t1);           // left : min = row1.xyz, max = row0.xyz
+        const bool i2 = ray_box(r, n0.w, n1.w, n2.w, n2.x, n2.y, n2.z, t2);           // right: min = (row0.w,row1.w,row2.w), max = row2.xyz
+        const uint32_t up = (cur & kLinkBlas) ? (cur & (kLinkBlas | 0x3FFFFC00u)) : 0u;   // keep isBlas + blasOffset
+        const uint32_t L = up | __float_as_uint(n3.x) | (__float_as_uint(n3.z) ? kLinkLeaf : 0u);
+        const uint32_t R = up | __float_as_uint(n3.y) | (__float_as_uint(n3.w) ? kLinkLeaf : 0u);
+        if (!i1 && !i2) pop = true;
+        else if (i1 && !i2) { s.cur = L; s.curT = t1; }
+        else if (!i1 && i2) { s.cur = R; s.curT = t2; }
+        else {
+            uint32_t farL; float farT;
+            if (t1 < t2) { farL = R; farT = t2; s.cur = L; s.curT = t1; }
+            else         { farL = L; farT = t1; s.cur = R; s.curT = t2; }
+            if (s.top < cap - 1) { ++s.top; stackLink[s.top * stride] = farL; stackT[s.top * stride] = farT; }   // dropped when full (src/traverse.h:32-40)
+        }
+    }
+    if (pop) {                                                                         // TestForFinish (src/traverse.h:88-105)
+        do {
+            if (s.top < 0) return true;
+            s.cur = stackLink[s.top * stride]; s.curT = stackT[s.top * stride]; --s.top;
+        } while (s.curT > s.t);
+    }
+    return false;
+}
+
 template <int STACK, bool COUNT>
 __device__ __forceinline__ TraverseResult traverse_bvh(const SceneView& sc, const RayPrep& r, int anyHit,
                                                        uint32_t* stackLink, float* stackT, const int stride) {
-    TraverseResult res;
-    res.t = kRayMax; res.tri = -1; res.u = 0.0f; res.v = 0.0f; res.ua = 0.0f; res.va = 0.0f;
-    res.nodeVisits = 0; res.leafTests = 0;
-    int top = -1;
+    TravState s;
+    trav_init(s);
     const int cap = sc.stackSize < STACK ? sc.stackSize : STACK;
-    uint32_t cur = 0u;              // TLAS node 0
-    float curT = -FLT_MAX;
     const uint32_t numTri = sc.numBatches * kBatchSize;
-
-    for (int it = 0; it < sc.maxLoop; ++it) {
-        bool pop = false;
-        if (cur & kLinkLeaf) {
-            if (cur & kLinkBlas) {
-                const uint32_t loadIdx = cur & 0x3FFFFFFFu;          // blasOffset*1024 + idx
-                float4 q1 = make_float4(0, 0, 0, 0), q2 = q1, q3 = q1;
-                if (loadIdx < numTri) {                               // SAFE_LOAD (src/traverse.h:155)
-                    const float4* row = sc.triRows + (size_t)loadIdx * 8;
-                    q1 = __ldg(row); q2 = __ldg(row + 1); q3 = __ldg(row + 2);
-                }
-                if (COUNT) res.leafTests++;
-                float tt, uu, vv;
-                if (ray_triangle(r, q1, q2, q3, res.t, tt, uu, vv)) {
-                    res.u = uu; res.v = vv;
-                    if (tt < res.t) {
-                        res.t = tt; res.tri = (int)loadIdx; res.ua = uu; res.va = vv;
-                        if (anyHit) break;
-                    }
-                }
-                pop = true;
-            } else {
-                // TLAS leaf -> root of that BLAS (src/traverse.h:191-197)
-                const uint32_t b = cur & 0x3FFFFFFFu;
-                cur = kLinkBlas | (b << 10);
-            }
-        } else {
-            float4 n0 = make_float4(0, 0, 0, 0), n1 = n0, n2 = n0, n3 = n0;
-            const uint32_t idx = cur & 0x3FFFFFFFu;
-            if (cur & kLinkBlas) {
-                if (idx < numTri) { const float4* row = sc.nodeRows + (size_t)idx * 4; n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
-            } else {
-                if (idx < sc.numBatches) { const float4* row = sc.tlasRows + (size_t)idx * 4; n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
-            }
-            if (COUNT) res.nodeVisits++;
-            float t1, t2;
-            const bool i1 = ray_box(r, n1.x, n1.y, n1.z, n0.x, n0.y, n0.z, t1);           // left : min = row1.xyz, max = row0.xyz
-            const bool i2 = ray_box(r, n0.w, n1.w, n2.w, n2.x, n2.y, n2.z, t2);           // right: min = (row0.w,row1.w,row2.w), max = row2.xyz
-            const uint32_t up = cur & (kLinkBlas | 0x3FFFFC00u) & ((cur & kLinkBlas) ? 0xFFFFFFFFu : 0u);   // keep isBlas + blasOffset
-            const uint32_t L = up | __float_as_uint(n3.x) | (__float_as_uint(n3.z) ? kLinkLeaf : 0u);
-            const uint32_t R = up | __float_as_uint(n3.y) | (__float_as_uint(n3.w) ? kLinkLeaf : 0u);
-            if (!i1 && !i2) pop = true;
-            else if (i1 && !i2) { cur = L; curT = t1; }
-            else if (!i1 && i2) { cur = R; curT = t2; }
-            else {
-                uint32_t farL; float farT;
-                if (t1 < t2) { farL = R; farT = t2; cur = L; curT = t1; }
-                else         { farL = L; farT = t1; cur = R; curT = t2; }
-                if (top < cap - 1) { ++top; stackLink[top * stride] = farL; stackT[top * stride] = farT; }   // dropped when full (src/traverse.h:32-40)
-            }
-        }
-        if (pop) {                                                                         // TestForFinish
-            bool finished = false;
-            do {
-                if (top < 0) { finished = true; break; }
-                cur = stackLink[top * stride]; curT = stackT[top * stride]; --top;
-            } while (curT > res.t);
-            if (finished) break;
-        }
-    }
-    (void)curT;
+    for (; s.it < sc.maxLoop; ++s.it)
+        if (trav_step<COUNT>(sc, r, s, anyHit, cap, numTri, stackLink, stackT, stride)) break;
+    TraverseResult res;
+    res.t = s.t; res.tri = s.tri; res.u = s.u; res.v = s.v; res.ua = s.ua; res.va = s.va;
+    res.nodeVisits = s.nodeVisits; res.leafTests = s.leafTests;
     return res;
 }
 
