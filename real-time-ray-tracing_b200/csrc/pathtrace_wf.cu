@@ -2,12 +2,14 @@
 // GPU without RT cores.  Every path runs the SAME per-pixel sequence of operations as the megakernel (same blue-noise
 // samples, same guards, same five segments), but the work is split where the rays are:
 //
-//   k_pt_primary   one thread per pixel: sampler, thin-lens ray, primary TraverseBvh (coherent), then the path logic
-//                  up to the point where the next ray is needed; that ray + 80 B of path state go to HBM and the
-//                  pixel id is appended (warp-aggregated) to the round-0 queue.  Sky pixels finish here.
+//   k_pt_primary   one thread per pixel: sampler, thin-lens ray, primary TraverseBvh (coherent) -> hit record (16 B/px).
+//   k_pt_logic_first  one thread per pixel: segment-0 outputs (depth, motion, mask) and the path logic up to the point
+//                  where the next ray is needed; that ray + 80 B of path state go to HBM and the pixel id is appended
+//                  (warp-aggregated) to the ray queue.  Sky pixels finish here.
 //   k_pt_trace     persistent CTAs; each lane pulls a queued ray, traverses it with the shared trav_step(), writes
 //                  (t, tri, u, v) and immediately REFILLS from the queue when enough lanes of its warp have gone idle,
-//                  so the wildly varying lengths of incoherent bounce rays do not leave lanes empty.
+//                  so the wildly varying lengths of incoherent bounce rays do not leave lanes empty.  Finished rays
+//                  are binned into the shade queue: hits from the front, misses from the back.
 //   k_pt_logic     compacted: one thread per queued path applies the hit (normal, material, ray cone), runs the
 //                  glossy / diffuse interactions of its segment(s) and either queues the next ray or writes the pixel.
 //   (trace, logic) x 4 rounds = at most 5 rays per path like the reference; empty rounds cost one idle launch.
@@ -24,8 +26,11 @@ constexpr int kRefillIdle = 8;        // refill a warp once this many of its lan
 
 struct WfBuffers {
     float4* st0; float4* st1; float4* st2; float4* st3; float4* st4; float4* hit;
-    uint32_t* queue[2];
-    uint32_t* counters;      // [r] = entries in the queue consumed by round r (r = 0..3), [8 + r] = fetch cursor of k_pt_trace
+    uint32_t* rayQueue;      // pixel ids whose next ray is to be traced (written by logic, read by trace)
+    uint32_t* shadeQueue;    // the same ids after tracing, hits packed from the front, misses from the back (written by trace)
+    uint32_t capacity;       // entries per queue (= pixels)
+    uint32_t* counters;      // [r] rays queued for round r (0..3)   [8+r] fetch cursor of k_pt_trace
+                             // [16+r] hits of round r               [24+r] misses of round r
 };
 
 enum : uint32_t { F_HITLIGHT = 1u, F_PROCESSED = 2u, F_OCCLUDED = 4u, F_SHADOW = 8u, F_DIFFUSE = 16u, F_HIT = 32u };
@@ -132,8 +137,20 @@ VD AABB scene_box(const SceneView& sc) {                     // merged box of TL
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// k_pt_primary: per pixel — sampler, camera ray, primary traversal, segment-0 outputs, path logic up to the next ray.
+// k_pt_primary: per pixel — sampler, thin-lens camera ray, primary traversal -> hit record.  Nothing else: the kernel
+// stays at traversal-kernel register counts, and all shading happens compacted in k_pt_logic.
 // ---------------------------------------------------------------------------------------------------------------------
+VD void init_path(const PathTraceParams& P, RayState& r, Float2& sampleUv, int ix, int iy) {
+    r.beta0 = f3(1.0f); r.beta1 = f3(1.0f);
+    r.hitLight = false; r.lightIdx = kDefaultLightId; r.isHitProcessed = false; r.isOccluded = false; r.isShadowRay = false;
+    r.isDiffuse = false; r.hit = false; r.matId = 0; r.matType = 0; r.objectIdx = -1;
+    r.normal = f3(0, -1, 0); r.fakeNormal = f3(0.0f); r.albedo = f3(1.0f); r.pos = f3(0.0f);
+    r.rayConeWidth = 0.0f; r.depth = 0.0f; r.offset = 0.0f; r.normalDotRayDir = 0.0f; r.isRayIntoSurface = false;
+    r.rayConeSpread = ray_cone_width(P.camera, ix, iy);
+    const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
+    generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams P, const WfBuffers B) {
     __shared__ uint32_t sLink[16 * kPtThreads];
@@ -141,46 +158,17 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams
     const int tid = threadIdx.y * kPtBlockX + threadIdx.x, lane = tid & 31;
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
     const int iy = P.rowBegin + blockIdx.y * kPtBlockY + threadIdx.y;
-    bool emit = false;
     uint32_t nodeVisits = 0, leafTests = 0;
     if (ix < P.width && iy < P.rowEnd) {
         const AABB sceneBox = scene_box(P.sc);
-        RayState r;
-        r.beta0 = f3(1.0f); r.beta1 = f3(1.0f);
-        r.hitLight = false; r.lightIdx = kDefaultLightId; r.isHitProcessed = false; r.isOccluded = false; r.isShadowRay = false;
-        r.isDiffuse = false; r.hit = false; r.matId = 0; r.matType = 0; r.objectIdx = -1;
-        r.normal = f3(0, -1, 0); r.fakeNormal = f3(0.0f); r.albedo = f3(1.0f); r.pos = f3(0.0f);
-        r.rayConeWidth = 0.0f; r.depth = 0.0f; r.offset = 0.0f; r.normalDotRayDir = 0.0f; r.isRayIntoSurface = false;
-        r.rayConeSpread = ray_cone_width(P.camera, ix, iy);
         const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
-        Float2 sampleUv;
-        generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
-        {
-            const RayPrep rp = prepare_ray(r.orig, r.dir, sceneBox);
-            const TraverseResult h = traverse_bvh<16, COUNT>(P.sc, rp, 0, sLink + tid, sT + tid, kPtThreads);
-            if (COUNT) { nodeVisits = h.nodeVisits; leafTests = h.leafTests; }
-            apply_hit(P, r, h.t, h.tri, h.ua, h.va);
-        }
-        float outDepth = r.depth;
-        const unsigned short mask = (unsigned short)r.matId;
-        Float2 motion{0.0f, 0.0f};
-        if (r.hit) {                                                            // HistoryCamera::WorldToScreenSpace src/kernel.cuh:144-151
-            const Float3 v = mul(P.historyCamera.invCamMat, r.pos - P.historyCamera.pos);
-            const Float2 ndc = (Float2{v.x, v.y} / v.z) / P.camera.tanHalfFov;
-            motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
-        }
-        motion = motion + 0.5f;
-        if (outDepth != outDepth) outDepth = 0.0f;                              // NAN_DETECTER src/pathtrace.cuh:113-117
-        if (motion.x != motion.x || motion.y != motion.y) motion = Float2{0.0f, 0.0f};
-        const size_t i = (size_t)iy * P.width + ix;
-        P.depth[i] = __float2half_rn(outDepth);
-        P.motion[i] = __float22half2_rn(make_float2(motion.x, motion.y));
-        int seg = 0;
-        emit = advance_path(P, r, seg, ix, iy, P.normal);
-        if (emit) { r.isHitProcessed = false; save_state(B, (uint32_t)i, r, seg, mask); }
-        else finalize_path(P, r, mask, ix, iy);
+        Float3 orig, dir, centerDir; Float2 sampleUv;
+        generate_ray(orig, dir, centerDir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
+        const RayPrep rp = prepare_ray(orig, dir, sceneBox);
+        const TraverseResult h = traverse_bvh<16, COUNT>(P.sc, rp, 0, sLink + tid, sT + tid, kPtThreads);
+        if (COUNT) { nodeVisits = h.nodeVisits; leafTests = h.leafTests; }
+        B.hit[(size_t)iy * P.width + ix] = make_float4(h.t, h.ua, h.va, __int_as_float(h.tri));
     }
-    queue_append(emit, (uint32_t)((size_t)iy * P.width + ix), B.queue[0], B.counters + 0, lane);
     if (COUNT && P.rayCounter) {
         for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
         if (lane == 0) { atomicAdd(P.rayCounter + 1, (unsigned long long)nodeVisits); atomicAdd(P.rayCounter + 2, (unsigned long long)leafTests); }
@@ -191,8 +179,9 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams
 // k_pt_trace: persistent wavefront traversal with lane refill.  Queue entries are pixel ids; rays come from st0/st1.
 // ---------------------------------------------------------------------------------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, const WfBuffers B, const uint32_t* __restrict__ queue,
-                                                            const uint32_t* __restrict__ countPtr, uint32_t* fetchPtr, unsigned long long* visitCounters) {
+__global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, const WfBuffers B, const uint32_t* __restrict__ countPtr,
+                                                            uint32_t* fetchPtr, uint32_t* hitCount, uint32_t* missCount, unsigned long long* visitCounters) {
+    const uint32_t* __restrict__ queue = B.rayQueue;
     __shared__ uint32_t sLink[16 * kTraceThreads];
     __shared__ float sT[16 * kTraceThreads];
     const int tid = threadIdx.x, lane = tid & 31;
@@ -232,13 +221,25 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
         if (!__any_sync(0xffffffffu, active)) break;
         // ---- traverse until enough lanes have finished to make a refill worthwhile ----
         while (true) {
+            bool finishedNow = false;
             if (active) {
-                bool done = trav_step<COUNT>(sc, rp, s, 0, cap, numTri, stL, stT, kTraceThreads);
-                ++s.it;
-                if (done || s.it >= maxLoop) {
+                if (trav_step<COUNT>(sc, rp, s, 0, cap, numTri, maxLoop, stL, stT, kTraceThreads)) {
                     B.hit[pix] = make_float4(s.t, s.ua, s.va, __int_as_float(s.tri));
                     if (COUNT) { nodeVisits += s.nodeVisits; leafTests += s.leafTests; }
-                    active = false;
+                    active = false; finishedNow = true;
+                }
+            }
+            // shade queue: hits from the front, misses from the back, so that k_pt_logic warps are all-surface or all-sky
+            const unsigned fin = __ballot_sync(0xffffffffu, finishedNow);
+            if (fin) {
+                const unsigned mh = __ballot_sync(0xffffffffu, finishedNow && s.tri >= 0), mm = fin & ~mh;
+                uint32_t bh = 0, bm = 0;
+                if (mh) { const int l = __ffs(mh) - 1; if (lane == l) bh = atomicAdd(hitCount, (uint32_t)__popc(mh)); bh = __shfl_sync(0xffffffffu, bh, l); }
+                if (mm) { const int l = __ffs(mm) - 1; if (lane == l) bm = atomicAdd(missCount, (uint32_t)__popc(mm)); bm = __shfl_sync(0xffffffffu, bm, l); }
+                if (finishedNow) {
+                    const unsigned below = (1u << lane) - 1u;
+                    if (s.tri >= 0) B.shadeQueue[bh + __popc(mh & below)] = pix;
+                    else B.shadeQueue[B.capacity - 1u - (bm + __popc(mm & below))] = pix;
                 }
             }
             const unsigned live = __ballot_sync(0xffffffffu, active);
@@ -253,31 +254,66 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// k_pt_logic: one thread per queued path (grid-stride over the device-side count): apply the hit of the ray just
-// traced, run the interactions of the segment(s), queue the next ray or write the pixel.
+// k_pt_logic: apply the hit of the ray just traced, run the interactions of the segment(s), queue the next ray or
+// write the pixel.  FIRST = the pass after the primary rays: one thread per pixel, the path is initialised here
+// (same sampler values as k_pt_primary) and the segment-0 outputs (depth, motion vector, material mask) are written.
+// Otherwise: one thread per entry of the shade queue (grid-stride over the device-side counts).
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParams P, const WfBuffers B, const uint32_t* __restrict__ queueIn,
-                                                            const uint32_t* __restrict__ countIn, uint32_t* queueOut, uint32_t* countOut) {
-    const uint32_t n = *countIn;
+VD void logic_body(const PathTraceParams& P, const WfBuffers& B, uint32_t pix, bool first, bool& emit) {
+    const int iy = (int)(pix / (uint32_t)P.width), ix = (int)(pix - (uint32_t)iy * (uint32_t)P.width);
+    RayState r; int seg = 0; unsigned short mask = 0; Float2 sampleUv{0.0f, 0.0f};
+    if (first) init_path(P, r, sampleUv, ix, iy);
+    else load_state(B, pix, r, seg, mask);
+    const float4 h = B.hit[pix];
+    apply_hit(P, r, h.x, __float_as_int(h.w), h.y, h.z);
+    if (first) {
+        float outDepth = r.depth;
+        mask = (unsigned short)r.matId;
+        Float2 motion{0.0f, 0.0f};
+        if (r.hit) {                                                            // HistoryCamera::WorldToScreenSpace src/kernel.cuh:144-151
+            const Float3 v = mul(P.historyCamera.invCamMat, r.pos - P.historyCamera.pos);
+            const Float2 ndc = (Float2{v.x, v.y} / v.z) / P.camera.tanHalfFov;
+            motion = (Float2{0.5f, 0.5f} - ndc * Float2{0.5f, 0.5f}) - sampleUv;
+        }
+        motion = motion + 0.5f;
+        if (outDepth != outDepth) outDepth = 0.0f;                              // NAN_DETECTER src/pathtrace.cuh:113-117
+        if (motion.x != motion.x || motion.y != motion.y) motion = Float2{0.0f, 0.0f};
+        P.depth[pix] = __float2half_rn(outDepth);
+        P.motion[pix] = __float22half2_rn(make_float2(motion.x, motion.y));
+    }
+    emit = advance_path(P, r, seg, ix, iy, P.normal);
+    if (emit) { r.isHitProcessed = false; save_state(B, pix, r, seg, mask); }
+    else finalize_path(P, r, mask, ix, iy);
+}
+
+__global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTraceParams P, const WfBuffers B, uint32_t* countOut) {
+    // 8x4-pixel warps like the primary kernel (sky / terrain coherence)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tilesX = (P.width + 7) / 8;
+    const int tile = blockIdx.x * (kLogicThreads / 32) + warp;
+    const int ix = (tile % tilesX) * 8 + (lane & 7), iy = P.rowBegin + (tile / tilesX) * 4 + (lane >> 3);
+    bool emit = false;
+    const uint32_t pix = (uint32_t)((size_t)iy * P.width + ix);
+    if (ix < P.width && iy < P.rowEnd) logic_body(P, B, pix, true, emit);
+    queue_append(emit, pix, B.rayQueue, countOut, lane);
+}
+
+__global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParams P, const WfBuffers B, const uint32_t* __restrict__ hitCount,
+                                                            const uint32_t* __restrict__ missCount, uint32_t* countOut) {
+    const uint32_t nHit = *hitCount, nMiss = *missCount;
+    const uint32_t padHit = (nHit + 31u) & ~31u, total = padHit + nMiss;
     const int lane = threadIdx.x & 31;
     const uint32_t stride = gridDim.x * kLogicThreads;
     // every lane of a warp runs the same number of iterations so that queue_append stays warp-converged
-    for (uint32_t q0 = blockIdx.x * kLogicThreads + (threadIdx.x & ~31u); q0 < n; q0 += stride) {
+    for (uint32_t q0 = blockIdx.x * kLogicThreads + (threadIdx.x & ~31u); q0 < total; q0 += stride) {
         const uint32_t q = q0 + lane;
-        bool emit = false;
+        bool emit = false, valid;
+        uint32_t slot;
+        if (q0 < padHit) { valid = q < nHit; slot = q; }
+        else { valid = q < total; slot = B.capacity - 1u - (q - padHit); }
         uint32_t pix = 0;
-        if (q < n) {
-            pix = __ldg(queueIn + q);
-            const int iy = (int)(pix / (uint32_t)P.width), ix = (int)(pix - (uint32_t)iy * (uint32_t)P.width);
-            RayState r; int seg; unsigned short mask;
-            load_state(B, pix, r, seg, mask);
-            const float4 h = B.hit[pix];
-            apply_hit(P, r, h.x, __float_as_int(h.w), h.y, h.z);
-            emit = advance_path(P, r, seg, ix, iy, P.normal);
-            if (emit) { r.isHitProcessed = false; save_state(B, pix, r, seg, mask); }
-            else finalize_path(P, r, mask, ix, iy);
-        }
-        queue_append(emit, pix, queueOut, countOut, lane);
+        if (valid) { pix = B.shadeQueue[slot]; logic_body(P, B, pix, false, emit); }
+        queue_append(emit, pix, B.rayQueue, countOut, lane);
     }
 }
 
@@ -301,8 +337,9 @@ static int ensure_wf_buffers(Context& c, WfBuffers& B) {
     B.counters = reinterpret_cast<uint32_t*>(p); p += 256;
     float4** f4[6] = {&B.st0, &B.st1, &B.st2, &B.st3, &B.st4, &B.hit};
     for (auto f : f4) { *f = reinterpret_cast<float4*>(p); p += px * sizeof(float4); }
-    B.queue[0] = reinterpret_cast<uint32_t*>(p); p += px * sizeof(uint32_t);
-    B.queue[1] = reinterpret_cast<uint32_t*>(p);
+    B.rayQueue = reinterpret_cast<uint32_t*>(p); p += px * sizeof(uint32_t);
+    B.shadeQueue = reinterpret_cast<uint32_t*>(p);
+    B.capacity = (uint32_t)px;
     return RTRT_OK;
 }
 
@@ -322,13 +359,15 @@ int launch_pathtrace_wavefront(Context& c) {
     const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
     if (c.countVisits) k_pt_primary<true><<<grid, block, 0, c.stream>>>(P, B);
     else k_pt_primary<false><<<grid, block, 0, c.stream>>>(P, B);
-    c.launches += 1;
+    const int tiles = ((c.width + 7) / 8) * ((rows + 3) / 4);
+    k_pt_logic_first<<<(tiles + kLogicThreads / 32 - 1) / (kLogicThreads / 32), kLogicThreads, 0, c.stream>>>(P, B, B.counters + 0);
+    c.launches += 2;
     const int traceGrid = smCount * 8, logicGrid = smCount * 8;
     for (int round = 0; round < 4; ++round) {
-        uint32_t* qin = B.queue[round & 1]; uint32_t* qout = B.queue[(round + 1) & 1];
-        if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, qin, B.counters + round, B.counters + 8 + round, c.dRayCounter);
-        else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, qin, B.counters + round, B.counters + 8 + round, nullptr);
-        k_pt_logic<<<logicGrid, kLogicThreads, 0, c.stream>>>(P, B, qin, B.counters + round, qout, B.counters + round + 1);
+        uint32_t* cnt = B.counters;
+        if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
+        else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
+        k_pt_logic<<<logicGrid, kLogicThreads, 0, c.stream>>>(P, B, cnt + 16 + round, cnt + 24 + round, cnt + round + 1);
         c.launches += 2;
     }
     k_pt_count_rays<<<1, 1, 0, c.stream>>>(B.counters, (unsigned long long)c.width * rows, c.dRayCounter);

@@ -72,7 +72,10 @@ __device__ __forceinline__ RayPrep prepare_ray(const Float3& org, const Float3& 
     int kz = max_dim3(fabsf(dir.x), fabsf(dir.y), fabsf(dir.z));
     int kx = kz + 1; if (kx == 3) kx = 0;
     int ky = kx + 1; if (ky == 3) ky = 0;
-    if (comp(dir, kz) < 0.0f) { const int t = kx; kx = ky; ky = t; }
+    // The reference swaps kx and ky when dir[kz] < 0 (src/geometry.cuh:415-416) to keep the winding.  The swap negates
+    // U, V, W, det and T exactly (fl(a-b) = -fl(b-a), no FMA contraction in this TU), so the sign tests, u = U/det,
+    // v = V/det and t = T/det are bit-identical without it; leaving it out makes (kx, ky, kz) a pure rotation of
+    // (x, y, z), which ray_triangle selects with predicated moves instead of divergent branches.
     r.kx = kx; r.ky = ky; r.kz = kz;
     r.Sx = comp(dir, kx) / comp(dir, kz);
     r.Sy = comp(dir, ky) / comp(dir, kz);
@@ -110,11 +113,21 @@ __device__ __forceinline__ bool ray_box(const RayPrep& r, float mnx, float mny, 
     const float tfx = ((r.negX ? mnx : mxx) - r.orgFar.x) * r.rdirFar.x;
     const float tfy = ((r.negY ? mny : mxy) - r.orgFar.y) * r.rdirFar.y;
     const float tfz = ((r.negZ ? mnz : mxz) - r.orgFar.z) * r.rdirFar.z;
-    const float tn = sel_max(sel_max(tnx, tny), tnz);
-    const float tf = sel_min(sel_min(tfx, tfy), tfz);
+    // fmaxf/fminf (one FMNMX each) instead of the reference's select-style max/min: the operands are never NaN here
+    // (safe_divide keeps the reciprocals finite) and the two forms differ only in the sign of a zero result, which
+    // no later comparison can see (tNear is re-clamped with max(.,0), everything else is </<=/>).
+    const float tn = fmaxf(fmaxf(tnx, tny), tnz);
+    const float tf = fminf(fminf(tfx, tfy), tfz);
     const bool hit = tn <= tf && (tf > 0.0f);
-    tNear = sel_max(tn, 0.0f);
+    tNear = fmaxf(tn, 0.0f);
     return hit;
+}
+
+// branch-free select (the compiler turns the ternary chains of comp() into divergent branches)
+__device__ __forceinline__ float fsel(int p, float a, float b) {
+    float r;
+    asm("{ .reg .pred q; setp.ne.s32 q, %1, 0; selp.f32 %0, %2, %3, q; }" : "=f"(r) : "r"(p), "f"(a), "f"(b));
+    return r;
 }
 
 // RayTriangleWatertight (src/geometry.cuh:406-472); v1,v2,v3 = triangle rows 0..2
@@ -123,13 +136,17 @@ __device__ __forceinline__ bool ray_triangle(const RayPrep& r, const float4& q1,
     const Float3 A{q1.x - r.org.x, q1.y - r.org.y, q1.z - r.org.z};
     const Float3 B{q2.x - r.org.x, q2.y - r.org.y, q2.z - r.org.z};
     const Float3 C{q3.x - r.org.x, q3.y - r.org.y, q3.z - r.org.z};
-    const float Akz = comp(A, r.kz), Bkz = comp(B, r.kz), Ckz = comp(C, r.kz);
-    const float Ax = comp(A, r.kx) - r.Sx * Akz;
-    const float Ay = comp(A, r.ky) - r.Sy * Akz;
-    const float Bx = comp(B, r.kx) - r.Sx * Bkz;
-    const float By = comp(B, r.ky) - r.Sy * Bkz;
-    const float Cx = comp(C, r.kx) - r.Sx * Ckz;
-    const float Cy = comp(C, r.ky) - r.Sy * Ckz;
+    // (kx, ky, kz) = rotation of (x, y, z):  kz == 2 -> (x,y,z)   kz == 0 -> (y,z,x)   kz == 1 -> (z,x,y)
+    const int p0 = r.kz == 0, p1 = r.kz == 1;
+    const float Akx = fsel(p0, A.y, fsel(p1, A.z, A.x)), Aky = fsel(p0, A.z, fsel(p1, A.x, A.y)), Akz = fsel(p0, A.x, fsel(p1, A.y, A.z));
+    const float Bkx = fsel(p0, B.y, fsel(p1, B.z, B.x)), Bky = fsel(p0, B.z, fsel(p1, B.x, B.y)), Bkz = fsel(p0, B.x, fsel(p1, B.y, B.z));
+    const float Ckx = fsel(p0, C.y, fsel(p1, C.z, C.x)), Cky = fsel(p0, C.z, fsel(p1, C.x, C.y)), Ckz = fsel(p0, C.x, fsel(p1, C.y, C.z));
+    const float Ax = Akx - r.Sx * Akz;
+    const float Ay = Aky - r.Sy * Akz;
+    const float Bx = Bkx - r.Sx * Bkz;
+    const float By = Bky - r.Sy * Bkz;
+    const float Cx = Ckx - r.Sx * Ckz;
+    const float Cy = Cky - r.Sy * Ckz;
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -178,35 +195,37 @@ __device__ __forceinline__ void trav_init(TravState& s) {
     s.nodeVisits = 0; s.leafTests = 0;
 }
 
-// returns true when the traversal is finished (stack empty, or any-hit satisfied)
+// Advances the traversal by one reference iteration — or by two when the current link is a TLAS leaf: the
+// TLAS-leaf -> BLAS-root transition (src/traverse.h:191-197) is its own iteration in the reference (and is counted
+// as such in s.it against maxLoop) but costs three instructions, so the BLAS root is visited in the same physical step.
+// Returns true when the traversal is finished (stack empty, any-hit satisfied, or iteration cap reached).
 template <bool COUNT>
-__device__ __forceinline__ bool trav_step(const SceneView& sc, const RayPrep& r, TravState& s, int anyHit, int cap, uint32_t numTri,
+__device__ __forceinline__ bool trav_step(const SceneView& sc, const RayPrep& r, TravState& s, int anyHit, int cap, uint32_t numTri, int maxLoop,
                                           uint32_t* stackLink, float* stackT, const int stride) {
     bool pop = false;
-    const uint32_t cur = s.cur;
+    uint32_t cur = s.cur;
+    if ((cur & (kLinkLeaf | kLinkBlas)) == kLinkLeaf) {
+        cur = kLinkBlas | ((cur & 0x3FFFFFFFu) << 10);          // root of BLAS b = node 1024*b
+        s.cur = cur;
+        if (++s.it >= maxLoop) return true;
+    }
     if (cur & kLinkLeaf) {
-        if (cur & kLinkBlas) {
-            const uint32_t loadIdx = cur & 0x3FFFFFFFu;          // blasOffset*1024 + idx
-            float4 q1 = make_float4(0, 0, 0, 0), q2 = q1, q3 = q1;
-            if (loadIdx < numTri) {                               // SAFE_LOAD (src/traverse.h:155)
-                const float4* row = sc.triRows + (size_t)loadIdx * 8;
-                q1 = __ldg(row); q2 = __ldg(row + 1); q3 = __ldg(row + 2);
-            }
-            if (COUNT) s.leafTests++;
-            float tt, uu, vv;
-            if (ray_triangle(r, q1, q2, q3, s.t, tt, uu, vv)) {
-                s.u = uu; s.v = vv;
-                if (tt < s.t) {
-                    s.t = tt; s.tri = (int)loadIdx; s.ua = uu; s.va = vv;
-                    if (anyHit) return true;
-                }
-            }
-            pop = true;
-        } else {
-            // TLAS leaf -> root of that BLAS (src/traverse.h:191-197)
-            const uint32_t b = cur & 0x3FFFFFFFu;
-            s.cur = kLinkBlas | (b << 10);
+        const uint32_t loadIdx = cur & 0x3FFFFFFFu;          // blasOffset*1024 + idx
+        float4 q1 = make_float4(0, 0, 0, 0), q2 = q1, q3 = q1;
+        if (loadIdx < numTri) {                               // SAFE_LOAD (src/traverse.h:155)
+            const float4* row = sc.triRows + (size_t)loadIdx * 8;
+            q1 = __ldg(row); q2 = __ldg(row + 1); q3 = __ldg(row + 2);
         }
+        if (COUNT) s.leafTests++;
+        float tt, uu, vv;
+        if (ray_triangle(r, q1, q2, q3, s.t, tt, uu, vv)) {
+            s.u = uu; s.v = vv;
+            if (tt < s.t) {
+                s.t = tt; s.tri = (int)loadIdx; s.ua = uu; s.va = vv;
+                if (anyHit) return true;
+            }
+        }
+        pop = true;
     } else {
         float4 n0 = make_float4(0, 0, 0, 0), n1 = n0, n2 = n0, n3 = n0;
         const uint32_t idx = cur & 0x3FFFFFFFu;
@@ -238,7 +257,7 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, const RayPrep& r,
             s.cur = stackLink[s.top * stride]; s.curT = stackT[s.top * stride]; --s.top;
         } while (s.curT > s.t);
     }
-    return false;
+    return ++s.it >= maxLoop;
 }
 
 template <int STACK, bool COUNT>
@@ -248,8 +267,7 @@ __device__ __forceinline__ TraverseResult traverse_bvh(const SceneView& sc, cons
     trav_init(s);
     const int cap = sc.stackSize < STACK ? sc.stackSize : STACK;
     const uint32_t numTri = sc.numBatches * kBatchSize;
-    for (; s.it < sc.maxLoop; ++s.it)
-        if (trav_step<COUNT>(sc, r, s, anyHit, cap, numTri, stackLink, stackT, stride)) break;
+    while (!trav_step<COUNT>(sc, r, s, anyHit, cap, numTri, sc.maxLoop, stackLink, stackT, stride)) {}
     TraverseResult res;
     res.t = s.t; res.tri = s.tri; res.u = s.u; res.v = s.v; res.ua = s.ua; res.va = s.va;
     res.nodeVisits = s.nodeVisits; res.leafTests = s.leafTests;
