@@ -154,13 +154,12 @@ VD Float4 sample_tex_lod_rolled(const MipTex* texs, int t, Float2 uv, float lod)
         const int w = texs[t].w[lv], h = texs[t].h[lv];
         const ushort4* __restrict__ img = texs[t].mip[lv];
         const BicubicTaps tp = bicubic_taps(uv, w, h);
+        int xs[2], ys[2];
+        repeat_pair(tp.x0, w, xs[0], xs[1]);
+        repeat_pair(tp.y0, h, ys[0], ys[1]);
         Float4 out{0, 0, 0, 0};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            int x = tp.x0 + (i & 1), y = tp.y0 + (i >> 1);
-            boundary_repeat(x, y, w, h);
-            out = out + load_ushort4(img, w, h, x, y) * tp.w[i];
-        }
+        for (int i = 0; i < 4; ++i) out = out + load_ushort4(img, w, h, xs[i & 1], ys[i >> 1]) * tp.w[i];
         out = out / tp.sum;
         acc = k ? (acc + out * f) : (out * (1.0f - f));       // a * (1 - f) + b * f
     }

@@ -77,22 +77,44 @@ VD BicubicTaps bicubic_taps(Float2 uv, int w, int h) {
     return t;
 }
 
+// x / 65535.0f for integer x in [0, 65535], correctly rounded: q = x*r, q' = q + r*(x - q*65535) with exact FMAs.
+// Verified exhaustively against IEEE division for all 65536 inputs (tools/check_unorm16.c); 3 instructions instead of
+// the ~10-instruction division sequence, and the texel loads are the hottest lines of the shading kernels.
+VD float unorm16(unsigned short v) {
+    const float x = (float)v, r = 1.0f / 65535.0f;
+    const float q = __fmul_rn(x, r);
+    return __fmaf_rn(__fmaf_rn(-q, 65535.0f, x), r, q);
+}
 VD Float4 load_ushort4(const ushort4* __restrict__ img, int w, int h, int x, int y) {      // Load2DUshort4 src/sampler.cuh:186-197
     x = clampi(x, 0, w - 1); y = clampi(y, 0, h - 1);                                       // surface clamp mode
     const ushort4 p = __ldg(img + (size_t)y * w + x);
-    return Float4{p.x / 65535.0f, p.y / 65535.0f, p.z / 65535.0f, p.w / 65535.0f};
+    return Float4{unorm16(p.x), unorm16(p.y), unorm16(p.z), unorm16(p.w)};
+}
+
+// BoundaryFuncRepeat (src/sampler.cuh:293-303) followed by the surface clamp, for the tap pair (x0, x0 + 1), with ONE
+// integer modulo (a mask when the extent is a power of two) instead of up to four per tap:
+//   x in [0,w) -> x ;  x >= w -> x % w ;  x < 0 -> w - (-x) % w  (which can be w: the clamp then gives w - 1)
+VD int mod_nonneg(int a, int w) { return ((w & (w - 1)) == 0) ? (a & (w - 1)) : (a % w); }
+VD void repeat_pair(int x0, int w, int& a0, int& a1) {
+    if (x0 >= 0) {
+        const int a = mod_nonneg(x0, w);
+        a0 = a; a1 = (a + 1 == w) ? 0 : a + 1;
+    } else {
+        const int b = mod_nonneg(-x0, w);
+        a0 = min(w - b, w - 1);
+        a1 = (x0 == -1) ? 0 : min(b == 0 ? 1 : w - b + 1, w - 1);
+    }
 }
 
 VD Float4 sample_tex_level(const MipTex& m, int lod, Float2 uv) {
     const int w = m.w[lod], h = m.h[lod];
     const BicubicTaps t = bicubic_taps(uv, w, h);
+    int xs[2], ys[2];
+    repeat_pair(t.x0, w, xs[0], xs[1]);
+    repeat_pair(t.y0, h, ys[0], ys[1]);
     Float4 out{0, 0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        int x = t.x0 + (i & 1), y = t.y0 + (i >> 1);
-        boundary_repeat(x, y, w, h);
-        out = out + load_ushort4(m.mip[lod], w, h, x, y) * t.w[i];
-    }
+    for (int i = 0; i < 4; ++i) out = out + load_ushort4(m.mip[lod], w, h, xs[i & 1], ys[i >> 1]) * t.w[i];
     return out / t.sum;
 }
 // SampleBicubicSmoothStepLod src/sampler.cuh:565-584
