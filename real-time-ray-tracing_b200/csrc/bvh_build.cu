@@ -14,7 +14,7 @@
 
 namespace rtrt {
 
-constexpr int kBuildThreads = 256;
+constexpr int kBuildThreads = 512;
 
 struct BuildParams {
     const float* __restrict__ pos;       // V x 3

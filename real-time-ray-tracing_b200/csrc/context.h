@@ -59,7 +59,7 @@ struct Context {
     // G-buffers, linear, reference formats (src/init.cu:473-500)
     void* dColor = nullptr; void* dNormal = nullptr; void* dAlbedo = nullptr; void* dDepth = nullptr; void* dMotion = nullptr;
     void* dAccum = nullptr; void* dHistoryColor = nullptr; void* dHistoryDepth = nullptr; void* dHistoryAlbedo = nullptr;
-    void* dNoise = nullptr; void* dNoise16 = nullptr; void* dColorTmp = nullptr;
+    void* dNoise = nullptr; void* dNoise16 = nullptr; void* dColorTmp = nullptr; void* dGuide = nullptr;
     int gbufW = 0, gbufH = 0;
     unsigned long long* dRayCounter = nullptr;
     rtrt_denoise_params denoiseParams{}; rtrt_pass_settings passSettings{};

@@ -24,6 +24,7 @@ struct DnParams {
     const ushort4* __restrict__ normal; const __half* __restrict__ depth; const __half2* __restrict__ motion;
     const ushort4* __restrict__ albedo;
     __half* noise8; __half* noise16;
+    const ushort4* __restrict__ guide;       // normal.xyz | depth, packed once per frame by k_dn_pack_guide (8 B/px)
 };
 
 __constant__ float cG3[9] = {0.0578968, 0.0921378, 0.0584323, 0.0921378, 0.146629, 0.09299, 0.0584322, 0.0929898, 0.0589727};
@@ -118,15 +119,33 @@ __device__ __forceinline__ void block_noise_levels(const DnParams& P, const usho
     }
 }
 
-// edge-stopping weight shared by the three bilateral filters
+// edge-stopping weight shared by the three bilateral filters (src/temporalDenoising.cuh:456-460, 565-569, 742-746).
+// powf(x, sigma) and expf(x) are evaluated as 2^(sigma*log2 x) and 2^(x*log2 e) on the SFU (MUFU.LG2 / MUFU.EX2):
+// three instructions instead of ~150 per tap, for 9 + 24 + 75 taps per pixel.  Relative error <= ~sigma * 2^-21
+// (1e-4 at sigma = 100) against the denoiser's stated 2e-2 rel-RMSE tolerance; tests/test_denoise_gpu.py holds.
+// plain 3-term dot for the edge weights (the reference's compensated dot, src/linearMath.h:484, costs ~30 instructions per tap;
+// the difference is one ulp of a value that is then raised to a power with 1e-4 relative error anyway)
+VD float dot_plain(Float3 a, Float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
 VD float bilateral_weight(Float3 n0, Float3 n1, float d0, float d1, bool maskDiffers, float sigN, float sigD, float sigM, float floorDot, float g) {
     float w = 1.0f;
-    w *= powf(sel_max(dot(n0, n1), floorDot), sigN);
+    w *= __powf(sel_max(dot_plain(n0, n1), floorDot), sigN);
     const float dd = (d0 - d1) / sigD;
-    w *= expf(-0.5f * dd * dd);
+    w *= __expf(-0.5f * dd * dd);
     w *= maskDiffers ? 1.0f / sigM : 1.0f;
     w *= g;
     return w;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Guide pack: normal.xyz (half) + depth (half) -> one 8-byte texel, so every later tap costs one guide load, not two.
+// -------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict__ normal, const __half* __restrict__ depth, ushort4* __restrict__ guide, size_t n) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    ushort4 g = __ldg(normal + i);
+    g.w = __half_as_ushort(__ldg(depth + i));
+    guide[i] = g;
 }
 
 // -------------------------------------------------------------------------------------------------------------------
@@ -146,9 +165,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
         const int gx = clampi(x0 + i % T, 0, P.W - 1), gy = clampi(y0 + i / T, 0, P.H - 1);
         const size_t g = (size_t)gy * P.W + gx;
         sC[i] = __ldg(in + g);
-        ushort4 n = __ldg(P.normal + g);
-        n.w = __half_as_ushort(__ldg(P.depth + g));
-        sG[i] = n;
+        sG[i] = __ldg(P.guide + g);
     }
     __syncthreads();
     const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
@@ -229,9 +246,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
         const int gx = clampi(x0 + lx, 0, P.W - 1), gy = clampi(y0 + ly, 0, P.H - 1);
         const size_t g = (size_t)gy * P.W + gx;
         sC[i] = __ldg(in + g);
-        ushort4 n = __ldg(P.normal + g);
-        n.w = __half_as_ushort(__ldg(P.depth + g));
-        sG[i] = n;
+        sG[i] = __ldg(P.guide + g);
     }
     __syncthreads();
     const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
@@ -283,8 +298,9 @@ __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ush
     ushort4 result = __ldg(in + c);
     const bool active = !(__half2float(__ldg(gate16 + (size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_large);
     if (active) {
-        const Float3 normalValue = px_rgb(__ldg(P.normal + c));
-        const float depthValue = __half2float(__ldg(P.depth + c));
+        const ushort4 cg = __ldg(P.guide + c);
+        const Float3 normalValue = px_rgb(cg);
+        const float depthValue = h2f(cg.w);
         const unsigned short maskValue = result.w;
         if (!(depthValue >= 10e9f)) {
             Float3 sumC = f3(0.0f); float sumW = 0.0f;
@@ -293,9 +309,9 @@ __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ush
                 const int i = k % 5, j = k / 5;
                 const int sx = clampi(x + (i - 2) * S, 0, P.W - 1), sy = clampi(y + (j - 2) * S, 0, P.H - 1);
                 const size_t g = (size_t)sy * P.W + sx;
-                const ushort4 q = __ldg(in + g);
+                const ushort4 q = __ldg(in + g), gg = __ldg(P.guide + g);
                 Float3 color = px_rgb(q);
-                float w = bilateral_weight(normalValue, px_rgb(__ldg(P.normal + g)), depthValue, __half2float(__ldg(P.depth + g)), maskValue != q.w,
+                float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w,
                                            P.large_n, P.large_d, P.large_m, 0.0f, cG5[k]);
                 if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
                 sumC = sumC + color * w; sumW += w;
@@ -390,6 +406,7 @@ int launch_denoise(Context& c) {
     P.normal = reinterpret_cast<const ushort4*>(c.dNormal); P.depth = reinterpret_cast<const __half*>(c.dDepth);
     P.motion = reinterpret_cast<const __half2*>(c.dMotion); P.albedo = reinterpret_cast<const ushort4*>(c.dAlbedo);
     P.noise8 = reinterpret_cast<__half*>(c.dNoise); P.noise16 = reinterpret_cast<__half*>(c.dNoise16);
+    P.guide = reinterpret_cast<const ushort4*>(c.dGuide);
     const rtrt_pass_settings& ps = c.passSettings;
     const bool temporal = ps.enableTemporalDenoising != 0, local = ps.enableLocalSpatialFilter != 0, wide = ps.enableWideSpatialFilter != 0,
                tf2 = ps.enableTemporalDenoising2 != 0, notFirst = c.frameNum != 1;
@@ -400,6 +417,11 @@ int launch_denoise(Context& c) {
     auto swap = [&]() { ushort4* t = cur; cur = oth; oth = t; };
     const size_t bytes = (size_t)c.width * c.height * sizeof(ushort4);
 
+    {
+        const size_t n = (size_t)c.width * c.height;
+        k_dn_pack_guide<<<(unsigned)((n + 255) / 256), 256, 0, c.stream>>>(P.normal, P.depth, reinterpret_cast<ushort4*>(c.dGuide), n);
+        c.launches++;
+    }
     // TemporalFilter (src/denoising.cu:49-64) [+ noise level of its output, :68-76]
     if (temporal && notFirst) { k_dn_temporal<true><<<grid, block, 0, c.stream>>>(P, cur, accum, oth); swap(); c.launches++; }
     else if (local) { k_dn_temporal<false><<<grid, block, 0, c.stream>>>(P, cur, accum, oth); c.launches++; }

@@ -210,7 +210,7 @@ static void dfree2(T*& p) { if (p) cudaFree(p); p = nullptr; }
 
 static void free_gbuffers(Context& c) {
     void** bufs[] = {&c.dColor, &c.dNormal, &c.dAlbedo, &c.dDepth, &c.dMotion, &c.dAccum, &c.dHistoryColor, &c.dHistoryDepth,
-                     &c.dHistoryAlbedo, &c.dNoise, &c.dNoise16, &c.dColorTmp};
+                     &c.dHistoryAlbedo, &c.dNoise, &c.dNoise16, &c.dColorTmp, &c.dGuide};
     for (void** b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
     c.gbufW = c.gbufH = 0;
 }
@@ -343,7 +343,7 @@ int ensure_frame_resources(Context& c) {
         struct { void** p; size_t bytes; } plan[] = {
             {&c.dColor, px * 8}, {&c.dNormal, px * 8}, {&c.dAlbedo, px * 8}, {&c.dDepth, px * 2}, {&c.dMotion, px * 4},
             {&c.dAccum, px * 8}, {&c.dHistoryColor, px * 8}, {&c.dHistoryDepth, px * 2}, {&c.dHistoryAlbedo, px * 8},
-            {&c.dNoise, n8 * 2}, {&c.dNoise16, n16 * 2}, {&c.dColorTmp, px * 8}};
+            {&c.dNoise, n8 * 2}, {&c.dNoise16, n16 * 2}, {&c.dColorTmp, px * 8}, {&c.dGuide, px * 8}};
         for (auto& e : plan) {
             RTRT_CUDA(c, cudaMalloc(e.p, e.bytes));
             RTRT_CUDA(c, cudaMemsetAsync(*e.p, 0, e.bytes, c.stream));
