@@ -53,12 +53,11 @@ struct SegSmem {
         uint16_t hist[32][256];
         AABB     nodeBox[kSeg];
     } scratch;                                 // 24 KB
-    uint32_t keys[2][kSeg];                    //  8 KB  ping-pong
+    uint32_t keys[2][kSeg];                    //  8 KB  ping-pong; after the sort keys[1] is reused as the refit rendezvous counters
     uint16_t ids[2][kSeg];                     //  4 KB
     uint32_t childL[kSeg], childR[kSeg];       //  8 KB  link | kLeafBit
     uint16_t parent[kSeg];                     //  2 KB  parent of internal node
     uint16_t leafParent[kSeg];                 //  2 KB  parent of the leaf at sorted position p
-    uint32_t arrive[kSeg];                     //  4 KB  refit rendezvous counters
     uint32_t digitBase[256];                   //  1 KB
     uint32_t warpSum[8];
     float    red[6][32];                       //  block AABB reduction
@@ -224,13 +223,14 @@ __device__ __forceinline__ AABB child_box(const SegSmem& s, uint32_t link) {
 // walker to reach a node merges its children.  Boxes are exact unions => order independent. ----
 template <int NT>
 __device__ __forceinline__ void block_refit(SegSmem& s, int n) {
-    for (int i = threadIdx.x; i < n - 1; i += NT) s.arrive[i] = 0u;
+    uint32_t* arrive = s.keys[1];              // dead after block_sort_1024 (the sorted keys live in keys[0])
+    for (int i = threadIdx.x; i < n - 1; i += NT) arrive[i] = 0u;
     __syncthreads();
     for (int p = threadIdx.x; p < n; p += NT) {
         uint32_t cur = s.leafParent[p];
         while (true) {
             __threadfence_block();
-            if (atomicAdd(&s.arrive[cur], 1u) == 0u) break;      // first arrival: sibling subtree pending
+            if (atomicAdd(&arrive[cur], 1u) == 0u) break;      // first arrival: sibling subtree pending
             __threadfence_block();
             AABB b = child_box(s, s.childL[cur]);
             aabb_grow(b, child_box(s, s.childR[cur]));

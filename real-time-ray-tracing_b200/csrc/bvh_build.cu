@@ -65,7 +65,7 @@ __device__ void tlas_build_block(SegSmem& s, const BuildParams& p) {
 
 // ---- one CTA per batch ----
 template <int NT>
-__global__ void __launch_bounds__(NT) k_build_blas(const BuildParams p) {
+__global__ void __launch_bounds__(NT, NT == 1024 ? 2 : 1) k_build_blas(const BuildParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SegSmem& s = *reinterpret_cast<SegSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
