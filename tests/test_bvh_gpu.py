@@ -107,3 +107,25 @@ def test_errors(pkg):
         with pytest.raises(pkg.RtrtError) as e:
             r.set_mesh(np.zeros((3, 3), np.float32), np.array([[0, 1, 7]], np.uint32), np.zeros((3, 3), np.float32))
         assert e.value.code == -1        # index out of range
+
+
+@pytest.mark.parametrize("quads", [(520, 1024), (1024, 2048)])      # 1 064 960 tris = 1040 batches; 4 194 304 tris = 4096 batches (C3)
+def test_build_beyond_1024_batches(pkg, orc, quads):
+    """Generalisation rule B7: the reference stops at 1023 batches (src/init.cu:126); the top level then runs the same
+    algorithm multi-CTA (device radix sort + global Karras + atomic refit).  Oracle = the same restatement over B items."""
+    pos, nrm, idx = pkg.scenes.terrain(*quads, seed=5)
+    ob = orc.build_bvh(pos, nrm, idx)
+    assert ob.num_batches > 1024
+    with pkg.RayTracer(64, 64) as r:
+        r.set_option("keep_presort_morton", 1)
+        r.set_mesh(pos, idx, nrm)
+        r.build_bvh()
+        assert r.counts() == (ob.num_tris, ob.num_batches, ob.num_batches_padded)
+        bufs = read_all_stage1(r, pkg, presort=True)
+        assert_bvh_equal(bufs, ob, pkg)
+        assert sorted(tree_leaves(bufs[pkg.BUF_TLAS_BVH_NODES], ob.num_batches)) == list(range(ob.num_batches))
+        # and the two-level hierarchy is traversable: primary rays, bit-exact hits
+        cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 96, 64)
+        rays = pkg.scenes.primary_rays(cam, 96, 64)
+        from helpers import assert_hits_equal
+        assert_hits_equal(r.traverse(rays), orc.traverse(ob, rays))
