@@ -87,6 +87,7 @@ typedef enum rtrt_buffer {
     RTRT_BUF_TLAS_MORTON,        /* uint32[Bp]                    (TLAS_morton2.csv)          */
     RTRT_BUF_TLAS_REORDER_IDX,   /* uint32[Bp]                    (TLAS_reorderIdx.csv)       */
     RTRT_BUF_TLAS_BVH_NODES,     /* BVHNode[Bp]                   (TLAS_bvhNodes.csv)         */
+    RTRT_BUF_TRI_PERMUTATION,    /* uint32[N]: sorted position -> input triangle id; only with option global_sort=1     */
     RTRT_BUF_COUNT_STAGE1,
     /* Buffer2DName surfaces of the path (src/kernel.cuh:286-330), linear, row-major, W x H unless noted */
     RTRT_BUF_RENDER_COLOR = 32,  /* half3 colour (demodulated radiance) + uint16 material mask, 8 B/px  */
@@ -157,6 +158,9 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
  *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
  *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)
+ *   "global_sort"         0/1  : rtrt_build_bvh first sorts the triangles by the 60-bit Morton code of their centroid in the
+ *                                mesh bounding box (the offline step of tool/meshProcessor.cpp:146-200, on the device, per
+ *                                call); triangle ids reported by the library are then positions in that order
  *   "wavefront"           1/0  : path-trace driver: wavefront ray queues with persistent traversal (default) or one megakernel
  *   "count_visits"        0/1  : rtrt_pathtrace also counts node visits / leaf tests (rtrt_timings)         */
 

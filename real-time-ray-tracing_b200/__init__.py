@@ -12,4 +12,4 @@ from ._lib import *  # noqa: F401,F403  (BUF_* ids, ctypes structs)
 from . import scenes  # noqa: F401
 from ._lib import (BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES,
                    BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX,
-                   BUF_TLAS_BVH_NODES)  # noqa: F401
+                   BUF_TLAS_BVH_NODES, BUF_TRI_PERMUTATION)  # noqa: F401

@@ -15,7 +15,7 @@ STATUS_NAMES = {0: "RTRT_OK", -1: "RTRT_ERR_ARG", -2: "RTRT_ERR_CUDA", -3: "RTRT
 
 # rtrt_buffer
 BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES, \
-    BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES = range(11)
+    BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES, BUF_TRI_PERMUTATION = range(12)
 BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCUMULATION_COLOR, BUF_HISTORY_COLOR, \
     BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF = range(32, 46)
 

@@ -29,7 +29,7 @@ BUFFER_DTYPES = {
     L.BUF_TRIANGLES: TRIANGLE_DTYPE, L.BUF_AABBS: AABB_DTYPE, L.BUF_MORTON_PRESORT: np.dtype("<u4"),
     L.BUF_MORTON: np.dtype("<u4"), L.BUF_REORDER_IDX: np.dtype("<u4"), L.BUF_BVH_NODES: BVHNODE_DTYPE,
     L.BUF_TLAS_AABBS: AABB_DTYPE, L.BUF_TLAS_MORTON_PRESORT: np.dtype("<u4"), L.BUF_TLAS_MORTON: np.dtype("<u4"),
-    L.BUF_TLAS_REORDER_IDX: np.dtype("<u4"), L.BUF_TLAS_BVH_NODES: BVHNODE_DTYPE,
+    L.BUF_TLAS_REORDER_IDX: np.dtype("<u4"), L.BUF_TLAS_BVH_NODES: BVHNODE_DTYPE, L.BUF_TRI_PERMUTATION: np.dtype("<u4"),
 }
 
 MATERIAL_DTYPE = np.dtype([("albedo", "<f4", 3), ("type", "<u4"), ("F0", "<f4", 3), ("alpha", "<f4")])   # src/kernel.cuh:182-196

@@ -147,8 +147,9 @@ __global__ void __launch_bounds__(NT) k_build_tlas(const BuildParams p) {
 // ------------------------------------------------------------------------------------------------
 int launch_build_bvh(Context& c) {
     if (c.numTris == 0) return c.fail(RTRT_ERR_STATE, "rtrt_build_bvh: no mesh set");
+    if (c.globalSort) { int rc = launch_presort(c); if (rc) return rc; }
     BuildParams p{};
-    p.pos = c.dPos; p.nrm = c.dNrm; p.idx = c.dIdx; p.numTris = c.numTris; p.numBatches = c.numBatches;
+    p.pos = c.dPos; p.nrm = c.dNrm; p.idx = c.globalSort ? c.dIdxSorted : c.dIdx; p.numTris = c.numTris; p.numBatches = c.numBatches;
     p.triangles = c.dTriangles; p.aabbs = c.dAabbs; p.morton = c.dMorton; p.reorderIdx = c.dReorderIdx; p.nodes = c.dNodes;
     p.mortonPre = c.keepPresortMorton ? c.dMortonPre : nullptr;
     p.tlasAabbs = c.dTlasAabbs; p.tlasMorton = c.dTlasMorton; p.tlasReorderIdx = c.dTlasReorderIdx; p.tlasNodes = c.dTlasNodes;

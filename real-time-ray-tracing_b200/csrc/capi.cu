@@ -28,6 +28,8 @@ static void free_mesh(Context& c) {
     dfree(c.dTriangles); dfree(c.dAabbs); dfree(c.dMorton); dfree(c.dReorderIdx); dfree(c.dNodes); dfree(c.dMortonPre);
     dfree(c.dTlasAabbs); dfree(c.dTlasMorton); dfree(c.dTlasReorderIdx); dfree(c.dTlasNodes); dfree(c.dTlasMortonPre);
     if (c.dSortTmp) { cudaFree(c.dSortTmp); c.dSortTmp = nullptr; c.sortTmpBytes = 0; }
+    if (c.dPresort) { cudaFree(c.dPresort); c.dPresort = nullptr; c.presortBytes = 0; }
+    dfree(c.dIdxSorted); dfree(c.dTriPerm);
     c.numVerts = c.numTris = c.numBatches = c.numBatchesPadded = 0;
     c.bvhValid = false;
 }
@@ -241,6 +243,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!name) return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: null name");
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 32) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..32"); c.stackSize = (int)value; return RTRT_OK; }
+    if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }
@@ -313,6 +316,7 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         case RTRT_BUF_TLAS_MORTON: p = c.dTlasMorton; b = bp * 4; break;
         case RTRT_BUF_TLAS_REORDER_IDX: p = c.dTlasReorderIdx; b = bp * 4; break;
         case RTRT_BUF_TLAS_BVH_NODES: p = c.dTlasNodes; b = bp * sizeof(BVHNode); break;
+        case RTRT_BUF_TRI_PERMUTATION: p = c.dTriPerm; b = (size_t)c.numTris * 4; break;
         case RTRT_BUF_RENDER_COLOR: p = c.dColor; b = px * 8; break;
         case RTRT_BUF_NORMAL: p = c.dNormal; b = px * 8; break;
         case RTRT_BUF_ALBEDO: p = c.dAlbedo; b = px * 8; break;

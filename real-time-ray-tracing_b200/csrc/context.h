@@ -30,6 +30,8 @@ struct Context {
     uint32_t* dTicket = nullptr;
     void* dSortTmp = nullptr; size_t sortTmpBytes = 0;     // scratch of the global (multi-CTA) paths
     bool keepPresortMorton = false;
+    bool globalSort = false;                              // option "global_sort": device Morton pre-sort of the triangles before batching
+    uint32_t* dIdxSorted = nullptr; uint32_t* dTriPerm = nullptr; void* dPresort = nullptr; size_t presortBytes = 0;
     bool bvhValid = false;
 
     // ---- traversal scratch for the host-buffer entry point ----
@@ -91,6 +93,7 @@ enum { STAGE_BUILD = 0, STAGE_TRAVERSE = 1, STAGE_PATHTRACE = 2, STAGE_DENOISE =
 // stage launchers (each enqueues on ctx.stream, no host sync)
 int launch_build_bvh(Context& c);
 int launch_build_tlas_global(Context& c);
+int launch_presort(Context& c);             // bvh_presort.cu
 int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int anyHit, unsigned long long* dCounters);
 int launch_pathtrace(Context& c);
 int launch_denoise(Context& c);

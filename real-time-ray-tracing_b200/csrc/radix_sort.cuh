@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(kRsThreads) k_rs_hist(const K* __restrict__ ke
 }
 
 // one CTA per digit: exclusive scan of that digit's counts over the tiles (in place) + the digit total
-__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* __restrict__ tileHist, uint32_t numTiles, uint32_t* __restrict__ digitTotal) {
+static __global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* __restrict__ tileHist, uint32_t numTiles, uint32_t* __restrict__ digitTotal) {
     __shared__ uint32_t warpSum[32];
     __shared__ uint32_t carry;
     uint32_t* row = tileHist + (size_t)blockIdx.x * numTiles;

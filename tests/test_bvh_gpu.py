@@ -129,3 +129,24 @@ def test_build_beyond_1024_batches(pkg, orc, quads):
         rays = pkg.scenes.primary_rays(cam, 96, 64)
         from helpers import assert_hits_equal
         assert_hits_equal(r.traverse(rays), orc.traverse(ob, rays))
+
+
+@pytest.mark.parametrize("quads", [(64, 80), (300, 512)])
+def test_global_morton_presort(pkg, orc, quads):
+    """option global_sort: the offline CPU pre-sort of tool/meshProcessor.cpp:146-200 (60-bit Morton of the centroid in the mesh
+    bounding box, stable) done on the device in front of the batch build.  Shuffled input + device sort must give exactly the
+    arrays of host-sorted input + plain build, and the permutation must be the stable argsort of the codes."""
+    pos, nrm, idx = pkg.scenes.terrain(*quads, seed=7, order="shuffle")
+    c = (pos[idx[:, 0]] + pos[idx[:, 1]] + pos[idx[:, 2]]) / np.float32(3.0)
+    code = pkg.scenes.morton60(c[:, 0], c[:, 1], c[:, 2], pos.min(axis=0), pos.max(axis=0))
+    perm = np.argsort(code, kind="stable").astype(np.uint32)
+    ob = orc.build_bvh(pos, nrm, idx[perm])
+    with pkg.RayTracer(64, 64) as r:
+        r.set_option("keep_presort_morton", 1)
+        r.set_option("global_sort", 1)
+        r.set_mesh(pos, idx, nrm)
+        r.build_bvh()
+        np.testing.assert_array_equal(r.read_buffer(pkg.BUF_TRI_PERMUTATION), perm)
+        assert_bvh_equal(read_all_stage1(r, pkg, presort=True), ob, pkg)
+        r.build_bvh()                                     # per-frame re-sort + rebuild is repeatable
+        assert_bvh_equal(read_all_stage1(r, pkg, presort=True), ob, pkg)
