@@ -1,6 +1,10 @@
 """ctypes wrapper of oracle/_build/liborc.so (the CPU restatement of the reference's hot path).
 
-ORACLE — TEST INFRASTRUCTURE ONLY; parity unpinned (the reference ships no golden vectors for this path).
+ORACLE — TEST INFRASTRUCTURE ONLY.
+Parity status: stage 1 (LBVH build) and the traversal are PINNED against the reference's own CUDA kernels compiled for
+sm_100 (oracle/refcuda -> oracle/_ref/librefcuda.so, tests/test_refcuda_gpu.py: bit-exact at 10 240 / 65 536 / 1 047 552
+triangles).  Shading (path trace) and denoise remain unpinned: the reference ships no golden vectors for them and their
+kernels need cudaArray surfaces + assets that are missing blobs.
 """
 import ctypes as C
 import os

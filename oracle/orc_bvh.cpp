@@ -182,7 +182,11 @@ int orc_build_bvh(const float* pos, const float* nrm, const u32* idx, u32 V, u32
         AABB m = node_merged(bn[(size_t)kBatch * k]);                            // :294-296
         centre[k] = (m.max + m.min) / 2.0f;                                      // :297
         tb[k] = m;
-        scene.min = min3f(scene.min, m.min); scene.max = max3f(scene.max, m.max);
+        // UpdateTLAS reduces its 256 per-thread boxes with strides 128 and 64 and then lets warp 0 reduce entries 0..31 only
+        // (src/updateGeometry.cuh:313-330; the "tid < 32: merge tid + 32" step of UpdateSceneGeometry :219-223 is missing), so
+        // the boxes of threads 32..63, 96..127, 160..191 and 224..255 never reach the scene box: batches with k mod 256 >= 128
+        // are left out.  Reproduced for every B the reference can run (< 1024); the multi-CTA generalisation uses all batches.
+        if (B >= kBatch || (k & 255u) < 128u) { scene.min = min3f(scene.min, m.min); scene.max = max3f(scene.max, m.max); }
     }
     for (u32 k = 0; k < Bp; ++k) tlasMorton[k] = (k < B) ? morton_of(centre[k], scene) : 0xFFFFFFFFu;
     if (tlasMortonPre) std::memcpy(tlasMortonPre, tlasMorton, Bp * sizeof(u32));

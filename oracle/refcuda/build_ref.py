@@ -27,7 +27,7 @@ REF = os.environ.get("RTRT_REFERENCE", "/root/reference")
 OUT_DIR = os.path.join(os.path.dirname(HERE), "_ref")
 
 HEADERS = ["linearMath.h", "geometry.h", "geometry.cuh", "bvhNode.cuh", "precision.cuh", "debugUtil.h", "updateGeometry.cuh",
-           "radixSort.cuh", "buildBVH.cuh", "traverse.h", "blueNoiseRandGen.h", "blueNoiseRandGenData.h"]
+           "radixSort.cuh", "buildBVH.cuh", "traverse.h", "blueNoiseRandGen.h", "blueNoiseRandGenData.h", "cudaError.cuh"]
 
 # POD proxies: same bytes as Float2/Float3, no constructors (so they may live in an anonymous struct), convertible.
 PROXIES = r'''
@@ -65,6 +65,7 @@ def patch_linear_math(t):
     t = sub1(t, r"struct \{\s*Float3 v0, v1, v2;\s*\};\s*Float3 _v3\[3\];", "struct { RefPod3 v0, v1, v2; };\n\t\tRefPod3 _v3p[3];", "Mat3 union")
     t = t.replace("Float3&       operator[](int i)       { return _v3[i]; }", "Float3&       operator[](int i)       { return *reinterpret_cast<Float3*>(&_v3p[i]); }")
     t = t.replace("const Float3& operator[](int i) const { return _v3[i]; }", "const Float3& operator[](int i) const { return *reinterpret_cast<const Float3*>(&_v3p[i]); }")
+    t = sub1(t, r": v0\{v0\}, v1\{v1\}, v2\{v2\} \{\}", "{ this->v0 = v0; this->v1 = v1; this->v2 = v2; }", "Mat3 column ctor")
     # proxies declared before the first struct, defined after Float3
     t = sub1(t, r"(struct Float2\s*\{)", PROXIES.replace("\\", "\\\\") + r"\n\1", "proxy decl")
     t = sub1(t, r"(struct Int3\s*\{)", PROXY_DEFS.replace("\\", "\\\\") + r"\n\1", "proxy defs")
@@ -97,7 +98,9 @@ def main():
             shutil.copy(os.path.join(REF, "src", h), os.path.join(tmp, h))
         for name, fn in (("linearMath.h", patch_linear_math), ("geometry.h", patch_geometry_h)):
             p = os.path.join(tmp, name)
-            open(p, "w").write(fn(open(p, encoding="utf-8", errors="replace").read()))
+            src = open(p, encoding="utf-8", errors="replace").read()
+            os.chmod(p, 0o644)
+            open(p, "w").write(fn(src))
         out = os.path.join(OUT_DIR, "librefcuda.so" if fmad == "false" else "librefcuda_fmad.so")
         cmd = ["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100,code=sm_100", "-O3", "-lineinfo", f"--fmad={fmad}", "-std=c++17",
                "-Xcompiler", "-fPIC", "-Xcompiler", "-w", "-w", "-shared", "-I", tmp, os.path.join(HERE, "harness.cu"), "-o", out, "-lcudart"]

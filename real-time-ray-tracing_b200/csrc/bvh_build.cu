@@ -50,7 +50,10 @@ __device__ void tlas_build_block(SegSmem& s, const BuildParams& p) {
             s.leafBox[k] = m;
             s.scratch.centre[k] = Float3{(m.max.x + m.min.x) / 2.0f, (m.max.y + m.min.y) / 2.0f, (m.max.z + m.min.z) / 2.0f};
             p.tlasAabbs[k] = m;
-            aabb_grow(mine, m);
+            // the reference's UpdateTLAS drops the per-thread boxes of threads 32..63 (mod 64) from its scene-box reduction
+            // (src/updateGeometry.cuh:313-330 lacks the "merge tid + 32" step of :219-223): batches with k mod 256 >= 128
+            // do not contribute.  Reproduced bit for bit (the Morton codes of the top level depend on it).
+            if ((k & 255) < 128) aabb_grow(mine, m);
         }
     }
     const AABB scene = block_reduce_aabb<NT>(s, mine);

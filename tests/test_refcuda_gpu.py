@@ -1,0 +1,68 @@
+"""GPU parity tests against the REFERENCE'S OWN CUDA kernels (oracle/_ref/librefcuda.so: UpdateSceneGeometry, RadixSort,
+BuildLBVH, UpdateTLAS and TraverseBvh compiled for sm_100 from /root/reference/src by oracle/refcuda/build_ref.py).
+This is what pins the oracle and the product for the bit-exact part of the path: Morton codes, sorted order,
+reorderIdx, BVH topology + boxes, TLAS, and per-ray (triangle id, t, u, v).  Skipped when the prebuilt library is absent."""
+import numpy as np
+import pytest
+
+from helpers import NODE_BOX_FIELDS, NODE_LINK_FIELDS, assert_bvh_equal, assert_hits_equal, read_all_stage1
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ref():
+    from oracle.refcuda import ref as r
+    if not r.available():
+        pytest.skip("oracle/_ref/librefcuda.so not built (needs /root/reference at build time)")
+    return r
+
+
+class _AsOracle:
+    """reference-kernel outputs in the shape helpers.assert_bvh_equal expects from the oracle"""
+
+    def __init__(self, rb, orc, Bp):
+        self.num_tris, self.num_batches, self.num_batches_padded = rb.num_tris, rb.num_batches, Bp
+        self.triangles = rb.host("triangles", orc.TRIANGLE_DTYPE); self.aabbs = rb.host("aabbs", orc.AABB_DTYPE)
+        self.morton = rb.host("morton", np.uint32); self.reorder_idx = rb.host("reorderIdx", np.uint32)
+        self.nodes = rb.host("nodes", orc.BVHNODE_DTYPE)
+        self.tlas_aabbs = rb.host("tlasAabbs", orc.AABB_DTYPE); self.tlas_morton = rb.host("tlasMorton", np.uint32)
+        self.tlas_reorder_idx = rb.host("tlasReorderIdx", np.uint32); self.tlas_nodes = rb.host("tlasNodes", orc.BVHNODE_DTYPE)
+
+
+@pytest.mark.parametrize("quads,seed", [((64, 80), 1), ((128, 256), 3), ((512, 1023), 1)])    # 10 240 / 65 536 / 1 047 552 triangles
+def test_product_and_oracle_match_reference_kernels(pkg, orc, ref, quads, seed):
+    pos, nrm, idx = pkg.scenes.terrain(*quads, seed=seed)
+    rb = ref.build_bvh(pos, nrm, idx)
+    want = _AsOracle(rb, orc, 1024)
+    # --- the CPU oracle against the reference kernels (pins the oracle) ---
+    ob = orc.build_bvh(pos, nrm, idx)
+    for f in ["v1", "v2", "v3", "n1", "n2", "n3"]:
+        np.testing.assert_array_equal(ob.triangles[f], want.triangles[f], err_msg=f"oracle triangles.{f}")
+    np.testing.assert_array_equal(ob.morton, want.morton); np.testing.assert_array_equal(ob.reorder_idx, want.reorder_idx)
+    np.testing.assert_array_equal(ob.tlas_morton, want.tlas_morton); np.testing.assert_array_equal(ob.tlas_reorder_idx, want.tlas_reorder_idx)
+    B = ob.num_batches
+    valid = np.zeros(B * 1024, bool)
+    for b in range(B):
+        valid[b * 1024: b * 1024 + 1023] = True
+    for f in NODE_LINK_FIELDS + NODE_BOX_FIELDS:
+        np.testing.assert_array_equal(ob.nodes[f][valid], want.nodes[f][valid], err_msg=f"oracle bvhNodes.{f}")
+        np.testing.assert_array_equal(ob.tlas_nodes[f][:B - 1], want.tlas_nodes[f][:B - 1], err_msg=f"oracle TLAS nodes.{f}")
+    # --- the product (CUDA, C ABI) against the reference kernels ---
+    cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 256, 192)
+    rays = pkg.scenes.primary_rays(cam, 256, 192)
+    rng = np.random.default_rng(7)                                   # + incoherent rays from points above the terrain
+    extra = np.zeros(20000, rays.dtype)
+    extra["orig"] = np.stack([rng.uniform(-50, 50, 20000), rng.uniform(5, 30, 20000), rng.uniform(-50, 50, 20000)], -1).astype(np.float32)
+    d = rng.normal(size=(20000, 3)).astype(np.float32); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    extra["dir"] = d
+    rays = np.concatenate([rays, extra])
+    with pkg.RayTracer(64, 64) as rt:
+        rt.set_mesh(pos, idx, nrm)
+        rt.build_bvh()
+        assert_bvh_equal(read_all_stage1(rt, pkg), want, pkg)
+        got = rt.traverse(rays)
+    ref_hits, _ = ref.traverse(rb, rays)
+    assert_hits_equal(got, ref_hits)
+    assert_hits_equal(orc.traverse(ob, rays), ref_hits)
+    assert (ref_hits["tri"] >= 0).mean() > 0.2
