@@ -103,7 +103,8 @@ typedef enum rtrt_buffer {
     RTRT_BUF_SKY,                /* float4[512*256]  (SkyBuffer)                                        */
     RTRT_BUF_SKY_CDF,            /* float[512*256]   inclusive luminance CDF                            */
     RTRT_BUF_SUN,                /* float4[32*32]    (SunBuffer)                                        */
-    RTRT_BUF_SUN_CDF             /* float[32*32]                                                        */
+    RTRT_BUF_SUN_CDF,            /* float[32*32]                                                        */
+    RTRT_BUF_ACCUM_RADIANCE      /* float4: sum of colour*albedo over the accumulated samples, .w = count (rtrt_accumulate) */
 } rtrt_buffer;
 
 /* SkyParams (src/settingParams.h:26-46), same defaults. */
@@ -158,6 +159,8 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
  *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
  *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)
+ *   "assume_bvh_valid"    0/1  : mark the BVH arrays as built (they were filled from outside, e.g. an NCCL broadcast from
+ *                                the rank that built them) or as stale
  *   "global_sort"         0/1  : rtrt_build_bvh first sorts the triangles by the 60-bit Morton code of their centroid in the
  *                                mesh bounding box (the offline step of tool/meshProcessor.cpp:146-200, on the device, per
  *                                call); triangle ids reported by the library are then positions in that order
@@ -203,6 +206,10 @@ int rtrt_set_data_dir(rtrt_ctx* ctx, const char* dir);               /* where bl
 int rtrt_pathtrace(rtrt_ctx* ctx);
 /* ---- stage 3: RayTracer::TemporalSpatialDenoising (src/denoising.cu:5-188) ---- */
 int rtrt_denoise(rtrt_ctx* ctx);
+/* ---- progressive mode (BASELINE config 5, N spp): add the remodulated radiance (colour x albedo, the ApplyAlbedo step of
+ *      src/temporalDenoising.cuh:1127-1139 in fp32) of the frame just path traced to RTRT_BUF_ACCUM_RADIANCE, rows of the
+ *      current row range only; reset != 0 starts a new accumulation. ---- */
+int rtrt_accumulate(rtrt_ctx* ctx, int reset);
 /* ---- the three stages in draw() order, then frameNum++ (src/kernel.cu:259-362) ---- */
 int rtrt_render_frame(rtrt_ctx* ctx);
 

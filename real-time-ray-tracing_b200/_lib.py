@@ -17,7 +17,7 @@ STATUS_NAMES = {0: "RTRT_OK", -1: "RTRT_ERR_ARG", -2: "RTRT_ERR_CUDA", -3: "RTRT
 BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES, \
     BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES, BUF_TRI_PERMUTATION = range(12)
 BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCUMULATION_COLOR, BUF_HISTORY_COLOR, \
-    BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF = range(32, 46)
+    BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF, BUF_ACCUM_RADIANCE = range(32, 47)
 
 
 class Config(C.Structure):
@@ -97,6 +97,7 @@ SYMBOLS = {
     "rtrt_pathtrace": (C.c_int, [C.c_void_p]),
     "rtrt_denoise": (C.c_int, [C.c_void_p]),
     "rtrt_render_frame": (C.c_int, [C.c_void_p]),
+    "rtrt_accumulate": (C.c_int, [C.c_void_p, C.c_int]),
 }
 
 _lib = None

@@ -39,7 +39,7 @@ for _b, _dt in ((L.BUF_RENDER_COLOR, COLOR_DTYPE), (L.BUF_NORMAL, np.dtype(("<f2
                 (L.BUF_ACCUMULATION_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_DEPTH, np.dtype("<f2")),
                 (L.BUF_NOISE_LEVEL, np.dtype("<f2")), (L.BUF_NOISE_LEVEL_16, np.dtype("<f2")),
                 (L.BUF_SKY, np.dtype(("<f4", 4))), (L.BUF_SKY_CDF, np.dtype("<f4")), (L.BUF_SUN, np.dtype(("<f4", 4))),
-                (L.BUF_SUN_CDF, np.dtype("<f4"))):
+                (L.BUF_SUN_CDF, np.dtype("<f4")), (L.BUF_ACCUM_RADIANCE, np.dtype(("<f4", 4)))):
     BUFFER_DTYPES[_b] = _dt
 MAT_LAMBERTIAN_DIFFUSE, MAT_PERFECT_REFLECTION, MAT_GLASS, MAT_MICROFACET_REFLECTION, MAT_EMISSIVE, MAT_SKY = range(6)
 
@@ -217,6 +217,10 @@ class RayTracer:
     def denoise(self):
         """TemporalSpatialDenoising (src/denoising.cu:5-188)."""
         self._check(self._lib.rtrt_denoise(self._h))
+
+    def accumulate(self, reset=False):
+        """Progressive mode: add colour x albedo of the last path-traced frame to BUF_ACCUM_RADIANCE (rows of the row range)."""
+        self._check(self._lib.rtrt_accumulate(self._h, int(reset)))
 
     def draw(self):
         """RayTracer::draw for the hot path: BuildBvhLevel1/2 -> PathTrace -> denoise, frameNum++ (src/kernel.cu:259-362)."""

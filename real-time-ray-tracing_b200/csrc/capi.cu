@@ -243,6 +243,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!name) return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: null name");
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 32) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..32"); c.stackSize = (int)value; return RTRT_OK; }
+    if (!strcmp(name, "assume_bvh_valid")) { c.bvhValid = value != 0; return RTRT_OK; }
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
@@ -327,6 +328,7 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         case RTRT_BUF_HISTORY_DEPTH: p = c.dHistoryDepth; b = px * 2; break;
         case RTRT_BUF_NOISE_LEVEL: p = c.dNoise; b = (size_t)((c.gbufW + 7) / 8) * ((c.gbufH + 7) / 8) * 2; break;
         case RTRT_BUF_NOISE_LEVEL_16: p = c.dNoise16; b = (size_t)((c.gbufW + 15) / 16) * ((c.gbufH + 15) / 16) * 2; break;
+        case RTRT_BUF_ACCUM_RADIANCE: p = c.dAccumRadiance; b = px * 16; break;
         case RTRT_BUF_SKY: p = c.dSky; b = sizeof(float) * 4 * kSkySize; break;
         case RTRT_BUF_SKY_CDF: p = c.dSkyCdf; b = sizeof(float) * kSkySize; break;
         case RTRT_BUF_SUN: p = c.dSun; b = sizeof(float) * 4 * kSunSize; break;
@@ -514,6 +516,13 @@ int rtrt_denoise(rtrt_ctx* ctx) {
     RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_DENOISE][1], c.stream));
     c.evPending[STAGE_DENOISE] = true;
     return RTRT_OK;
+}
+
+int rtrt_accumulate(rtrt_ctx* ctx, int reset) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    return launch_accumulate(c, reset);
 }
 
 int rtrt_render_frame(rtrt_ctx* ctx) {

@@ -63,6 +63,7 @@ struct Context {
     void* dAccum = nullptr; void* dHistoryColor = nullptr; void* dHistoryDepth = nullptr; void* dHistoryAlbedo = nullptr;
     void* dNoise = nullptr; void* dNoise16 = nullptr; void* dColorTmp = nullptr; void* dGuide = nullptr;
     int gbufW = 0, gbufH = 0;
+    void* dAccumRadiance = nullptr; size_t accumRadiancePx = 0;      // progressive fp32 accumulation (rtrt_accumulate)
     unsigned long long* dRayCounter = nullptr;
     rtrt_denoise_params denoiseParams{}; rtrt_pass_settings passSettings{};
 
@@ -97,6 +98,7 @@ int launch_presort(Context& c);             // bvh_presort.cu
 int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int anyHit, unsigned long long* dCounters);
 int launch_pathtrace(Context& c);
 int launch_denoise(Context& c);
+int launch_accumulate(Context& c, int reset);
 int ensure_frame_resources(Context& c);      // frame.cu: G-buffers, tables, default materials/textures, sky regeneration
 void free_frame_resources(Context& c);
 int set_texture(Context& c, int slot, int w, int h, const uint16_t* rgba);

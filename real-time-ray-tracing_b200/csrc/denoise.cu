@@ -394,6 +394,39 @@ __global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort
 }
 
 // -------------------------------------------------------------------------------------------------------------------
+// Progressive accumulation (BASELINE config 5: N spp without the denoiser): sum += colour * albedo of the frame just path
+// traced (the remodulation of ApplyAlbedo, src/temporalDenoising.cuh:1127-1139, in fp32), sample count in .w; rows
+// [rowBegin, rowEnd) only, so row-sharded GPUs accumulate their own band.
+// -------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_accumulate(const ushort4* __restrict__ color, const ushort4* __restrict__ albedo, float4* __restrict__ acc,
+                                                    size_t begin, size_t end, int reset) {
+    const size_t i = begin + (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= end) return;
+    const Float3 c = px_rgb(__ldg(color + i)) * px_rgb(__ldg(albedo + i));
+    float4 a = reset ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : acc[i];
+    a.x += c.x; a.y += c.y; a.z += c.z; a.w += 1.0f;
+    acc[i] = a;
+}
+
+int launch_accumulate(Context& c, int reset) {
+    if (!c.dColor || c.gbufW != c.width || c.gbufH != c.height) return c.fail(RTRT_ERR_STATE, "rtrt_accumulate: no path-traced frame");
+    const size_t px = (size_t)c.width * c.height;
+    if (!c.dAccumRadiance || c.accumRadiancePx != px) {
+        if (c.dAccumRadiance) cudaFree(c.dAccumRadiance);
+        c.dAccumRadiance = nullptr; c.accumRadiancePx = 0;
+        RTRT_CUDA(c, cudaMalloc(&c.dAccumRadiance, px * sizeof(float4)));
+        RTRT_CUDA(c, cudaMemsetAsync(c.dAccumRadiance, 0, px * sizeof(float4), c.stream));
+        c.accumRadiancePx = px;
+    }
+    const size_t begin = (size_t)c.rowBegin * c.width, end = (size_t)c.rowEnd * c.width;
+    k_accumulate<<<(unsigned)((end - begin + 255) / 256), 256, 0, c.stream>>>(reinterpret_cast<const ushort4*>(c.dColor), reinterpret_cast<const ushort4*>(c.dAlbedo),
+                                                                             reinterpret_cast<float4*>(c.dAccumRadiance), begin, end, reset);
+    c.launches++;
+    RTRT_CUDA(c, cudaGetLastError());
+    return RTRT_OK;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
 int launch_denoise(Context& c) {
     if (!c.dColor || c.gbufW != c.width || c.gbufH != c.height) return c.fail(RTRT_ERR_STATE, "rtrt_denoise: no path-traced frame to denoise");
     DnParams P{};

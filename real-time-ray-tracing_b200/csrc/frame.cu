@@ -212,6 +212,7 @@ static void free_gbuffers(Context& c) {
     void** bufs[] = {&c.dColor, &c.dNormal, &c.dAlbedo, &c.dDepth, &c.dMotion, &c.dAccum, &c.dHistoryColor, &c.dHistoryDepth,
                      &c.dHistoryAlbedo, &c.dNoise, &c.dNoise16, &c.dColorTmp, &c.dGuide};
     for (void** b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
+    if (c.dAccumRadiance) { cudaFree(c.dAccumRadiance); c.dAccumRadiance = nullptr; c.accumRadiancePx = 0; }
     c.gbufW = c.gbufH = 0;
 }
 
