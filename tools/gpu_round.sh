@@ -16,7 +16,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu1.log 2>&1
 echo "ncu launches exit $?"
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_pathtrace|k_build_blas|k_dn_' -s 16 -c 8 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_pt_|k_pathtrace|k_build_blas|k_dn_' -s 30 -c 14 \
     -o $OUT/${TAG}_prof -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu2.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT | tail -20
