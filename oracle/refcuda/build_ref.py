@@ -26,8 +26,13 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("RTRT_REFERENCE", "/root/reference")
 OUT_DIR = os.path.join(os.path.dirname(HERE), "_ref")
 
-HEADERS = ["linearMath.h", "geometry.h", "geometry.cuh", "bvhNode.cuh", "precision.cuh", "debugUtil.h", "updateGeometry.cuh",
-           "radixSort.cuh", "buildBVH.cuh", "traverse.h", "blueNoiseRandGen.h", "blueNoiseRandGenData.h", "cudaError.cuh"]
+# every header of src/ is staged (the stage-2/3 kernels include most of them through kernel.cuh); .cu/.cpp files are not
+SKIP_HEADERS = {"timer.h"}      # replaced by a declaration-only stub (std::chrono code that libstdc++ rejects; not on the path)
+TIMER_STUB = """#pragma once
+#include <string>
+struct Timer { void init() {} void update() {} void updateWithLimiter(float) {} float getDeltaTime() { return 0.0f; } float getTime() { return 0.0f; }
+               static std::string getTimeString() { return std::string(); } unsigned int fps = 0; };
+"""
 
 # POD proxies: same bytes as Float2/Float3, no constructors (so they may live in an anonymous struct), convertible.
 PROXIES = r'''
@@ -83,6 +88,18 @@ def patch_geometry_h(t):
     return t
 
 
+def patch_fp16(t):
+    # union ctor that initialises two overlapping members (MSVC extension); the two-argument form is never called on the path
+    return sub1(t, r": hf3\{v\}, hf1\{v2\} \{\}", ": hf3{v} { (void)v2; }", "ushort4ToHalf3Converter ctor")
+
+
+def patch_temporal(t):
+    # brace-initialiser narrowing int -> ushort in TemporalFilter2 (accepted by MSVC, an error for EDG): explicit conversion
+    if "{ outColor, maskValue }" not in t:
+        raise RuntimeError("patch did not apply: TemporalFilter2 narrowing")
+    return t.replace("{ outColor, maskValue }", "{ outColor, (ushort)maskValue }")
+
+
 def main():
     fmad = "false"
     if "--fmad" in sys.argv:
@@ -94,16 +111,20 @@ def main():
     os.makedirs(OUT_DIR, exist_ok=True)
     tmp = tempfile.mkdtemp(prefix="refcuda_")
     try:
-        for h in HEADERS:
-            shutil.copy(os.path.join(REF, "src", h), os.path.join(tmp, h))
-        for name, fn in (("linearMath.h", patch_linear_math), ("geometry.h", patch_geometry_h)):
+        for h in sorted(os.listdir(os.path.join(REF, "src"))):
+            if h.endswith((".h", ".cuh")) and h not in SKIP_HEADERS:
+                shutil.copy(os.path.join(REF, "src", h), os.path.join(tmp, h))
+        open(os.path.join(tmp, "timer.h"), "w").write(TIMER_STUB)
+        for name, fn in (("linearMath.h", patch_linear_math), ("geometry.h", patch_geometry_h), ("fp16Utils.cuh", patch_fp16),
+                         ("temporalDenoising.cuh", patch_temporal)):
             p = os.path.join(tmp, name)
             src = open(p, encoding="utf-8", errors="replace").read()
             os.chmod(p, 0o644)
             open(p, "w").write(fn(src))
         out = os.path.join(OUT_DIR, "librefcuda.so" if fmad == "false" else "librefcuda_fmad.so")
         cmd = ["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100,code=sm_100", "-O3", "-lineinfo", f"--fmad={fmad}", "-std=c++17",
-               "-Xcompiler", "-fPIC", "-Xcompiler", "-w", "-w", "-shared", "-I", tmp, os.path.join(HERE, "harness.cu"), "-o", out, "-lcudart"]
+               "-Xcompiler", "-fPIC", "-Xcompiler", "-w", "-w", "-shared", "-I", tmp, "-I", os.path.join(REF, "ext", "cuda-samples", "Common"),
+               os.path.join(HERE, "harness.cu"), os.path.join(HERE, "harness_frame.cu"), "-o", out, "-lcudart"]
         print(" ".join(cmd), flush=True)
         subprocess.check_call(cmd)
         print("built", out)

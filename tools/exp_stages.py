@@ -43,6 +43,25 @@ try:
         out["ref_build_ms"] = rb.ms
         _, ms = ref.traverse(rb, rays, iterations=6)
         out["ref_traverse_primary_ms"] = ms; out["ref_primary_mrays_s"] = rays.shape[0] / ms / 1e3
+        if hasattr(ref.load(), "refcuda_frame_create"):
+            from oracle import orc
+            orc.build()
+            for fm in ([False, True] if ref.available(fmad=True) else [False]):
+                tag = "ref_fmad_" if fm else "ref_"
+                rbf = ref.build_bvh(pos, nrm, idx, fmad=fm)
+                with ref.RefFrame(W, H, fmad=fm) as rf:
+                    sky = orc.Sky(); sky.sky = rt.read_buffer(pkg.BUF_SKY); sky.sky_cdf = rt.read_buffer(pkg.BUF_SKY_CDF)
+                    sky.sun = rt.read_buffer(pkg.BUF_SUN); sky.sun_cdf = rt.read_buffer(pkg.BUF_SUN_CDF); sky.sun_dir, sky.cos_theta_max = rt.get_sun()
+                    rf.set_tables(orc.load_tables()[0]); rf.set_scene(rbf)
+                    rf.set_materials(orc.default_materials(), np.full(rbf.num_batches * 1024, 3, np.int32))
+                    rf.set_texture(0, orc.mip_chain(orc.DEFAULT_TEX[0])); rf.set_texture(1, orc.mip_chain(orc.DEFAULT_TEX[1])); rf.set_sky(sky)
+                    out[tag + "pathtrace_ms"] = rf.pathtrace(cam, 2, iterations=6)
+                    out[tag + "pathtrace_mrays_s"] = out["rays"] / out[tag + "pathtrace_ms"] / 1e3
+                    dn_ms = []
+                    for fr in range(1, 7):
+                        rf.pathtrace(cam, fr)
+                        dn_ms.append(rf.denoise(fr))
+                    out[tag + "denoise_ms"] = float(np.median(dn_ms[2:]))
         if ref.available(fmad=True):
             rb2 = ref.build_bvh(pos, nrm, idx, iterations=6, fmad=True)
             _, ms2 = ref.traverse(rb2, rays, iterations=6, fmad=True)
