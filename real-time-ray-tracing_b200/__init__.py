@@ -10,6 +10,8 @@ from .api import (RayTracer, RtrtError, load_config, config_defaults, TRIANGLE_D
                   RAY_DTYPE, HIT_DTYPE, RAY_MAX, MATERIAL_DTYPE, COLOR_DTYPE)  # noqa: F401
 from ._lib import *  # noqa: F401,F403  (BUF_* ids, ctypes structs)
 from . import scenes  # noqa: F401
+from . import parallel  # noqa: F401
+from .parallel import RowShardedRayTracer, row_bands  # noqa: F401
 from ._lib import (BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_BVH_NODES,
                    BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX,
                    BUF_TLAS_BVH_NODES, BUF_TRI_PERMUTATION)  # noqa: F401

@@ -20,6 +20,7 @@ namespace rtrt {
 
 struct DnParams {
     int W, H, frameNum;
+    int by0;                                  // first 16-row block row this launch covers (row-band mode; 0 = whole frame)
     float local_n, local_d, local_m, large_n, large_d, large_m, temp_n, temp_d, temp_m, thr_local, thr_large;
     const ushort4* __restrict__ normal; const __half* __restrict__ depth; const __half2* __restrict__ motion;
     const ushort4* __restrict__ albedo;
@@ -79,13 +80,13 @@ __device__ __forceinline__ void block_noise_levels(const DnParams& P, const usho
     const int warp = tid >> 5, lane = tid & 31;
     const int gw = (P.W + 7) / 8, gh = (P.H + 7) / 8;
     if (warp < 4) {
-        const int t8x = blockIdx.x * 2 + (warp & 1), t8y = blockIdx.y * 2 + (warp >> 1);
+        const int t8x = blockIdx.x * 2 + (warp & 1), t8y = (blockIdx.y + P.by0) * 2 + (warp >> 1);
         const int tx = lane & 7, ty = lane >> 3;
         float l1, l2, b1, b2;
         {
             // pixel coordinates are clamped to the image like the surface reads, then made block-local
             const int gx = min(t8x * 8 + tx, P.W - 1) - blockIdx.x * 16;
-            const int gy1 = min(t8y * 8 + 2 * ty, P.H - 1) - blockIdx.y * 16, gy2 = min(t8y * 8 + 2 * ty + 1, P.H - 1) - blockIdx.y * 16;
+            const int gy1 = min(t8y * 8 + 2 * ty, P.H - 1) - (blockIdx.y + P.by0) * 16, gy2 = min(t8y * 8 + 2 * ty + 1, P.H - 1) - (blockIdx.y + P.by0) * 16;
             const bool in = gx >= 0 && gx < 16 && gy1 >= 0 && gy1 < 16 && gy2 >= 0 && gy2 < 16;   // false only for tiles fully outside the image
             const ushort4 p1 = in ? sOut[gy1 * 16 + gx] : make_ushort4(0, 0, 0, 0), p2 = in ? sOut[gy2 * 16 + gx] : make_ushort4(0, 0, 0, 0);
             l1 = getmax3(px_rgb(p1)); l2 = getmax3(px_rgb(p2));
@@ -113,9 +114,9 @@ __device__ __forceinline__ void block_noise_levels(const DnParams& P, const usho
     __syncthreads();
     if (tid == 0) {
         // tiles beyond the 8x8 grid read the clamped (= last valid) tile, like the surface read in :97-100
-        const bool xo = blockIdx.x * 2 + 1 >= gw, yo = blockIdx.y * 2 + 1 >= gh;
+        const bool xo = blockIdx.x * 2 + 1 >= gw, yo = (blockIdx.y + P.by0) * 2 + 1 >= gh;
         const float v1 = sN8[0], v2 = sN8[xo ? 0 : 1], v3 = sN8[yo ? 0 : 2], v4 = sN8[(yo ? 0 : 2) + (xo ? 0 : 1)];
-        P.noise16[(size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x] = __float2half_rn((v1 + v2 + v3 + v4) / 4);
+        P.noise16[(size_t)(blockIdx.y + P.by0) * ((P.W + 15) / 16) + blockIdx.x] = __float2half_rn((v1 + v2 + v3 + v4) / 4);
     }
 }
 
@@ -140,9 +141,9 @@ VD float bilateral_weight(Float3 n0, Float3 n1, float d0, float d1, bool maskDif
 // -------------------------------------------------------------------------------------------------------------------
 // Guide pack: normal.xyz (half) + depth (half) -> one 8-byte texel, so every later tap costs one guide load, not two.
 // -------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict__ normal, const __half* __restrict__ depth, ushort4* __restrict__ guide, size_t n) {
-    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= n) return;
+__global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict__ normal, const __half* __restrict__ depth, ushort4* __restrict__ guide, size_t first, size_t n) {
+    const size_t i = first + (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= first + n) return;
     ushort4 g = __ldg(normal + i);
     g.w = __half_as_ushort(__ldg(depth + i));
     guide[i] = g;
@@ -160,7 +161,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
     __shared__ unsigned short sDepth[256];
     __shared__ float sN8[4];
     const int tid = threadIdx.y * 16 + threadIdx.x;
-    const int x0 = blockIdx.x * 16 - 1, y0 = blockIdx.y * 16 - 1;
+    const int x0 = blockIdx.x * 16 - 1, y0 = (blockIdx.y + P.by0) * 16 - 1;
     for (int i = tid; i < T * T; i += 256) {
         const int gx = clampi(x0 + i % T, 0, P.W - 1), gy = clampi(y0 + i / T, 0, P.H - 1);
         const size_t g = (size_t)gy * P.W + gx;
@@ -168,7 +169,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
         sG[i] = __ldg(P.guide + g);
     }
     __syncthreads();
-    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
     const int ci = (threadIdx.y + 1) * T + threadIdx.x + 1;
     ushort4 result = sC[ci];
     const ushort4 cg = sG[ci];
@@ -236,9 +237,9 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
     __shared__ unsigned short sDepth[256];
     __shared__ float sN8[4];
     const int tid = threadIdx.y * 16 + threadIdx.x;
-    const int x0 = blockIdx.x * 16 - 3, y0 = blockIdx.y * 16 - 3;
+    const int x0 = blockIdx.x * 16 - 3, y0 = (blockIdx.y + P.by0) * 16 - 3;
     bool active = FILTER;
-    if (FILTER) active = !(__half2float(__ldg(gate16 + (size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_local);
+    if (FILTER) active = !(__half2float(__ldg(gate16 + (size_t)(blockIdx.y + P.by0) * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_local);
     const int lo = active ? 0 : 3, hi = active ? T : T - 3;          // gated tiles only need their own 16x16 pixels
     for (int i = tid; i < T * T; i += 256) {
         const int lx = i % T, ly = i / T;
@@ -249,7 +250,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
         sG[i] = __ldg(P.guide + g);
     }
     __syncthreads();
-    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
     const int ci = (threadIdx.y + 3) * T + threadIdx.x + 3;
     ushort4 result = sC[ci];
     const ushort4 cg = sG[ci];
@@ -292,11 +293,11 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
 // -------------------------------------------------------------------------------------------------------------------
 template <int S>
 __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, const __half* __restrict__ gate16) {
-    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
     if (x >= P.W || y >= P.H) return;
     const size_t c = (size_t)y * P.W + x;
     ushort4 result = __ldg(in + c);
-    const bool active = !(__half2float(__ldg(gate16 + (size_t)blockIdx.y * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_large);
+    const bool active = !(__half2float(__ldg(gate16 + (size_t)(blockIdx.y + P.by0) * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_large);
     if (active) {
         const ushort4 cg = __ldg(P.guide + c);
         const Float3 normalValue = px_rgb(cg);
@@ -337,7 +338,7 @@ __global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort
     constexpr int T = 18;
     __shared__ Float3 sY[T * T];
     const int tid = threadIdx.y * 16 + threadIdx.x;
-    const int x = blockIdx.x * 16 + threadIdx.x, y = blockIdx.y * 16 + threadIdx.y;
+    const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
     const unsigned short kOne = 0x3C00;                                   // half(1.0): what ApplyAlbedo leaves in the mask channel
     auto remodulated = [&](int gx, int gy) {
         const size_t g = (size_t)clampi(gy, 0, P.H - 1) * P.W + clampi(gx, 0, P.W - 1);
@@ -346,7 +347,7 @@ __global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort
     };
     ushort4 result;
     if (TF2) {
-        const int x0 = blockIdx.x * 16 - 1, y0 = blockIdx.y * 16 - 1;
+        const int x0 = blockIdx.x * 16 - 1, y0 = (blockIdx.y + P.by0) * 16 - 1;
         for (int i = tid; i < T * T; i += 256) sY[i] = rgb_to_ycocg(px_rgb(remodulated(x0 + i % T, y0 + i / T)));
         __syncthreads();
         if (x >= P.W || y >= P.H) return;
@@ -443,7 +444,19 @@ int launch_denoise(Context& c) {
     const rtrt_pass_settings& ps = c.passSettings;
     const bool temporal = ps.enableTemporalDenoising != 0, local = ps.enableLocalSpatialFilter != 0, wide = ps.enableWideSpatialFilter != 0,
                tf2 = ps.enableTemporalDenoising2 != 0, notFirst = c.frameNum != 1;
-    const dim3 grid((c.width + 15) / 16, (c.height + 15) / 16), block(16, 16);
+    // Row-band mode (multi-GPU, rtrt_set_row_range): only the 16-row block rows that can influence rows [rowBegin, rowEnd) are
+    // filtered.  Dependency reach of the band through the passes, walking backwards: TemporalFilter2 1 row, the dilated 5x5
+    // passes 24 + 12 + 6, their 16x16 noise gate (tile-aligned, so up to 15 more rows of SpatialFilter7x7 output), 7x7: 3,
+    // its own gate 15, TemporalFilter 1  => 77 rows; kBandHalo = 80 = five block rows.  Every pass covers the same block rows:
+    // what the outer halo rows compute from rows outside is garbage by construction and never reaches the band.
+    // The caller must have made ALL rows of the G-buffers and history valid first (all-gather of the bands).
+    constexpr int kBandHalo = 80;
+    const int blocksY = (c.height + 15) / 16;
+    const bool band = c.rowBegin > 0 || c.rowEnd < c.height;
+    const int by0 = band ? (c.rowBegin - kBandHalo < 0 ? 0 : (c.rowBegin - kBandHalo) / 16) : 0;
+    const int by1 = band ? (c.rowEnd + kBandHalo + 15) / 16 < blocksY ? (c.rowEnd + kBandHalo + 15) / 16 : blocksY : blocksY;
+    P.by0 = by0;
+    const dim3 grid((c.width + 15) / 16, by1 - by0), block(16, 16);
     ushort4* cur = reinterpret_cast<ushort4*>(c.dColor); ushort4* oth = reinterpret_cast<ushort4*>(c.dColorTmp);
     ushort4* accum = reinterpret_cast<ushort4*>(c.dAccum);
     const __half* n16 = reinterpret_cast<const __half*>(c.dNoise16);
@@ -451,8 +464,10 @@ int launch_denoise(Context& c) {
     const size_t bytes = (size_t)c.width * c.height * sizeof(ushort4);
 
     {
-        const size_t n = (size_t)c.width * c.height;
-        k_dn_pack_guide<<<(unsigned)((n + 255) / 256), 256, 0, c.stream>>>(P.normal, P.depth, reinterpret_cast<ushort4*>(c.dGuide), n);
+        // guide rows: the filtered block rows + the 24-row reach of the widest dilated pass
+        const int g0 = by0 * 16 - 24 < 0 ? 0 : by0 * 16 - 24, g1 = by1 * 16 + 24 > c.height ? c.height : by1 * 16 + 24;
+        const size_t first = (size_t)g0 * c.width, n = (size_t)(g1 - g0) * c.width;
+        k_dn_pack_guide<<<(unsigned)((n + 255) / 256), 256, 0, c.stream>>>(P.normal, P.depth, reinterpret_cast<ushort4*>(c.dGuide), first, n);
         c.launches++;
     }
     // TemporalFilter (src/denoising.cu:49-64) [+ noise level of its output, :68-76]
@@ -473,6 +488,7 @@ int launch_denoise(Context& c) {
     if (tf2 && notFirst) k_dn_final<true><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, histNext, reinterpret_cast<__half*>(c.dHistoryDepth));
     else k_dn_final<false><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, tf2 ? histNext : nullptr, reinterpret_cast<__half*>(c.dHistoryDepth));
     swap(); c.launches++;
+    if (band && tf2) RTRT_CUDA(c, cudaMemcpyAsync(c.dHistoryDepth, c.dDepth, (size_t)c.width * c.height * sizeof(__half), cudaMemcpyDeviceToDevice, c.stream));
     if (tf2) { void* t = c.dHistoryColor; c.dHistoryColor = c.dHistoryAlbedo; c.dHistoryAlbedo = t; }       // history ping-pong
     (void)bytes;
     c.dColor = cur; c.dColorTmp = oth;          // RTRT_BUF_RENDER_COLOR now names the denoised frame

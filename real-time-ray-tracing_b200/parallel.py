@@ -1,0 +1,154 @@
+"""Multi-GPU host logic: one process and one RayTracer context per GPU, torch.distributed for the plumbing.
+
+The path shards by IMAGE ROWS.  Rank r owns the contiguous band rows [H*r/N, H*(r+1)/N) of every frame:
+
+    build      every rank rebuilds the whole BVH redundantly (no communication), or rank 0 builds and the three traversal
+               arrays (Triangle[], BVHNode[], TLAS BVHNode[]) are broadcast over NVLink — `bvh="rebuild" | "broadcast"`.
+    pathtrace  each rank traces its band (rtrt_set_row_range).
+    exchange   all-gather of the five G-buffers by rows (colour+mask 8, normal 8, albedo 8, depth 2, motion 4 = 30 B/px),
+               so every rank holds the whole frame's denoiser inputs.
+    denoise    each rank filters its band plus the 80-row dependency halo (csrc/denoise.cu, launch_denoise): the halo is
+               recomputed instead of exchanged pass by pass, so there is no collective inside the denoiser.
+    gather     all-gather of the band's denoised colour (the frame buffer), history colour and accumulation colour — what the
+               next frame's temporal filters re-project from.
+
+Progressive mode (BASELINE config 5): each rank accumulates N samples of its band in fp32 (rtrt_accumulate) and the bands are
+gathered once at the end (16 B/px).
+
+Everything here works on byte tensors and a process group, so the same code runs over NCCL on device buffers and over gloo
+on CPU tensors (tests/test_parallel_cpu.py drives it with world_size 2 on the CPU).
+"""
+import numpy as np
+
+from . import _lib as L
+
+
+def row_bands(height, world):
+    """Contiguous row bands, one per rank: [(begin, end), ...]; every row belongs to exactly one band."""
+    if world < 1 or height < world:
+        raise ValueError(f"cannot split {height} rows over {world} ranks")
+    return [(height * r // world, height * (r + 1) // world) for r in range(world)]
+
+
+def all_gather_rows(buf, row_bytes, bands, rank, group=None):
+    """In-place all-gather of a row-major full-frame byte tensor `buf` (uint8, H*row_bytes): on entry rank r's rows
+    bands[r] are valid, on return all rows are.  Equal bands -> one all_gather_into_tensor (in place: NCCL recognises the
+    input as a slice of the output); ragged bands -> one broadcast per rank."""
+    import torch.distributed as dist
+    world = len(bands)
+    if world == 1:
+        return
+    sizes = {e - b for b, e in bands}
+    if len(sizes) == 1:
+        b, e = bands[rank]
+        mine = buf[b * row_bytes: e * row_bytes]
+        dist.all_gather_into_tensor(buf[: bands[-1][1] * row_bytes], mine if buf.is_cuda else mine.clone(), group=group)
+    else:
+        for r, (b, e) in enumerate(bands):
+            dist.broadcast(buf[b * row_bytes: e * row_bytes], src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+
+
+class _DevBytes:
+    """A borrowed device buffer as a __cuda_array_interface__ object (so torch / NCCL can address it)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+# (buffer id, bytes per pixel)
+GBUFFERS = [(L.BUF_RENDER_COLOR, 8), (L.BUF_NORMAL, 8), (L.BUF_ALBEDO, 8), (L.BUF_DEPTH, 2), (L.BUF_MOTION_VECTOR, 4)]
+DENOISED = [(L.BUF_RENDER_COLOR, 8), (L.BUF_HISTORY_COLOR, 8), (L.BUF_ACCUMULATION_COLOR, 8)]
+BVH_ARRAYS = [L.BUF_TRIANGLES, L.BUF_BVH_NODES, L.BUF_TLAS_BVH_NODES]
+
+
+class RowShardedRayTracer:
+    """Drives one RayTracer context as rank `rank` of `world` row-sharded GPUs.  Collectives run on the context's stream."""
+
+    def __init__(self, rt, width, height, rank, world, bvh="rebuild", group=None):
+        if bvh not in ("rebuild", "broadcast"):
+            raise ValueError("bvh must be 'rebuild' or 'broadcast'")
+        self.rt, self.W, self.H, self.rank, self.world, self.bvh, self.group = rt, width, height, rank, world, bvh, group
+        self.bands = row_bands(height, world)
+        rt.set_row_range(*self.bands[rank])
+        self._stream = None
+
+    @property
+    def band(self):
+        return self.bands[self.rank]
+
+    def _on_stream(self):
+        import torch
+        if self._stream is None:
+            self._stream = torch.cuda.ExternalStream(self.rt.stream)
+        return torch.cuda.stream(self._stream)
+
+    def _tensor(self, which):
+        import torch
+        ptr, nbytes = self.rt.get_buffer(which)
+        return torch.as_tensor(_DevBytes(ptr, nbytes), device="cuda")
+
+    def _gather(self, bufs):
+        if self.world == 1:
+            return
+        with self._on_stream():
+            for which, bpp in bufs:
+                all_gather_rows(self._tensor(which), self.W * bpp, self.bands, self.rank, self.group)
+
+    # -- stages -------------------------------------------------------------------------------------------------------
+    def build_bvh(self):
+        """Rebuild on every rank, or build on rank 0 and broadcast the traversal arrays."""
+        import torch.distributed as dist
+        if self.bvh == "rebuild" or self.world == 1:
+            self.rt.build_bvh()
+            return
+        if self.rank == 0:
+            self.rt.build_bvh()
+        with self._on_stream():
+            for which in BVH_ARRAYS:
+                dist.broadcast(self._tensor(which), src=0, group=self.group)
+        if self.rank != 0:
+            self.rt.set_option("assume_bvh_valid", 1)
+
+    def pathtrace(self):
+        self.rt.pathtrace()
+
+    def exchange_gbuffers(self):
+        self._gather(GBUFFERS)
+
+    def denoise(self):
+        self.rt.denoise()
+
+    def gather_frame(self):
+        self._gather(DENOISED)
+
+    def draw(self, frame_number=None):
+        """One frame of RayTracer::draw, row-sharded; on return RTRT_BUF_RENDER_COLOR holds the whole denoised frame on
+        every rank and the history buffers are complete for the next frame."""
+        if frame_number is not None:
+            self.rt.set_frame_number(frame_number)
+        self.build_bvh()
+        self.pathtrace()
+        self.exchange_gbuffers()
+        self.denoise()
+        self.gather_frame()
+
+    # -- progressive mode (BASELINE config 5) ---------------------------------------------------------------------------
+    def render_progressive(self, spp, first_frame=1, rebuild_every_sample=False):
+        """spp path-traced samples of this rank's band accumulated in fp32, then ONE gather of the accumulation buffer.
+        Returns nothing; read RTRT_BUF_ACCUM_RADIANCE (sum in .xyz, sample count in .w)."""
+        self.build_bvh()
+        for s in range(spp):
+            if rebuild_every_sample and s:
+                self.build_bvh()
+            self.rt.set_frame_number(first_frame + s)
+            self.rt.pathtrace()
+            self.rt.accumulate(reset=(s == 0))
+        self._gather([(L.BUF_ACCUM_RADIANCE, 16)])
+
+
+def assemble_rows(parts, bands, row_items):
+    """Host-side twin of the gather: stitch per-rank arrays (each full-frame sized, valid only on its band) into one."""
+    out = np.array(parts[0], copy=True)
+    for p, (b, e) in zip(parts, bands):
+        out[b * row_items: e * row_items] = p[b * row_items: e * row_items]
+    return out

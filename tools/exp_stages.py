@@ -37,6 +37,7 @@ out["denoise_ms"] = timeit(dn)
 out["pathtrace_mrays_s"] = out["rays"] / out["pathtrace_ms"] / 1e3
 out["primary_mrays_s"] = rays.shape[0] / out["traverse_primary_ms"] / 1e3
 try:
+    if os.environ.get("NOREF"): raise ImportError("skipped")
     from oracle.refcuda import ref
     if ref.available() and idx.shape[0] < 1023 * 1024 + 1:
         rb = ref.build_bvh(pos, nrm, idx, iterations=6)
@@ -66,6 +67,8 @@ try:
             rb2 = ref.build_bvh(pos, nrm, idx, iterations=6, fmad=True)
             _, ms2 = ref.traverse(rb2, rays, iterations=6, fmad=True)
             out["ref_fmad_build_ms"] = rb2.ms; out["ref_fmad_primary_mrays_s"] = rays.shape[0] / ms2 / 1e3
+except ImportError:
+    pass
 except Exception as e:
     out["ref_error"] = repr(e)
 print(json.dumps(out))
