@@ -13,7 +13,12 @@ terrain at 1920x1080, 1 spp:
 N > 1    : one process per GPU, the frame is partitioned BY SAMPLE (north_star: "by tile or by sample"): every rank
            renders the same view with its own sample index (frame number), BVH rebuilt redundantly per GPU, and the
            denoised frames are averaged with one NCCL all-reduce (the framebuffer combine) inside the timed region
-           -> per-GPU work fixed -> "scaling": "weak".  `--mode rows` shards ONE frame by row bands instead (strong).
+           -> per-GPU work fixed -> "scaling": "weak".
+           `--mode rows` shards ONE frame by row bands instead (strong scaling; parallel.RowShardedRayTracer: band path
+           trace, NCCL all-gather of the G-buffers, band + halo denoise, NCCL gather of the frame); `--bvh broadcast` builds
+           the BVH on rank 0 and broadcasts it instead of rebuilding it on every GPU.
+`--workload C5` : BASELINE config 5 — 3840x2160, 64 spp progressive (no denoiser), 16 777 216-triangle terrain, row bands,
+           one gather of the fp32 accumulation buffer per step (always `--mode rows`).
 `--impl reference` : the reference has no CPU path and does not build on Linux; this tier's reference arm times the CPU
            oracle (oracle/, multithreaded C++ restatement) with all host threads on a bounded sample of the workload.
 """
@@ -36,6 +41,7 @@ WIDTH, HEIGHT = 1920, 1080
 SCENE = "C2ref"
 WORKLOAD = ("C2: 1080p 1 spp frame, 1 047 552-tri procedural terrain (1023 batches), per-frame two-level LBVH rebuild + "
             "path trace (blue noise, Lambert BSDF + MIS, sky/sun) + temporal/a-trous denoise")
+C5_SPP = 64
 CAMERA = dict(pos=(0, 30, -60), yaw=0.0, pitch=-0.4)
 BUILD_BYTES_PER_TRI = 248          # SURVEY.md §8(d) / BASELINE.md §4 / DESIGN.md
 DENOISE_BYTES_PER_PX = 252         # reference pass sequence; fused lower bound 74
@@ -175,6 +181,106 @@ class DevView:
                                          "strides": None}
 
 
+def reference_kernels(pkg, rt, pos, nrm, idx, cam, rays_per_frame):
+    """The reference's own CUDA kernels (oracle/_ref/librefcuda.so, built for sm_100 from /root/reference by oracle/refcuda/build_ref.py)
+    timed on this GPU on the same scene: the baseline north_star asks to report next to the CPU one.  Baseline leg only."""
+    try:
+        from oracle.refcuda import ref
+        from oracle import orc
+        if not ref.available() or not hasattr(ref.load(), "refcuda_frame_create") or idx.shape[0] >= 1023 * 1024 + 1:
+            return {"unavailable": "oracle/_ref/librefcuda.so not present (or scene above the reference's 1023-batch limit)"}
+        orc.build()
+        rb = ref.build_bvh(pos, nrm, idx, iterations=6)
+        out = {"build_ms": rb.ms, "flags": "-arch=sm_100 --fmad=false", "what": "UpdateSceneGeometry+RadixSort+BuildLBVH+UpdateTLAS+RadixSort+BuildLBVH | PathTrace | "
+               "TemporalSpatialDenoising kernel sequence; CUDA events, no per-stage device sync"}
+        with ref.RefFrame(WIDTH, HEIGHT) as rf:
+            sky = orc.Sky(); sky.sky = rt.read_buffer(pkg.BUF_SKY); sky.sky_cdf = rt.read_buffer(pkg.BUF_SKY_CDF)
+            sky.sun = rt.read_buffer(pkg.BUF_SUN); sky.sun_cdf = rt.read_buffer(pkg.BUF_SUN_CDF); sky.sun_dir, sky.cos_theta_max = rt.get_sun()
+            rf.set_tables(orc.load_tables()[0]); rf.set_scene(rb)
+            rf.set_materials(orc.default_materials(), np.full(rb.num_batches * 1024, 3, np.int32))
+            rf.set_texture(0, orc.mip_chain(orc.DEFAULT_TEX[0])); rf.set_texture(1, orc.mip_chain(orc.DEFAULT_TEX[1])); rf.set_sky(sky)
+            out["pathtrace_ms"] = rf.pathtrace(cam, 2, iterations=6)
+            dn = []
+            for fr in range(1, 7):
+                rf.pathtrace(cam, fr)
+                dn.append(rf.denoise(fr))
+            out["denoise_ms"] = float(np.median(dn[2:]))
+        out["frame_ms"] = out["build_ms"] + out["pathtrace_ms"] + out["denoise_ms"]
+        out["mrays_s"] = rays_per_frame / (out["frame_ms"] * 1e-3) / 1e6
+        out["pathtrace_mrays_s"] = rays_per_frame / (out["pathtrace_ms"] * 1e-3) / 1e6
+        return out
+    except Exception as e:                                     # baseline leg: never fail the bench line
+        return {"unavailable": repr(e)}
+
+
+def run_c5(args, rank, world, local, torch, dist, pkg):
+    """BASELINE config 5: 3840x2160, 64 spp progressive (no denoiser), 16 777 216-triangle terrain, row bands over the GPUs,
+    BVH rebuilt per GPU or built once and broadcast (--bvh), one NCCL gather of the fp32 accumulation buffer per step."""
+    W, H, spp = 3840, 2160, args.spp
+    gx, gz = pkg.scenes.TERRAIN_SIZES["C5"]
+    pos, nrm, idx = pkg.scenes.terrain(gx, gz, seed=1)
+    cam = pkg.scenes.make_camera(CAMERA["pos"], CAMERA["yaw"], CAMERA["pitch"], W, H)
+    rt = pkg.RayTracer(W, H, device=local).init()
+    rt.set_mesh(pos, idx, nrm)
+    rt.set_camera(cam, reset_history=True)
+    sh = pkg.RowShardedRayTracer(rt, W, H, rank, world, bvh=args.bvh)
+    stream = torch.cuda.ExternalStream(rt.stream, device=torch.device("cuda", local))
+    h_out = torch.empty(W * H * 16, dtype=torch.uint8).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # rays per step are deterministic (same frame numbers every step): count them once, untimed
+    sh.build_bvh()
+    rays_rank = 0
+    for smp in range(spp):
+        rt.set_frame_number(1 + smp); rt.pathtrace(); rays_rank += rt.timings()["rays_traced"]
+    sampler = ClockSampler(local); sampler.start()
+    res = {}
+    for name, e2e in (("device", False), ("e2e", True)):
+        steps = args.steps if not e2e else max(2, args.steps // 2)
+        for _ in range(args.warmup if not e2e else 1):
+            sh.render_progressive(spp)
+        barrier()
+        l0 = rt.timings()["kernel_launches"]
+        evs = []
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            sh.render_progressive(spp)
+            if e2e:
+                rt.read_buffer_into(pkg.BUF_ACCUM_RADIANCE, h_out.data_ptr(), h_out.numel())
+            b.record(stream)
+            evs.append((a, b))
+        barrier()
+        res[name] = (float(np.sum([a.elapsed_time(b) for a, b in evs])), steps, rt.timings()["kernel_launches"] - l0)
+        if not e2e:
+            sampler.stop_flag = True; sampler.join()
+    t = torch.tensor([res["device"][0], res["e2e"][0]], dtype=torch.float64, device="cuda")
+    r = torch.tensor([float(rays_rank)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(r, op=dist.ReduceOp.SUM)
+    dev_ms, e2e_ms = t.tolist(); rays_step = r.item()
+    if rank == 0:
+        ms_step = dev_ms / res["device"][1]
+        e2e_step = e2e_ms / res["e2e"][1]
+        line = {"metric": "Mrays/s", "value": rays_step / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": f"C5: 3840x2160, {spp} spp progressive path trace (no denoiser), {idx.shape[0]}-tri procedural terrain "
+                                       f"({(idx.shape[0] + 1023) // 1024} batches, global top level), row bands x{world}",
+                           "width": W, "height": H, "triangles": int(idx.shape[0]), "spp": spp, "rays_per_step": rays_step,
+                           "parallelism": f"row bands x{world}, BVH {args.bvh} per step, NCCL all-gather of the fp32 accumulation buffer",
+                           "l2": "inputs larger than L2 (3.2 GB BVH)", "ms_per_sample": ms_step / spp},
+                "e2e": {"value": rays_step / (e2e_step * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_step, "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": int(h_out.numel()), "note": "static scene: no per-step upload; the accumulated frame is read back"},
+                "gpu_launches": int(res["device"][2]), "clocks": sampler.summary()}
+        print(json.dumps(line), flush=True)
+    rt.cleanup()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -182,7 +288,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--mode", default="samples", choices=["samples", "rows"])
+    ap.add_argument("--bvh", default="rebuild", choices=["rebuild", "broadcast"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C5"])
+    ap.add_argument("--spp", type=int, default=C5_SPP)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-kernels", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -199,6 +309,11 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = importlib.import_module(PKG)        # raises if librtrt.so is missing: no fallback
+    if args.workload == "C5":
+        run_c5(args, rank, world, local, torch, dist, pkg)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     pos, nrm, idx, cam = make_scene(pkg)
     n_tris, n_px = int(idx.shape[0]), WIDTH * HEIGHT
     hbm_peak, peak_kind = peaks()
@@ -206,17 +321,16 @@ def main():
     rt = pkg.RayTracer(WIDTH, HEIGHT, device=local).init()
     rt.set_mesh(pos, idx, nrm)
     rt.set_camera(cam, reset_history=True)
-    rows = (0, HEIGHT)
-    if args.mode == "rows" and world > 1:                      # strong scaling: one frame, contiguous row bands
-        rows = (HEIGHT * rank // world, HEIGHT * (rank + 1) // world)
-        rt.set_row_range(*rows)
+    by_rows = args.mode == "rows"
+    sh = pkg.RowShardedRayTracer(rt, WIDTH, HEIGHT, rank, world, bvh=args.bvh) if by_rows else None
+    rows = sh.band if by_rows else (0, HEIGHT)
     stream = torch.cuda.ExternalStream(rt.stream, device=torch.device("cuda", local))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     h_pos = torch.from_numpy(pos.reshape(-1).copy()).pin_memory()
     h_nrm = torch.from_numpy(nrm.reshape(-1).copy()).pin_memory()
     h_out = torch.empty(n_px * 8, dtype=torch.uint8).pin_memory()
     torch.cuda.synchronize()
-    frame_no = [1 + (rank if args.mode == "samples" else 0)]
+    frame_no = [1 + (rank if not by_rows else 0)]
 
     def barrier():
         if world > 1:
@@ -224,39 +338,46 @@ def main():
         torch.cuda.synchronize()
 
     def combine():
-        """framebuffer combine across ranks (NCCL over NVLink), on the library's stream"""
-        if world == 1:
+        """sample mode: average the ranks' denoised frames (NCCL all-reduce over NVLink), on the library's stream"""
+        if world == 1 or by_rows:
             return
         ptr, nbytes = rt.get_buffer(pkg.BUF_RENDER_COLOR)
         with torch.cuda.stream(stream):
-            if args.mode == "samples":
-                t = torch.as_tensor(DevView(ptr, nbytes), device="cuda")
-                dist.all_reduce(t, op=dist.ReduceOp.AVG)
-            else:
-                t = torch.as_tensor(DevView(ptr, nbytes, "|u1", 1), device="cuda")
-                parts = [t[HEIGHT * r // world * WIDTH * 8: HEIGHT * (r + 1) // world * WIDTH * 8] for r in range(world)]
-                dist.all_gather(parts, parts[rank].clone())
+            dist.all_reduce(torch.as_tensor(DevView(ptr, nbytes), device="cuda"), op=dist.ReduceOp.AVG)
+
+    def frame(e):
+        """build | path trace | (G-buffer exchange) | denoise | (frame gather / combine)"""
+        rt.set_frame_number(frame_no[0]); frame_no[0] += world if not by_rows else 1
+        if by_rows:
+            sh.build_bvh()
+            if e: e[1].record(stream)
+            sh.pathtrace()
+            if e: e[2].record(stream)
+            sh.exchange_gbuffers()
+            if e: e[3].record(stream)
+            sh.denoise()
+            if e: e[4].record(stream)
+            sh.gather_frame()
+        else:
+            rt.build_bvh()
+            if e: e[1].record(stream)
+            rt.pathtrace()
+            if e: e[2].record(stream); e[3].record(stream)
+            rt.denoise()
+            if e: e[4].record(stream)
+            combine()
 
     def step_device(e):
-        rt.set_frame_number(frame_no[0]); frame_no[0] += world if args.mode == "samples" else 1
         if e: e[0].record(stream)
-        rt.build_bvh()
-        if e: e[1].record(stream)
-        rt.pathtrace()
-        if e: e[2].record(stream)
-        rt.denoise()
-        if e: e[3].record(stream)
-        combine()
-        if e: e[4].record(stream)
+        frame(e)
+        if e: e[5].record(stream)
 
     def step_e2e(e):
-        rt.set_frame_number(frame_no[0]); frame_no[0] += world if args.mode == "samples" else 1
         if e: e[0].record(stream)
         rt.update_vertices(h_pos.data_ptr(), h_nrm.data_ptr())             # H2D, pinned
-        rt.build_bvh(); rt.pathtrace(); rt.denoise()
-        combine()
+        frame(None)
         rt.read_buffer_into(pkg.BUF_RENDER_COLOR, h_out.data_ptr(), h_out.numel())   # D2H + stream sync
-        if e: e[4].record(stream)
+        if e: e[5].record(stream)
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):
@@ -267,16 +388,16 @@ def main():
         for _ in range(steps):
             with torch.cuda.stream(stream):
                 flush.zero_()                                            # L2 flush, outside the event pair
-            e = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
             step_fn(e)
             evs.append(e)
             rays += rt.timings()["rays_traced"]                          # synchronises the stream (outside the event pair)
         barrier()
         nl = rt.timings()["kernel_launches"] - lbefore
-        tot = float(np.sum([e[0].elapsed_time(e[4]) for e in evs]))
+        tot = float(np.sum([e[0].elapsed_time(e[5]) for e in evs]))
         stages = None
         if step_fn is step_device:
-            stages = [float(np.mean([e[k].elapsed_time(e[k + 1]) for e in evs])) for k in range(4)]
+            stages = [float(np.mean([e[k].elapsed_time(e[k + 1]) for e in evs])) for k in range(5)]
         return tot, stages, int(nl), int(rays)
 
     sampler = ClockSampler(local); sampler.start()
@@ -297,7 +418,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(r, op=dist.ReduceOp.SUM)
-    total_ms, e2e_ms, build_ms, pt_ms, dn_ms, comb_ms = t.tolist()
+    total_ms, e2e_ms, build_ms, pt_ms, xch_ms, dn_ms, comb_ms = t.tolist()
     rays, e2e_rays = r.tolist()
     ms_step = total_ms / args.steps
     value = rays / (total_ms * 1e-3) / 1e6
@@ -309,27 +430,30 @@ def main():
         dn_gbs = DENOISE_BYTES_PER_PX * WIDTH * rows_n / (dn_ms * 1e-3) / 1e9
         pt_bytes = node_visits * NODE_BYTES + leaf_tests * TRI_BYTES + GBUF_BYTES_PER_PX * WIDTH * rows_n
         pt_gbs = pt_bytes / (pt_ms * 1e-3) / 1e9
+        par = (f"sample-partitioned x{world}, BVH rebuilt per GPU, NCCL all-reduce of the frame" if not by_rows else
+               f"row bands x{world}, BVH {args.bvh}, NCCL all-gather of the G-buffers (30 B/px) and of the denoised frame + history (24 B/px), "
+               f"denoise of band + 80-row halo")
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if args.mode == "samples" else "strong",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if not by_rows else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "width": WIDTH, "height": HEIGHT, "triangles": n_tris, "spp": 1,
-                       "rays_per_step": rays / args.steps,
-                       "parallelism": (f"sample-partitioned x{world}, BVH rebuilt per GPU, NCCL all-reduce of the frame" if args.mode == "samples"
-                                       else f"row bands x{world}, BVH rebuilt per GPU, NCCL all-gather of the frame"),
+                       "rays_per_step": rays / args.steps, "parallelism": par,
                        "l2": "flushed between steps (256 MiB memset, outside the event pairs)",
-                       "stages_ms": {"build_bvh": build_ms, "pathtrace": pt_ms, "denoise": dn_ms, "combine": comb_ms},
+                       "stages_ms": {"build_bvh": build_ms, "pathtrace": pt_ms, "exchange_gbuffers": xch_ms, "denoise": dn_ms, "combine": comb_ms},
                        "pathtrace_mrays_s": rays / args.steps / (pt_ms * 1e-3) / 1e6,
                        "build_mtris_s": n_tris / (build_ms * 1e-3) / 1e6},
-            "roofline": {"kernel": "k_pathtrace (dominant: %.0f%% of the step)" % (100 * pt_ms / max(ms_step, 1e-9)), "bound": "hbm",
+            "roofline": {"kernel": "k_pt_primary + k_pt_logic_first + 4 x (k_pt_trace, k_pt_logic): the path-trace stage, %.0f%% of the step"
+                                   % (100 * pt_ms / max(ms_step, 1e-9)), "bound": "hbm",
                          "achieved": pt_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pt_gbs / hbm_peak, "traffic": None,
                          "peak_kind": peak_kind, "algorithmic_bytes_per_launch": int(pt_bytes),
-                         "note": "latency/divergence-bound traversal (no RT cores); bytes = node visits x 64 + leaf tests x 128 + 30 B/px G-buffer",
+                         "note": "latency/divergence-bound traversal (no RT cores); bytes = node visits x 64 + leaf tests x 128 + 30 B/px G-buffer "
+                                 "(reference layout, SURVEY 8d 'secondary'); most of them are L1/L2 hits, see profiles/ for dram__bytes",
                          "node_visits_per_ray": node_visits / max(rays_cnt, 1), "leaf_tests_per_ray": leaf_tests / max(rays_cnt, 1)},
             "roofline_build": {"kernel": "k_build_blas (gather+AABB+Morton+sort+Karras+refit+TLAS, one launch)", "bound": "hbm",
                                "achieved": build_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": build_gbs / hbm_peak,
                                "algorithmic_bytes_per_launch": BUILD_BYTES_PER_TRI * n_tris},
-            "roofline_denoise": {"kernel": "k_dn_* (6 launches)", "bound": "hbm", "achieved": dn_gbs, "peak": hbm_peak, "unit": "GB/s",
+            "roofline_denoise": {"kernel": "k_dn_* (7 launches)", "bound": "hbm", "achieved": dn_gbs, "peak": hbm_peak, "unit": "GB/s",
                                  "frac": dn_gbs / hbm_peak, "algorithmic_bytes_per_step": DENOISE_BYTES_PER_PX * WIDTH * rows_n,
                                  "note": "252 B/px = the reference's pass-wise traffic; fused lower bound 74 B/px"},
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "ms_per_step": e2e_ms / e2e_steps,
@@ -337,6 +461,8 @@ def main():
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
         }
+        if world == 1 and not args.no_ref_kernels:
+            line["reference_kernels"] = reference_kernels(pkg, rt, pos, nrm, idx, cam, rays / args.steps)
         if not args.no_cpu_baseline and world == 1:
             _, _, line["cpu_baseline"] = CpuArm(pkg).baseline(steps=1, warmup=0)
         print(json.dumps(line), flush=True)

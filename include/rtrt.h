@@ -200,6 +200,10 @@ int rtrt_set_materials(rtrt_ctx* ctx, const rtrt_material* materials, int32_t nu
 int rtrt_set_texture(rtrt_ctx* ctx, int32_t slot, int32_t width, int32_t height, const uint16_t* rgba16);
 /* rows [begin,end) of the frame this context traces and denoises (multi-GPU row bands); default: all rows */
 int rtrt_set_row_range(rtrt_ctx* ctx, int32_t row_begin, int32_t row_end);
+/* multi-GPU load balance: rtrt_pathtrace / rtrt_accumulate cover the rows with (row / strip_height) % num_shards == shard instead of
+ * the contiguous band (a terrain frame is sky at the top, geometry at the bottom); rtrt_denoise keeps using the row range, whose
+ * band + 80-row halo must have been made valid by the caller (all-gather).  num_shards <= 1 switches strips off. */
+int rtrt_set_row_strips(rtrt_ctx* ctx, int32_t strip_height, int32_t num_shards, int32_t shard);
 int rtrt_set_data_dir(rtrt_ctx* ctx, const char* dir);               /* where blue_noise_4spp.bin / hosek_sky.bin live */
 
 /* ---- stage 2: the PathTrace launch of RayTracer::draw (src/kernel.cu:336-357, src/pathtrace.cuh:11-128) ---- */

@@ -98,6 +98,7 @@ SYMBOLS = {
     "rtrt_denoise": (C.c_int, [C.c_void_p]),
     "rtrt_render_frame": (C.c_int, [C.c_void_p]),
     "rtrt_accumulate": (C.c_int, [C.c_void_p, C.c_int]),
+    "rtrt_set_row_strips": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
 }
 
 _lib = None

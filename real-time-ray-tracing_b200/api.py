@@ -209,6 +209,10 @@ class RayTracer:
     def set_row_range(self, begin, end):
         self._check(self._lib.rtrt_set_row_range(self._h, begin, end))
 
+    def set_row_strips(self, strip_height, num_shards, shard):
+        """Path trace / accumulate the rows with (row // strip_height) % num_shards == shard (load-balanced multi-GPU split)."""
+        self._check(self._lib.rtrt_set_row_strips(self._h, strip_height, num_shards, shard))
+
     # -- stages 2, 3 ------------------------------------------------------------------------------
     def pathtrace(self):
         """The PathTrace launch of RayTracer::draw (src/kernel.cu:336-357)."""

@@ -485,6 +485,15 @@ int rtrt_set_row_range(rtrt_ctx* ctx, int32_t b, int32_t e) {
     return RTRT_OK;
 }
 
+int rtrt_set_row_strips(rtrt_ctx* ctx, int32_t strip_height, int32_t num_shards, int32_t shard) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (num_shards <= 1) { c.stripH = 0; c.stripShards = 1; c.stripShard = 0; return RTRT_OK; }
+    if (strip_height < 1 || shard < 0 || shard >= num_shards) return c.fail(RTRT_ERR_ARG, "rtrt_set_row_strips: bad arguments");
+    c.stripH = strip_height; c.stripShards = num_shards; c.stripShard = shard;
+    return RTRT_OK;
+}
+
 int rtrt_set_data_dir(rtrt_ctx* ctx, const char* dir) {
     CTX_OR_FAIL(ctx);
     if (!dir) return ctx->c.fail(RTRT_ERR_ARG, "rtrt_set_data_dir: null");

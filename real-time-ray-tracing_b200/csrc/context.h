@@ -45,6 +45,7 @@ struct Context {
     // ---- frame state: ConstBuffer (src/kernel.cuh:211-231) + Buffer2DManager (src/init.cu:441-584) ----
     int width = 0, height = 0;               // render size
     int rowBegin = 0, rowEnd = 0;            // rows this GPU traces / denoises (multi-GPU row bands); default = whole frame
+    int stripH = 0, stripShards = 1, stripShard = 0;   // rtrt_set_row_strips: path trace / accumulate rows with (row / stripH) % stripShards == stripShard
     int frameNum = 1;                        // src/kernel.cu:61-63 (first frame is 1)
     bool cameraSet = false;
     Camera camera{}; Camera prevCamera{}; HistoryCamera historyCamera{};
@@ -99,6 +100,7 @@ int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int an
 int launch_pathtrace(Context& c);
 int launch_denoise(Context& c);
 int launch_accumulate(Context& c, int reset);
+int local_rows(const Context& c);            // rows of the frame this context path-traces (band or strips)
 int ensure_frame_resources(Context& c);      // frame.cu: G-buffers, tables, default materials/textures, sky regeneration
 void free_frame_resources(Context& c);
 int set_texture(Context& c, int slot, int w, int h, const uint16_t* rgba);

@@ -400,9 +400,13 @@ __global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort
 // [rowBegin, rowEnd) only, so row-sharded GPUs accumulate their own band.
 // -------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_accumulate(const ushort4* __restrict__ color, const ushort4* __restrict__ albedo, float4* __restrict__ acc,
-                                                    size_t begin, size_t end, int reset) {
-    const size_t i = begin + (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= end) return;
+                                                    int W, int localRows, int rowBegin, int stripH, int stripShards, int stripShard, int reset) {
+    const size_t k = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (k >= (size_t)W * localRows) return;
+    const int j = (int)(k / W), x = (int)(k - (size_t)j * W);
+    int y = rowBegin + j;
+    if (stripShards > 1) { const int q = j / stripH; y = (q * stripShards + stripShard) * stripH + (j - q * stripH); }
+    const size_t i = (size_t)y * W + x;
     const Float3 c = px_rgb(__ldg(color + i)) * px_rgb(__ldg(albedo + i));
     float4 a = reset ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : acc[i];
     a.x += c.x; a.y += c.y; a.z += c.z; a.w += 1.0f;
@@ -419,9 +423,11 @@ int launch_accumulate(Context& c, int reset) {
         RTRT_CUDA(c, cudaMemsetAsync(c.dAccumRadiance, 0, px * sizeof(float4), c.stream));
         c.accumRadiancePx = px;
     }
-    const size_t begin = (size_t)c.rowBegin * c.width, end = (size_t)c.rowEnd * c.width;
-    k_accumulate<<<(unsigned)((end - begin + 255) / 256), 256, 0, c.stream>>>(reinterpret_cast<const ushort4*>(c.dColor), reinterpret_cast<const ushort4*>(c.dAlbedo),
-                                                                             reinterpret_cast<float4*>(c.dAccumRadiance), begin, end, reset);
+    const int rows = local_rows(c);
+    const size_t n = (size_t)rows * c.width;
+    k_accumulate<<<(unsigned)((n + 255) / 256), 256, 0, c.stream>>>(reinterpret_cast<const ushort4*>(c.dColor), reinterpret_cast<const ushort4*>(c.dAlbedo),
+                                                                   reinterpret_cast<float4*>(c.dAccumRadiance), c.width, rows, c.rowBegin, c.stripH,
+                                                                   c.stripShards, c.stripShard, reset);
     c.launches++;
     RTRT_CUDA(c, cudaGetLastError());
     return RTRT_OK;

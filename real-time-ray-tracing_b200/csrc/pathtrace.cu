@@ -19,9 +19,9 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
     if (tid == 0) sRays = 0;
     __syncthreads();
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
-    const int iy = P.rowBegin + blockIdx.y * kPtBlockY + threadIdx.y;
+    const int jy = blockIdx.y * kPtBlockY + threadIdx.y, iy = frame_row(P, jy);
     uint32_t rays = 0, nodeVisits = 0, leafTests = 0;
-    if (ix < P.width && iy < P.rowEnd) {
+    if (ix < P.width && jy < P.localRows) {
         const float4 a = __ldg(P.sc.tlasRows), b = __ldg(P.sc.tlasRows + 1), c = __ldg(P.sc.tlasRows + 2);
         AABB sceneBox;
         sceneBox.max = Float3{sel_max(a.x, c.x), sel_max(a.y, c.y), sel_max(a.z, c.z)};
@@ -111,6 +111,7 @@ void fill_pathtrace_params(Context& c, PathTraceParams& P) {
     for (int t = 0; t < 2; ++t) P.tex[t] = c.tex[t];
     P.frameNum = c.frameNum; P.width = c.width; P.height = c.height;
     P.rowBegin = c.rowBegin; P.rowEnd = c.rowEnd;
+    P.stripH = c.stripH; P.stripShards = c.stripShards; P.stripShard = c.stripShard; P.localRows = local_rows(c);
     P.color = reinterpret_cast<ushort4*>(c.dColor); P.normal = reinterpret_cast<ushort4*>(c.dNormal);
     P.albedo = reinterpret_cast<ushort4*>(c.dAlbedo); P.depth = reinterpret_cast<__half*>(c.dDepth);
     P.motion = reinterpret_cast<__half2*>(c.dMotion);
@@ -118,6 +119,15 @@ void fill_pathtrace_params(Context& c, PathTraceParams& P) {
 }
 
 int launch_pathtrace_wavefront(Context& c);   // pathtrace_wf.cu
+
+int local_rows(const Context& c) {
+    if (c.stripShards <= 1) return c.rowEnd - c.rowBegin;
+    const int strips = (c.height + c.stripH - 1) / c.stripH;                       // strips of the frame, the last one may be short
+    const int mine = strips > c.stripShard ? (strips - c.stripShard + c.stripShards - 1) / c.stripShards : 0;
+    int rows = mine * c.stripH;
+    if (mine > 0 && (strips - 1) % c.stripShards == c.stripShard) rows -= strips * c.stripH - c.height;   // the short last strip is mine
+    return rows;
+}
 
 int launch_pathtrace(Context& c) {
     if (!c.bvhValid) return c.fail(RTRT_ERR_STATE, "rtrt_pathtrace: BVH not built");
@@ -128,7 +138,7 @@ int launch_pathtrace(Context& c) {
     PathTraceParams P{};
     fill_pathtrace_params(c, P);
     RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));
-    const int rows = c.rowEnd - c.rowBegin;
+    const int rows = local_rows(c);
     const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
     if (c.countVisits) k_pathtrace<true><<<grid, block, 0, c.stream>>>(P);
     else k_pathtrace<false><<<grid, block, 0, c.stream>>>(P);

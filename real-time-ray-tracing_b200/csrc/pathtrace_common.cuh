@@ -18,9 +18,17 @@ struct PathTraceParams {
     Camera camera; HistoryCamera historyCamera;
     EnvMaps env; BlueNoiseTables bn; MipTex tex[2];
     int frameNum, width, height, rowBegin, rowEnd;
+    int stripH, stripShards, stripShard, localRows;        // row strips (stripShards > 1) or the contiguous band [rowBegin, rowEnd)
     ushort4* color; ushort4* normal; ushort4* albedo; __half* depth; __half2* motion;
     unsigned long long* rayCounter;
 };
+
+// local row j (0 .. localRows-1) of this context -> frame row
+VD int frame_row(const PathTraceParams& P, int j) {
+    if (P.stripShards <= 1) return P.rowBegin + j;
+    const int q = j / P.stripH;
+    return (q * P.stripShards + P.stripShard) * P.stripH + (j - q * P.stripH);
+}
 
 struct RayState {            // live subset of src/kernel.cuh:233-284
     Float3 orig, dir, beta0, beta1, pos, normal, fakeNormal, albedo, centerRaydir;

@@ -157,9 +157,9 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams
     __shared__ float sT[16 * kPtThreads];
     const int tid = threadIdx.y * kPtBlockX + threadIdx.x, lane = tid & 31;
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
-    const int iy = P.rowBegin + blockIdx.y * kPtBlockY + threadIdx.y;
+    const int jy = blockIdx.y * kPtBlockY + threadIdx.y, iy = frame_row(P, jy);
     uint32_t nodeVisits = 0, leafTests = 0;
-    if (ix < P.width && iy < P.rowEnd) {
+    if (ix < P.width && jy < P.localRows) {
         const AABB sceneBox = scene_box(P.sc);
         const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
         Float3 orig, dir, centerDir; Float2 sampleUv;
@@ -291,10 +291,10 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTrac
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tilesX = (P.width + 7) / 8;
     const int tile = blockIdx.x * (kLogicThreads / 32) + warp;
-    const int ix = (tile % tilesX) * 8 + (lane & 7), iy = P.rowBegin + (tile / tilesX) * 4 + (lane >> 3);
+    const int ix = (tile % tilesX) * 8 + (lane & 7), jy = (tile / tilesX) * 4 + (lane >> 3), iy = frame_row(P, jy);
     bool emit = false;
     const uint32_t pix = (uint32_t)((size_t)iy * P.width + ix);
-    if (ix < P.width && iy < P.rowEnd) logic_body(P, B, pix, true, emit);
+    if (ix < P.width && jy < P.localRows) logic_body(P, B, pix, true, emit);
     queue_append(emit, pix, B.rayQueue, countOut, lane);
 }
 
@@ -355,7 +355,7 @@ int launch_pathtrace_wavefront(Context& c) {
     if (!smCount) { cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c.device); if (smCount <= 0) smCount = 148; }
     RTRT_CUDA(c, cudaMemsetAsync(B.counters, 0, 256, c.stream));
     RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));
-    const int rows = c.rowEnd - c.rowBegin;
+    const int rows = local_rows(c);
     const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
     if (c.countVisits) k_pt_primary<true><<<grid, block, 0, c.stream>>>(P, B);
     else k_pt_primary<false><<<grid, block, 0, c.stream>>>(P, B);

@@ -1,12 +1,15 @@
 """Multi-GPU host logic: one process and one RayTracer context per GPU, torch.distributed for the plumbing.
 
-The path shards by IMAGE ROWS.  Rank r owns the contiguous band rows [H*r/N, H*(r+1)/N) of every frame:
+The path shards by IMAGE ROWS.  For the denoiser rank r owns the contiguous band rows [H*r/N, H*(r+1)/N) of every frame; the
+path tracer splits the frame into interleaved STRIPS of `strip_height` rows, strip k going to rank k % N, because a frame is
+not uniform (sky at the top, geometry at the bottom: contiguous bands leave half of the GPUs idle):
 
     build      every rank rebuilds the whole BVH redundantly (no communication), or rank 0 builds and the three traversal
                arrays (Triangle[], BVHNode[], TLAS BVHNode[]) are broadcast over NVLink — `bvh="rebuild" | "broadcast"`.
-    pathtrace  each rank traces its band (rtrt_set_row_range).
+    pathtrace  each rank traces its strips (rtrt_set_row_strips), or its band when strip_height == 0 (rtrt_set_row_range).
     exchange   all-gather of the five G-buffers by rows (colour+mask 8, normal 8, albedo 8, depth 2, motion 4 = 30 B/px),
-               so every rank holds the whole frame's denoiser inputs.
+               so every rank holds the whole frame's denoiser inputs.  Strips are packed into one contiguous staging block
+               per rank (row gather), all-gathered, and scattered back to their rows (one pack + one unpack kernel per buffer).
     denoise    each rank filters its band plus the 80-row dependency halo (csrc/denoise.cu, launch_denoise): the halo is
                recomputed instead of exchanged pass by pass, so there is no collective inside the denoiser.
     gather     all-gather of the band's denoised colour (the frame buffer), history colour and accumulation colour — what the
@@ -48,6 +51,49 @@ def all_gather_rows(buf, row_bytes, bands, rank, group=None):
             dist.broadcast(buf[b * row_bytes: e * row_bytes], src=dist.get_global_rank(group, r) if group is not None else r, group=group)
 
 
+def strip_rows(height, strip_height, world):
+    """Rows of each rank under the interleaved split: strip k = rows [k*h, (k+1)*h) belongs to rank k % world."""
+    rows = np.arange(height)
+    owner = (rows // strip_height) % world
+    return [rows[owner == r] for r in range(world)]
+
+
+class StripGather:
+    """All-gather of interleaved row strips of row-major full-frame byte tensors.  Per buffer: index_select of the own rows into
+    the rank's slot of a staging tensor, one all_gather_into_tensor, index_copy_ of all rows back.  Ranks with fewer rows pad
+    their slot by repeating their last row (the duplicate is written twice with the same bytes)."""
+
+    def __init__(self, height, strip_height, world, rank, device, group=None):
+        import torch
+        self.world, self.rank, self.group, self.H = world, rank, group, height
+        per = strip_rows(height, strip_height, world)
+        if any(len(p) == 0 for p in per):
+            raise ValueError("strip split leaves a rank without rows")
+        self.nmax = max(len(p) for p in per)
+        padded = [np.concatenate([p, np.full(self.nmax - len(p), p[-1])]) for p in per]
+        self.mine = torch.from_numpy(padded[rank].astype(np.int64)).to(device)
+        self.all_rows = torch.from_numpy(np.concatenate(padded).astype(np.int64)).to(device)
+        self._staging = {}
+
+    def gather(self, buf, row_bytes):
+        """buf: uint8 tensor of H*row_bytes; on entry the own strips are valid, on return every row is."""
+        import torch
+        import torch.distributed as dist
+        if self.world == 1:
+            return
+        wide = torch.int64 if row_bytes % 8 == 0 and buf.data_ptr() % 8 == 0 else torch.uint8
+        item = 8 if wide is torch.int64 else 1
+        v = buf[: self.H * row_bytes].view(wide).view(self.H, row_bytes // item)
+        key = (row_bytes, wide)
+        if key not in self._staging:
+            self._staging[key] = torch.empty((self.world * self.nmax, row_bytes // item), dtype=wide, device=buf.device)
+        st = self._staging[key]
+        mine = st[self.rank * self.nmax: (self.rank + 1) * self.nmax]
+        torch.index_select(v, 0, self.mine, out=mine)
+        dist.all_gather_into_tensor(st, mine if buf.is_cuda else mine.clone(), group=self.group)
+        v.index_copy_(0, self.all_rows, st)
+
+
 class _DevBytes:
     """A borrowed device buffer as a __cuda_array_interface__ object (so torch / NCCL can address it)."""
 
@@ -64,12 +110,16 @@ BVH_ARRAYS = [L.BUF_TRIANGLES, L.BUF_BVH_NODES, L.BUF_TLAS_BVH_NODES]
 class RowShardedRayTracer:
     """Drives one RayTracer context as rank `rank` of `world` row-sharded GPUs.  Collectives run on the context's stream."""
 
-    def __init__(self, rt, width, height, rank, world, bvh="rebuild", group=None):
+    def __init__(self, rt, width, height, rank, world, bvh="rebuild", group=None, strip_height=8):
         if bvh not in ("rebuild", "broadcast"):
             raise ValueError("bvh must be 'rebuild' or 'broadcast'")
         self.rt, self.W, self.H, self.rank, self.world, self.bvh, self.group = rt, width, height, rank, world, bvh, group
         self.bands = row_bands(height, world)
         rt.set_row_range(*self.bands[rank])
+        self.strip_height = strip_height if world > 1 else 0
+        self._strips = None
+        if self.strip_height:
+            rt.set_row_strips(self.strip_height, world, rank)
         self._stream = None
 
     @property
@@ -87,12 +137,19 @@ class RowShardedRayTracer:
         ptr, nbytes = self.rt.get_buffer(which)
         return torch.as_tensor(_DevBytes(ptr, nbytes), device="cuda")
 
-    def _gather(self, bufs):
+    def _gather(self, bufs, strips=False):
+        """all-gather full-frame buffers by contiguous bands, or by the path tracer's interleaved strips"""
         if self.world == 1:
             return
         with self._on_stream():
-            for which, bpp in bufs:
-                all_gather_rows(self._tensor(which), self.W * bpp, self.bands, self.rank, self.group)
+            if strips and self.strip_height:
+                if self._strips is None:
+                    self._strips = StripGather(self.H, self.strip_height, self.world, self.rank, "cuda", self.group)
+                for which, bpp in bufs:
+                    self._strips.gather(self._tensor(which), self.W * bpp)
+            else:
+                for which, bpp in bufs:
+                    all_gather_rows(self._tensor(which), self.W * bpp, self.bands, self.rank, self.group)
 
     # -- stages -------------------------------------------------------------------------------------------------------
     def build_bvh(self):
@@ -113,7 +170,7 @@ class RowShardedRayTracer:
         self.rt.pathtrace()
 
     def exchange_gbuffers(self):
-        self._gather(GBUFFERS)
+        self._gather(GBUFFERS, strips=True)
 
     def denoise(self):
         self.rt.denoise()
@@ -143,7 +200,7 @@ class RowShardedRayTracer:
             self.rt.set_frame_number(first_frame + s)
             self.rt.pathtrace()
             self.rt.accumulate(reset=(s == 0))
-        self._gather([(L.BUF_ACCUM_RADIANCE, 16)])
+        self._gather([(L.BUF_ACCUM_RADIANCE, 16)], strips=True)
 
 
 def assemble_rows(parts, bands, row_items):

@@ -29,6 +29,15 @@ def test_assemble_rows(pkg):
     assert out.tolist() == [0, 1, 2, 3, 4, 5, -6, -7, -8, -9, -10, -11]
 
 
+def test_strip_rows_partition(pkg):
+    for H, sh, world in [(1080, 8, 2), (1080, 8, 8), (2160, 8, 8), (45, 4, 2), (136, 8, 3), (17, 1, 4)]:
+        per = pkg.parallel.strip_rows(H, sh, world)
+        allr = np.sort(np.concatenate(per))
+        assert np.array_equal(allr, np.arange(H))                        # every row exactly once
+        for r, p in enumerate(per):
+            assert ((p // sh) % world == r).all()
+
+
 def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
     return p
@@ -61,6 +70,16 @@ def _worker(rank, world, port, H, out_dir):
             other[b * row_bytes: e * row_bytes] = t[b * row_bytes: e * row_bytes]
             pkg.parallel.all_gather_rows(other, row_bytes, bands, rank)
             gathered[name] = other.numpy().view(a.dtype).reshape(a.shape)
+        # the interleaved-strip gather on the same planes: keep only the own strips, poison the rest, gather
+        sg = pkg.parallel.StripGather(H, 4, world, rank, "cpu")
+        full_planes = {k: v.copy() for k, v in gathered.items()}
+        for name, a in full_planes.items():
+            row_bytes = a.nbytes // H
+            t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy())
+            keep = np.zeros(H, bool); keep[pkg.parallel.strip_rows(H, 4, world)[rank]] = True
+            t.view(H, row_bytes)[torch.from_numpy(~keep)] = 0xCD
+            sg.gather(t, row_bytes)
+            assert np.array_equal(t.numpy(), a.view(np.uint8).reshape(-1)), f"{name}: strip gather"
         if rank == 0:
             full = orc.pathtrace(ob, cam, W, H, 3, sky, threads=2)
             for name, a in gathered.items():

@@ -24,21 +24,26 @@ def dev_tensor(rt, pkg, which):
     return torch.as_tensor(pkg.parallel._DevBytes(ptr, nbytes), device="cuda")
 
 
-def exchange(rts, pkg, bufs, bands, W):
-    """what all_gather_rows does over NCCL, as device copies between the contexts of one GPU"""
+def exchange(rts, pkg, bufs, bands, W, rows_of=None):
+    """what all_gather_rows / StripGather do over NCCL, as device copies between the contexts of one GPU.
+    rows_of: per-rank row index arrays (interleaved strips); None = the contiguous bands"""
     import torch
     torch.cuda.synchronize()
+    H = bands[-1][1]
+    if rows_of is None:
+        rows_of = [np.arange(b, e) for b, e in bands]
     for which, bpp in bufs:
-        ts = [dev_tensor(rt, pkg, which) for rt in rts]
-        for src, (b, e) in enumerate(bands):
+        ts = [dev_tensor(rt, pkg, which)[: H * W * bpp].view(H, W * bpp) for rt in rts]
+        for src, rows in enumerate(rows_of):
+            idx = torch.from_numpy(np.asarray(rows, np.int64)).cuda()
             for dst in range(len(rts)):
                 if dst != src:
-                    ts[dst][b * W * bpp: e * W * bpp].copy_(ts[src][b * W * bpp: e * W * bpp])
+                    ts[dst].index_copy_(0, idx, ts[src].index_select(0, idx))
     torch.cuda.synchronize()
 
 
-@pytest.mark.parametrize("W,H,world", [(256, 256, 2), (200, 136, 3), (320, 400, 4)])
-def test_row_bands_on_one_gpu(pkg, W, H, world):
+@pytest.mark.parametrize("W,H,world,strip", [(256, 256, 2, 0), (200, 136, 3, 8), (320, 400, 4, 8), (256, 250, 2, 5)])
+def test_row_bands_on_one_gpu(pkg, W, H, world, strip):
     pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C1"], seed=1)
     bands = pkg.row_bands(H, world)
     full = pkg.RayTracer(W, H).init()
@@ -48,12 +53,15 @@ def test_row_bands_on_one_gpu(pkg, W, H, world):
             rt.set_mesh(pos, idx, nrm); rt.build_bvh()
         for r, rt in enumerate(rts):
             rt.set_row_range(*bands[r])
+            if strip:
+                rt.set_row_strips(strip, world, r)                      # path trace by interleaved strips, denoise by bands
+        rows_of = pkg.parallel.strip_rows(H, strip, world) if strip else None
         for frame in range(1, 6):
             cam = pkg.scenes.make_camera((0.3 * frame, 30, -60 + 0.2 * frame), 0.01 * frame, -0.4 - 0.01 * frame, W, H)
             for rt in [full] + rts:
                 rt.set_camera(cam, reset_history=(frame == 1)); rt.set_frame_number(frame)
                 rt.pathtrace()
-            exchange(rts, pkg, pkg.parallel.GBUFFERS, bands, W)
+            exchange(rts, pkg, pkg.parallel.GBUFFERS, bands, W, rows_of)
             for which, _ in pkg.parallel.GBUFFERS:
                 want = full.read_buffer(which)
                 for rt in rts:
@@ -84,12 +92,12 @@ def test_progressive_accumulation_by_bands(pkg):
         for rt in [full] + rts:
             rt.set_mesh(pos, idx, nrm); rt.build_bvh(); rt.set_camera(cam, reset_history=True)
         for r, rt in enumerate(rts):
-            rt.set_row_range(*bands[r])
+            rt.set_row_strips(8, 2, r)
         for s in range(spp):
             for rt in [full] + rts:
                 rt.set_frame_number(1 + s); rt.pathtrace(); rt.accumulate(reset=(s == 0))
             ref_sum += full.read_buffer(pkg.BUF_RENDER_COLOR)["rgb"].astype(np.float64) * full.read_buffer(pkg.BUF_ALBEDO).astype(np.float64)[:, :3]
-        exchange(rts, pkg, [(pkg.BUF_ACCUM_RADIANCE, 16)], bands, W)
+        exchange(rts, pkg, [(pkg.BUF_ACCUM_RADIANCE, 16)], bands, W, pkg.parallel.strip_rows(H, 8, 2))
         want = full.read_buffer(pkg.BUF_ACCUM_RADIANCE)
         assert (want[:, 3] == spp).all()
         np.testing.assert_allclose(want[:, :3], ref_sum, rtol=1e-5, atol=1e-6)
