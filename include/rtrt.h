@@ -104,7 +104,9 @@ typedef enum rtrt_buffer {
     RTRT_BUF_SKY_CDF,            /* float[512*256]   inclusive luminance CDF                            */
     RTRT_BUF_SUN,                /* float4[32*32]    (SunBuffer)                                        */
     RTRT_BUF_SUN_CDF,            /* float[32*32]                                                        */
-    RTRT_BUF_ACCUM_RADIANCE      /* float4: sum of colour*albedo over the accumulated samples, .w = count (rtrt_accumulate) */
+    RTRT_BUF_ACCUM_RADIANCE,     /* float4: sum of colour*albedo over the accumulated samples, .w = count (rtrt_accumulate) */
+    RTRT_BUF_WF_COUNTERS = 100   /* diagnostics: uint32[64] of the wavefront path tracer: [r] rays of bounce round r, [16+r] hits, [24+r] misses,
+                                    with option count_visits: [40+r] max and [48+r] sum of traversal iterations of round r */
 } rtrt_buffer;
 
 /* SkyParams (src/settingParams.h:26-46), same defaults. */
@@ -159,6 +161,9 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
  *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
  *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)
+ *   "pt_chunks"           1    : rtrt_pathtrace splits the frame into this many independent sets of 8-row strips and runs their
+ *                                wavefront pipelines on side streams, so that the latency tail of one set's bounce rounds overlaps
+ *                                the bulk of another's (1..8; results do not depend on it; measured slower than 1 on B200, kept for experiments)
  *   "assume_bvh_valid"    0/1  : mark the BVH arrays as built (they were filled from outside, e.g. an NCCL broadcast from
  *                                the rank that built them) or as stale
  *   "global_sort"         0/1  : rtrt_build_bvh first sorts the triangles by the 60-bit Morton code of their centroid in the

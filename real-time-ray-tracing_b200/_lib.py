@@ -18,6 +18,7 @@ BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_B
     BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES, BUF_TRI_PERMUTATION = range(12)
 BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCUMULATION_COLOR, BUF_HISTORY_COLOR, \
     BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF, BUF_ACCUM_RADIANCE = range(32, 47)
+BUF_WF_COUNTERS = 100
 
 
 class Config(C.Structure):

@@ -39,7 +39,7 @@ for _b, _dt in ((L.BUF_RENDER_COLOR, COLOR_DTYPE), (L.BUF_NORMAL, np.dtype(("<f2
                 (L.BUF_ACCUMULATION_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_DEPTH, np.dtype("<f2")),
                 (L.BUF_NOISE_LEVEL, np.dtype("<f2")), (L.BUF_NOISE_LEVEL_16, np.dtype("<f2")),
                 (L.BUF_SKY, np.dtype(("<f4", 4))), (L.BUF_SKY_CDF, np.dtype("<f4")), (L.BUF_SUN, np.dtype(("<f4", 4))),
-                (L.BUF_SUN_CDF, np.dtype("<f4")), (L.BUF_ACCUM_RADIANCE, np.dtype(("<f4", 4)))):
+                (L.BUF_SUN_CDF, np.dtype("<f4")), (L.BUF_ACCUM_RADIANCE, np.dtype(("<f4", 4))), (L.BUF_WF_COUNTERS, np.dtype("<u4"))):
     BUFFER_DTYPES[_b] = _dt
 MAT_LAMBERTIAN_DIFFUSE, MAT_PERFECT_REFLECTION, MAT_GLASS, MAT_MICROFACET_REFLECTION, MAT_EMISSIVE, MAT_SKY = range(6)
 

@@ -148,6 +148,9 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     free_frame_resources(c);
     dfree(c.dRayStage); dfree(c.dHitStage); dfree(c.dTicket);
     for (auto& e : c.ev) { if (e[0]) cudaEventDestroy(e[0]); if (e[1]) cudaEventDestroy(e[1]); }
+    for (auto& st : c.chunkStream) if (st) cudaStreamDestroy(st);
+    for (auto& ev : c.chunkJoin) if (ev) cudaEventDestroy(ev);
+    if (c.chunkFork) cudaEventDestroy(c.chunkFork);
     if (c.stream) cudaStreamDestroy(c.stream);
     delete ctx;
     return RTRT_OK;
@@ -247,6 +250,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
+    if (!strcmp(name, "pt_chunks")) { if (value < 1 || value > Context::kMaxChunks) return c.fail(RTRT_ERR_ARG, "pt_chunks must be 1..8"); c.ptChunks = (int)value; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }
     return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: unknown option");
 }
@@ -329,6 +333,7 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         case RTRT_BUF_NOISE_LEVEL: p = c.dNoise; b = (size_t)((c.gbufW + 7) / 8) * ((c.gbufH + 7) / 8) * 2; break;
         case RTRT_BUF_NOISE_LEVEL_16: p = c.dNoise16; b = (size_t)((c.gbufW + 15) / 16) * ((c.gbufH + 15) / 16) * 2; break;
         case RTRT_BUF_ACCUM_RADIANCE: p = c.dAccumRadiance; b = px * 16; break;
+        case RTRT_BUF_WF_COUNTERS: p = c.dWf; b = c.dWf ? 256 : 0; break;
         case RTRT_BUF_SKY: p = c.dSky; b = sizeof(float) * 4 * kSkySize; break;
         case RTRT_BUF_SKY_CDF: p = c.dSkyCdf; b = sizeof(float) * kSkySize; break;
         case RTRT_BUF_SUN: p = c.dSun; b = sizeof(float) * 4 * kSunSize; break;

@@ -41,6 +41,9 @@ struct Context {
     bool countVisits = false;
     bool wavefront = true;                 // path-trace driver: wavefront queues (default) or the single megakernel
     void* dWf = nullptr; size_t wfBytes = 0;   // wavefront path state + queues (pathtrace_wf.cu)
+    int ptChunks = 1;                          // option pt_chunks: independent pixel chunks of one frame, pipelined on side streams
+    static constexpr int kMaxChunks = 8;
+    cudaStream_t chunkStream[kMaxChunks] = {}; cudaEvent_t chunkFork = nullptr; cudaEvent_t chunkJoin[kMaxChunks] = {};
 
     // ---- frame state: ConstBuffer (src/kernel.cuh:211-231) + Buffer2DManager (src/init.cu:441-584) ----
     int width = 0, height = 0;               // render size

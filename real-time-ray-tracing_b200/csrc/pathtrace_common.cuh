@@ -19,9 +19,16 @@ struct PathTraceParams {
     EnvMaps env; BlueNoiseTables bn; MipTex tex[2];
     int frameNum, width, height, rowBegin, rowEnd;
     int stripH, stripShards, stripShard, localRows;        // row strips (stripShards > 1) or the contiguous band [rowBegin, rowEnd)
+    int chunks, chunk, chunkRows;                          // this launch covers the local 8-row strips s with s % chunks == chunk
     ushort4* color; ushort4* normal; ushort4* albedo; __half* depth; __half2* motion;
     unsigned long long* rayCounter;
 };
+
+// row jj of this launch's chunk (0 .. chunkRows-1) -> local row of the context (0 .. localRows-1)
+VD int chunk_row(const PathTraceParams& P, int jj) {
+    if (P.chunks <= 1) return jj;
+    return (((jj >> 3) * P.chunks + P.chunk) << 3) + (jj & 7);
+}
 
 // local row j (0 .. localRows-1) of this context -> frame row
 VD int frame_row(const PathTraceParams& P, int j) {

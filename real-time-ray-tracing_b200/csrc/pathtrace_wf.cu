@@ -157,9 +157,9 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams
     __shared__ float sT[16 * kPtThreads];
     const int tid = threadIdx.y * kPtBlockX + threadIdx.x, lane = tid & 31;
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
-    const int jy = blockIdx.y * kPtBlockY + threadIdx.y, iy = frame_row(P, jy);
+    const int jc = blockIdx.y * kPtBlockY + threadIdx.y, jy = chunk_row(P, jc), iy = frame_row(P, jy);
     uint32_t nodeVisits = 0, leafTests = 0;
-    if (ix < P.width && jy < P.localRows) {
+    if (ix < P.width && jc < P.chunkRows && jy < P.localRows) {
         const AABB sceneBox = scene_box(P.sc);
         const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
         Float3 orig, dir, centerDir; Float2 sampleUv;
@@ -192,6 +192,13 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
     const uint32_t numTri = sc.numBatches * kBatchSize;
     const int maxLoop = sc.maxLoop;
     uint32_t* stL = sLink + tid; float* stT = sT + tid;
+    // Small queues (the later bounce rounds: a few 10^4 rays) are spread thin: with fewer rays than lanes on the device every warp
+    // takes only `perWarp` rays at a time, so a warp's time is the longest of a few traversals (and each of its steps waits on a
+    // few node loads) instead of the longest of 32.
+    const uint32_t totalWarps = gridDim.x * (kTraceThreads / 32);
+    const uint32_t perWarp = min(32u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    const unsigned laneMask = perWarp >= 32u ? 0xffffffffu : ((1u << perWarp) - 1u);
+    const int refillIdle = perWarp >= 32u ? kRefillIdle : 1;
     bool active = false, exhausted = false;
     uint32_t pix = 0;
     RayPrep rp; TravState s;
@@ -200,13 +207,13 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
     rp = prepare_ray(Float3{0, 0, 0}, Float3{0, 1, 0}, sceneBox);
     while (true) {
         // ---- refill idle lanes from the queue ----
-        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        const unsigned idle = __ballot_sync(0xffffffffu, !active) & laneMask;
         if (!exhausted && idle != 0u) {
             const int leader = __ffs(idle) - 1;
             uint32_t base = 0;
             if (lane == leader) base = atomicAdd(fetchPtr, (uint32_t)__popc(idle));
             base = __shfl_sync(0xffffffffu, base, leader);
-            if (!active) {
+            if (!active && ((idle >> lane) & 1u)) {
                 const uint32_t q = base + __popc(idle & ((1u << lane) - 1u));
                 if (q < n) {
                     pix = __ldg(queue + q);
@@ -225,7 +232,10 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
             if (active) {
                 if (trav_step<COUNT>(sc, rp, s, 0, cap, numTri, maxLoop, stL, stT, kTraceThreads)) {
                     B.hit[pix] = make_float4(s.t, s.ua, s.va, __int_as_float(s.tri));
-                    if (COUNT) { nodeVisits += s.nodeVisits; leafTests += s.leafTests; }
+                    if (COUNT) {
+                        nodeVisits += s.nodeVisits; leafTests += s.leafTests;
+                        atomicMax(fetchPtr + 32, (uint32_t)s.it); atomicAdd(fetchPtr + 40, (uint32_t)s.it);      // diagnostics: [40+r] max, [48+r] sum of iterations
+                    }
                     active = false; finishedNow = true;
                 }
             }
@@ -244,7 +254,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
             }
             const unsigned live = __ballot_sync(0xffffffffu, active);
             if (live == 0u) break;
-            if (!exhausted && 32 - __popc(live) >= kRefillIdle) break;
+            if (!exhausted && __popc(laneMask & ~live) >= refillIdle) break;
         }
     }
     if (COUNT && visitCounters) {
@@ -291,10 +301,10 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTrac
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tilesX = (P.width + 7) / 8;
     const int tile = blockIdx.x * (kLogicThreads / 32) + warp;
-    const int ix = (tile % tilesX) * 8 + (lane & 7), jy = (tile / tilesX) * 4 + (lane >> 3), iy = frame_row(P, jy);
+    const int ix = (tile % tilesX) * 8 + (lane & 7), jc = (tile / tilesX) * 4 + (lane >> 3), jy = chunk_row(P, jc), iy = frame_row(P, jy);
     bool emit = false;
     const uint32_t pix = (uint32_t)((size_t)iy * P.width + ix);
-    if (ix < P.width && jy < P.localRows) logic_body(P, B, pix, true, emit);
+    if (ix < P.width && jc < P.chunkRows && jy < P.localRows) logic_body(P, B, pix, true, emit);
     queue_append(emit, pix, B.rayQueue, countOut, lane);
 }
 
@@ -319,14 +329,14 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParam
 
 // rays traced = pixels + every queued ray (src/traverse.cuh:64-72: one TraverseBvh per passed guard)
 __global__ void k_pt_count_rays(const uint32_t* __restrict__ counters, unsigned long long pixels, unsigned long long* out) {
-    out[0] = pixels + counters[0] + counters[1] + counters[2] + counters[3];
+    atomicAdd(out, pixels + counters[0] + counters[1] + counters[2] + counters[3]);      // one add per chunk of the frame
 }
 
 SceneView make_scene_view(const Context& c);   // traverse.cu
 
 static int ensure_wf_buffers(Context& c, WfBuffers& B) {
     const size_t px = (size_t)c.width * c.height;
-    const size_t need = px * (6 * sizeof(float4) + 2 * sizeof(uint32_t)) + 256;
+    const size_t need = px * (6 * sizeof(float4) + 2 * sizeof(uint32_t)) + 256 * Context::kMaxChunks;
     if (c.wfBytes < need) {
         if (c.dWf) cudaFree(c.dWf);
         c.dWf = nullptr; c.wfBytes = 0;
@@ -334,7 +344,7 @@ static int ensure_wf_buffers(Context& c, WfBuffers& B) {
         c.wfBytes = need;
     }
     char* p = reinterpret_cast<char*>(c.dWf);
-    B.counters = reinterpret_cast<uint32_t*>(p); p += 256;
+    B.counters = reinterpret_cast<uint32_t*>(p); p += 256 * Context::kMaxChunks;
     float4** f4[6] = {&B.st0, &B.st1, &B.st2, &B.st3, &B.st4, &B.hit};
     for (auto f : f4) { *f = reinterpret_cast<float4*>(p); p += px * sizeof(float4); }
     B.rayQueue = reinterpret_cast<uint32_t*>(p); p += px * sizeof(uint32_t);
@@ -345,6 +355,46 @@ static int ensure_wf_buffers(Context& c, WfBuffers& B) {
 
 void fill_pathtrace_params(Context& c, PathTraceParams& P);   // pathtrace.cu
 
+// rows of chunk k when the context's local rows are dealt out in 8-row strips, strip s to chunk s % K
+static int chunk_rows(int localRows, int K, int k) {
+    if (K <= 1) return localRows;
+    const int strips = (localRows + 7) / 8;
+    const int mine = strips > k ? (strips - k + K - 1) / K : 0;
+    int rows = mine * 8;
+    if (mine > 0 && (strips - 1) % K == k) rows -= strips * 8 - localRows;
+    return rows;
+}
+
+// One wavefront pipeline (primary, first logic, 4 x (trace, logic), ray count) over the pixels of chunk P.chunk, on `st`.
+static void launch_chunk(Context& c, const PathTraceParams& P, const WfBuffers& B, cudaStream_t st, int smCount) {
+    const int rows = P.chunkRows;
+    const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
+    if (c.countVisits) k_pt_primary<true><<<grid, block, 0, st>>>(P, B);
+    else k_pt_primary<false><<<grid, block, 0, st>>>(P, B);
+    const int tiles = ((c.width + 7) / 8) * ((rows + 3) / 4);
+    k_pt_logic_first<<<(tiles + kLogicThreads / 32 - 1) / (kLogicThreads / 32), kLogicThreads, 0, st>>>(P, B, B.counters + 0);
+    c.launches += 2;
+    // persistent grids sized for the chunk: at most one CTA per 128 pixels, never more than are resident at once
+    static int traceResident = 0;
+    if (!traceResident) {
+        int perSm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_pt_trace<false>, kTraceThreads, 0);
+        traceResident = smCount * (perSm > 0 ? perSm : 4);
+    }
+    const int maxGrid = traceResident;
+    const int want = (int)(((size_t)c.width * rows + 127) / 128);
+    const int traceGrid = want < maxGrid ? (want > 0 ? want : 1) : maxGrid, logicGrid = traceGrid;
+    for (int round = 0; round < 4; ++round) {
+        uint32_t* cnt = B.counters;
+        if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
+        else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
+        k_pt_logic<<<logicGrid, kLogicThreads, 0, st>>>(P, B, cnt + 16 + round, cnt + 24 + round, cnt + round + 1);
+        c.launches += 2;
+    }
+    k_pt_count_rays<<<1, 1, 0, st>>>(B.counters, (unsigned long long)c.width * rows, c.dRayCounter);
+    c.launches += 1;
+}
+
 int launch_pathtrace_wavefront(Context& c) {
     PathTraceParams P{};
     fill_pathtrace_params(c, P);
@@ -353,25 +403,33 @@ int launch_pathtrace_wavefront(Context& c) {
     if (rc) return rc;
     static int smCount = 0;
     if (!smCount) { cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c.device); if (smCount <= 0) smCount = 148; }
-    RTRT_CUDA(c, cudaMemsetAsync(B.counters, 0, 256, c.stream));
+    RTRT_CUDA(c, cudaMemsetAsync(B.counters, 0, 256 * Context::kMaxChunks, c.stream));
     RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));
     const int rows = local_rows(c);
-    const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
-    if (c.countVisits) k_pt_primary<true><<<grid, block, 0, c.stream>>>(P, B);
-    else k_pt_primary<false><<<grid, block, 0, c.stream>>>(P, B);
-    const int tiles = ((c.width + 7) / 8) * ((rows + 3) / 4);
-    k_pt_logic_first<<<(tiles + kLogicThreads / 32 - 1) / (kLogicThreads / 32), kLogicThreads, 0, c.stream>>>(P, B, B.counters + 0);
-    c.launches += 2;
-    const int traceGrid = smCount * 8, logicGrid = smCount * 8;
-    for (int round = 0; round < 4; ++round) {
-        uint32_t* cnt = B.counters;
-        if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
-        else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, c.stream>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
-        k_pt_logic<<<logicGrid, kLogicThreads, 0, c.stream>>>(P, B, cnt + 16 + round, cnt + 24 + round, cnt + round + 1);
-        c.launches += 2;
+    int K = c.ptChunks;
+    if (K > (rows + 7) / 8) K = (rows + 7) / 8;
+    if (K < 1) K = 1;
+    if (K > 1 && !c.chunkFork) {
+        RTRT_CUDA(c, cudaEventCreateWithFlags(&c.chunkFork, cudaEventDisableTiming));
+        for (int k = 0; k < Context::kMaxChunks; ++k) {
+            RTRT_CUDA(c, cudaStreamCreateWithFlags(&c.chunkStream[k], cudaStreamNonBlocking));
+            RTRT_CUDA(c, cudaEventCreateWithFlags(&c.chunkJoin[k], cudaEventDisableTiming));
+        }
     }
-    k_pt_count_rays<<<1, 1, 0, c.stream>>>(B.counters, (unsigned long long)c.width * rows, c.dRayCounter);
-    c.launches += 1;
+    if (K > 1) RTRT_CUDA(c, cudaEventRecord(c.chunkFork, c.stream));
+    size_t queueOff = 0;
+    for (int k = 0; k < K; ++k) {
+        PathTraceParams Pk = P; WfBuffers Bk = B;
+        Pk.chunks = K; Pk.chunk = k; Pk.chunkRows = chunk_rows(rows, K, k);
+        const size_t chunkPx = (size_t)c.width * Pk.chunkRows;
+        Bk.counters = B.counters + 64 * k;
+        Bk.rayQueue = B.rayQueue + queueOff; Bk.shadeQueue = B.shadeQueue + queueOff; Bk.capacity = (uint32_t)chunkPx;
+        queueOff += chunkPx;
+        cudaStream_t st = c.stream;
+        if (k > 0) { st = c.chunkStream[k]; RTRT_CUDA(c, cudaStreamWaitEvent(st, c.chunkFork, 0)); }
+        launch_chunk(c, Pk, Bk, st, smCount);
+        if (k > 0) { RTRT_CUDA(c, cudaEventRecord(c.chunkJoin[k], st)); RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.chunkJoin[k], 0)); }
+    }
     RTRT_CUDA(c, cudaGetLastError());
     return RTRT_OK;
 }
