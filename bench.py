@@ -235,21 +235,28 @@ def run_c5(args, rank, world, local, torch, dist, pkg):
     # rays per step are deterministic (same frame numbers every step): count them once, untimed
     sh.build_bvh()
     rays_rank = 0
+    by_samples = args.partition == "samples" and world > 1
+    if by_samples:
+        rt.set_row_range(0, H); rt.set_row_strips(0, 1, 0)
     for smp in range(spp):
+        if by_samples and smp % world != rank:
+            continue
         rt.set_frame_number(1 + smp); rt.pathtrace(); rays_rank += rt.timings()["rays_traced"]
+    if by_samples:
+        rt.set_row_range(*sh.band); rt.set_row_strips(sh.strip_height, world, rank)
     sampler = ClockSampler(local); sampler.start()
     res = {}
     for name, e2e in (("device", False), ("e2e", True)):
         steps = args.steps if not e2e else max(2, args.steps // 2)
         for _ in range(args.warmup if not e2e else 1):
-            sh.render_progressive(spp)
+            sh.render_progressive(spp, partition=args.partition)
         barrier()
         l0 = rt.timings()["kernel_launches"]
         evs = []
         for _ in range(steps):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
-            sh.render_progressive(spp)
+            sh.render_progressive(spp, partition=args.partition)
             if e2e:
                 rt.read_buffer_into(pkg.BUF_ACCUM_RADIANCE, h_out.data_ptr(), h_out.numel())
             b.record(stream)
@@ -270,9 +277,10 @@ def run_c5(args, rank, world, local, torch, dist, pkg):
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
                 "config": {"workload": f"C5: 3840x2160, {spp} spp progressive path trace (no denoiser), {idx.shape[0]}-tri procedural terrain "
-                                       f"({(idx.shape[0] + 1023) // 1024} batches, global top level), row bands x{world}",
+                                       f"({(idx.shape[0] + 1023) // 1024} batches, global top level), {args.partition}-partitioned x{world}",
                            "width": W, "height": H, "triangles": int(idx.shape[0]), "spp": spp, "rays_per_step": rays_step,
-                           "parallelism": f"row bands x{world}, BVH {args.bvh} per step, NCCL all-gather of the fp32 accumulation buffer",
+                           "parallelism": (f"row strips x{world}, BVH {args.bvh} per step, NCCL all-gather of the fp32 accumulation buffer" if not by_samples else
+                                           f"samples x{world} (rank r renders samples r, r+N, ...), BVH {args.bvh} per step, NCCL all-reduce of the fp32 accumulation buffer"),
                            "l2": "inputs larger than L2 (3.2 GB BVH)", "ms_per_sample": ms_step / spp},
                 "e2e": {"value": rays_step / (e2e_step * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_step, "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": int(h_out.numel()), "note": "static scene: no per-step upload; the accumulated frame is read back"},
@@ -291,6 +299,7 @@ def main():
     ap.add_argument("--bvh", default="rebuild", choices=["rebuild", "broadcast"])
     ap.add_argument("--workload", default="C2", choices=["C2", "C5"])
     ap.add_argument("--spp", type=int, default=C5_SPP)
+    ap.add_argument("--partition", default="samples", choices=["samples", "rows"], help="C5: how the 64 spp are split over the GPUs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-kernels", action="store_true")
     args = ap.parse_args()

@@ -190,17 +190,43 @@ class RowShardedRayTracer:
         self.gather_frame()
 
     # -- progressive mode (BASELINE config 5) ---------------------------------------------------------------------------
-    def render_progressive(self, spp, first_frame=1, rebuild_every_sample=False):
-        """spp path-traced samples of this rank's band accumulated in fp32, then ONE gather of the accumulation buffer.
-        Returns nothing; read RTRT_BUF_ACCUM_RADIANCE (sum in .xyz, sample count in .w)."""
+    def render_progressive(self, spp, first_frame=1, partition="samples"):
+        """spp path-traced samples accumulated in fp32 (rtrt_accumulate); on return RTRT_BUF_ACCUM_RADIANCE holds, on every rank, the
+        sum over all spp samples in .xyz and the sample count in .w.
+        partition="samples": rank r renders the WHOLE frame for the samples s with s % N == r, then one NCCL all-reduce (sum) of the
+                             accumulation buffer (16 B/px).  Per-kernel latency tails do not shrink with the pixel count, so this
+                             scales better than splitting every sample N ways (measured).
+        partition="rows":    every rank renders its row strips of every sample, then one all-gather of the strips."""
+        import torch
+        import torch.distributed as dist
+        if partition not in ("samples", "rows"):
+            raise ValueError("partition must be 'samples' or 'rows'")
         self.build_bvh()
-        for s in range(spp):
-            if rebuild_every_sample and s:
-                self.build_bvh()
-            self.rt.set_frame_number(first_frame + s)
-            self.rt.pathtrace()
-            self.rt.accumulate(reset=(s == 0))
-        self._gather([(L.BUF_ACCUM_RADIANCE, 16)], strips=True)
+        if partition == "rows" or self.world == 1:
+            for s in range(spp):
+                self.rt.set_frame_number(first_frame + s)
+                self.rt.pathtrace()
+                self.rt.accumulate(reset=(s == 0))
+            self._gather([(L.BUF_ACCUM_RADIANCE, 16)], strips=True)
+            return
+        self.rt.set_row_range(0, self.H); self.rt.set_row_strips(0, 1, 0)          # whole frames on every rank
+        try:
+            mine = [s for s in range(spp) if s % self.world == self.rank]
+            for k, s in enumerate(mine):
+                self.rt.set_frame_number(first_frame + s)
+                self.rt.pathtrace()
+                self.rt.accumulate(reset=(k == 0))
+            if not mine:                                                            # more ranks than samples: contribute zeros
+                self.rt.set_frame_number(first_frame); self.rt.pathtrace(); self.rt.accumulate(reset=True)
+            with self._on_stream():
+                t = self._tensor(L.BUF_ACCUM_RADIANCE).view(torch.float32)
+                if not mine:
+                    t.zero_()
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        finally:
+            self.rt.set_row_range(*self.bands[self.rank])
+            if self.strip_height:
+                self.rt.set_row_strips(self.strip_height, self.world, self.rank)
 
 
 def assemble_rows(parts, bands, row_items):

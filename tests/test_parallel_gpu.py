@@ -139,10 +139,13 @@ def _nccl_worker(rank, world, port, bvh_mode, out_dir):
                 full.build_bvh(); full.pathtrace(); full.denoise()
                 for which in (pkg.BUF_RENDER_COLOR, pkg.BUF_HISTORY_COLOR, pkg.BUF_ACCUMULATION_COLOR, pkg.BUF_HISTORY_DEPTH, pkg.BUF_NORMAL):
                     assert np.array_equal(rt.read_buffer(which).view(np.uint8), full.read_buffer(which).view(np.uint8)), f"frame {frame} buffer {which}"
-        sh.render_progressive(4, first_frame=10)
-        rt.sync()
-        acc = rt.read_buffer(pkg.BUF_ACCUM_RADIANCE)
-        assert (acc[:, 3] == 4).all()
+        accs = {}
+        for part in ("rows", "samples"):
+            sh.render_progressive(4, first_frame=10, partition=part)
+            rt.sync()
+            accs[part] = rt.read_buffer(pkg.BUF_ACCUM_RADIANCE).copy()
+            assert (accs[part][:, 3] == 4).all()
+        np.testing.assert_allclose(accs["samples"][:, :3], accs["rows"][:, :3], rtol=1e-5, atol=1e-6)     # same samples, other summation order
         if rank == 0:
             open(os.path.join(out_dir, f"ok_{bvh_mode}"), "w").write("ok")
         rt.cleanup()
