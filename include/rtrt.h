@@ -105,6 +105,10 @@ typedef enum rtrt_buffer {
     RTRT_BUF_SUN,                /* float4[32*32]    (SunBuffer)                                        */
     RTRT_BUF_SUN_CDF,            /* float[32*32]                                                        */
     RTRT_BUF_ACCUM_RADIANCE,     /* float4: sum of colour*albedo over the accumulated samples, .w = count (rtrt_accumulate) */
+    RTRT_BUF_OUTPUT_RGBA8,       /* uchar4[outW*outH]: the tone-mapped, dithered frame CopyToOutput writes (src/kernel.cu:26-59); rtrt_postprocess */
+    RTRT_BUF_COLOR64,            /* half4[w64*h64]: ColorBuffer64, the 1/64-resolution colour the histogram reads                    */
+    RTRT_BUF_EXPOSURE,           /* float[4]: d_exposure = EV, adapted luminance, adapted bright luminance, bright luminance          */
+    RTRT_BUF_HISTOGRAM,          /* uint32[64]: d_histogram                                                                           */
     RTRT_BUF_WF_COUNTERS = 100   /* diagnostics: uint32[64] of the wavefront path tracer: [r] rays of bounce round r, [16+r] hits, [24+r] misses,
                                     with option count_visits: [40+r] max and [48+r] sum of traversal iterations of round r */
 } rtrt_buffer;
@@ -122,6 +126,13 @@ typedef struct rtrt_denoise_params {
 typedef struct rtrt_pass_settings {
     int32_t enableTemporalDenoising, enableLocalSpatialFilter, enableWideSpatialFilter, enableTemporalDenoising2;
 } rtrt_pass_settings;
+/* PostProcessParams (src/settingParams.h:101-116: exposure 1, gain 40, maxWhite 7, gamma 2.2) and the post-processing toggles of
+ * RenderPassSettings (src/settingParams.h:92-99).  Only the default tone mapper (Reinhard extended, luminance) is implemented;
+ * bloom and lens flare (off by default in the reference) are not. */
+typedef struct rtrt_postprocess_params {
+    float exposure, gain, maxWhite, gamma;
+    int32_t enablePostProcess, enableAutoExposure, enableSharpening, enableToneMapping;
+} rtrt_postprocess_params;
 /* SurfaceMaterial (src/kernel.cuh:182-196), 32 bytes; type = SurfaceMaterialType (src/kernel.cuh:172-180) */
 typedef struct rtrt_material { float albedo[3]; uint32_t type; float F0[3]; float alpha; } rtrt_material;
 
@@ -219,6 +230,15 @@ int rtrt_denoise(rtrt_ctx* ctx);
  *      src/temporalDenoising.cuh:1127-1139 in fp32) of the frame just path traced to RTRT_BUF_ACCUM_RADIANCE, rows of the
  *      current row range only; reset != 0 starts a new accumulation. ---- */
 int rtrt_accumulate(rtrt_ctx* ctx, int reset);
+/* ---- RayTracer::PostProcessing (src/postprocessing.cu:5-160, default passes) + CopyToOutput (src/kernel.cu:26-59,
+ *      :369-375) on the frame in RTRT_BUF_RENDER_COLOR: down-scale x3, 64-bin histogram, auto exposure (delta_time_ms = the frame time
+ *      the reference's Timer feeds the eye adaptation with), Catmull-Rom scale to the output size, sharpening, Reinhard-extended
+ *      tone map + gamma, blue-noise dither to RGBA8 -> RTRT_BUF_OUTPUT_RGBA8.  Output size defaults to the render size. ---- */
+int rtrt_set_postprocess_params(rtrt_ctx* ctx, const rtrt_postprocess_params* p_or_null_for_defaults);
+int rtrt_set_output_size(rtrt_ctx* ctx, int32_t width, int32_t height);
+int rtrt_postprocess(rtrt_ctx* ctx, float delta_time_ms);
+/* binary PPM (P6) of RTRT_BUF_OUTPUT_RGBA8, like the reference's writeToPPM frame dump (src/kernel.cu:379-390); synchronises */
+int rtrt_write_ppm(rtrt_ctx* ctx, const char* path);
 /* ---- the three stages in draw() order, then frameNum++ (src/kernel.cu:259-362) ---- */
 int rtrt_render_frame(rtrt_ctx* ctx);
 

@@ -4,14 +4,20 @@
 // Buffer2DManager::init does (src/init.cu:441-584, src/kernel.cuh:344-410) and reproduces the launch sequences of
 // RayTracer::draw (src/kernel.cu:283-354) and RayTracer::TemporalSpatialDenoising (src/denoising.cu:48-186).
 // Built by oracle/refcuda/build_ref.py into oracle/_ref/ together with harness.cu.
-#include "kernel.cuh"
-#include "debugUtil.h"
-#include "scan.cuh"
-#include "sky.cuh"
-#include "settingParams.h"
-#include "pathtrace.cuh"
+#include "kernel_cu.inc"          /* = src/kernel.cu (CopyToOutput, and the includes of kernel.cuh, scan.cuh, sky.cuh, pathtrace.cuh) */
 #include "temporalDenoising.cuh"
+#include "postprocessing.cuh"
 #include <cstring>
+
+GlobalSettings* g_settings = nullptr;      /* extern in src/kernel.cu:8 (defined in src/main.cu:43, which is not part of this build) */
+/* RayTracer::draw / UpdateFrame come along with src/kernel.cu; nothing here calls them.  The members they reference live in
+ * reference .cu files that are not part of this build (bvh.cu, denoising.cu, postprocessing.cu, inputControl.cu) — their launch
+ * sequences are reproduced by the extern "C" functions below — so the loader only needs the symbols to exist. */
+void RayTracer::BuildBvhLevel1() {}
+void RayTracer::BuildBvhLevel2() {}
+void RayTracer::PostProcessing(Int2, Int2) {}
+void RayTracer::InputControlUpdate() {}
+void RayTracer::TemporalSpatialDenoising(Int2, Int2) {}
 
 static_assert(sizeof(Camera) == 176 && sizeof(SurfaceMaterial) == 32 && sizeof(Triangle) == 128 && sizeof(BVHNode) == 64,
               "type shim changed a reference layout");
@@ -20,7 +26,8 @@ static_assert(sizeof(Camera) == 176 && sizeof(SurfaceMaterial) == 32 && sizeof(T
 
 namespace {
 
-enum RefBuf { RB_COLOR, RB_ACCUM, RB_HISTORY, RB_NORMAL, RB_DEPTH, RB_HISTORY_DEPTH, RB_MOTION, RB_NOISE, RB_NOISE16, RB_SKY, RB_SUN, RB_ALBEDO, RB_COUNT };
+enum RefBuf { RB_COLOR, RB_ACCUM, RB_HISTORY, RB_NORMAL, RB_DEPTH, RB_HISTORY_DEPTH, RB_MOTION, RB_NOISE, RB_NOISE16, RB_SKY, RB_SUN, RB_ALBEDO,
+              RB_COLOR4, RB_COLOR16, RB_COLOR64, RB_SCALED, RB_OUTPUT, RB_COUNT };
 
 struct Surf { cudaArray* array = nullptr; SurfObj surf = 0; int w = 0, h = 0, bytes = 0; };
 
@@ -40,6 +47,8 @@ struct RefFrame {
     float *skyPdf = nullptr, *skyCdf = nullptr, *skyTmp = nullptr, *sunPdf = nullptr, *sunCdf = nullptr, *sunTmp = nullptr;
     ConstBuffer cbo = {};
     bool skyConstInit = false;
+    // post-processing (src/init.cu:331-336): exposure[4], histogram[64], the output surface handle in device memory
+    float* dExposure = nullptr; uint* dHistogram = nullptr; SurfObj* dRenderTarget = nullptr; int outW = 0, outH = 0;
 };
 
 int make_surf(Surf& s, cudaChannelFormatDesc d, int w, int h, int bytes) {
@@ -89,7 +98,7 @@ void refcuda_frame_destroy(void* h) {
         for (int l = 0; l < (int)Mipmap::numMipLevels; ++l)
             if (f->texArray[t][l]) { cudaDestroySurfaceObject(f->hAtlas.mipmapTex[t].mip[l]); cudaFreeArray(f->texArray[t][l]); }
     cudaFree(f->skyPdf); cudaFree(f->skyCdf); cudaFree(f->skyTmp); cudaFree(f->sunPdf); cudaFree(f->sunCdf); cudaFree(f->sunTmp);
-    cudaFree(f->dAtlas); cudaFree(f->dMaterials); cudaFree(f->dMaterialsIdx);
+    cudaFree(f->dAtlas); cudaFree(f->dMaterials); cudaFree(f->dMaterialsIdx); cudaFree(f->dExposure); cudaFree(f->dHistogram); cudaFree(f->dRenderTarget);
     for (auto p : f->dTables) cudaFree(p);
     delete f;
 }
@@ -253,6 +262,63 @@ int refcuda_frame_denoise(void* h, int frameNum, const int* passes, const float*
     float ms = 0; CKF(cudaEventElapsedTime(&ms, e0, e1));
     if (ms_out) ms_out[0] = ms;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+}
+
+// RayTracer::PostProcessing with the default pass set (src/postprocessing.cu:16-158: DownScale4 x3, Histogram2, AutoExposure, BicubicScale,
+// SharpeningFilter, ToneMappingReinhardExtended) + the CopyToOutput launch of draw() (src/kernel.cu:369-375), same launch shapes.
+// params = {gain, maxWhite, gamma}; the exposure state persists across calls like d_exposure.
+int refcuda_frame_postprocess(void* h, int frameNum, float deltaTime, int outW, int outH, const float* params, float* ms_out) {
+    RefFrame* f = (RefFrame*)h;
+    const int W = f->W, H = f->H;
+    const UInt2 s4(divRoundUp(W, 4u), divRoundUp(H, 4u)), s16(divRoundUp(s4.x, 4u), divRoundUp(s4.y, 4u)), s64(divRoundUp(s16.x, 4u), divRoundUp(s16.y, 4u));
+    if (!f->dExposure || f->outW != outW || f->outH != outH) {
+        const cudaChannelFormatDesc h4 = cudaCreateChannelDescHalf4(), u4 = cudaCreateChannelDesc<uchar4>();
+        for (int b : {RB_COLOR4, RB_COLOR16, RB_COLOR64, RB_SCALED, RB_OUTPUT})
+            if (f->buf[b].surf) { cudaDestroySurfaceObject(f->buf[b].surf); cudaFreeArray(f->buf[b].array); f->buf[b] = Surf(); }
+        if (make_surf(f->buf[RB_COLOR4], h4, s4.x, s4.y, 8) || make_surf(f->buf[RB_COLOR16], h4, s16.x, s16.y, 8) || make_surf(f->buf[RB_COLOR64], h4, s64.x, s64.y, 8) ||
+            make_surf(f->buf[RB_SCALED], h4, outW, outH, 8) || make_surf(f->buf[RB_OUTPUT], u4, outW, outH, 4)) return -1;
+        if (!f->dExposure) {
+            CKF(cudaMalloc(&f->dExposure, 4 * sizeof(float))); CKF(cudaMalloc(&f->dHistogram, 64 * sizeof(uint))); CKF(cudaMalloc(&f->dRenderTarget, sizeof(SurfObj)));
+            const float init[4] = {1.0f, 1.0f, 1.0f, 1.0f};                                            // src/init.cu:332-333
+            CKF(cudaMemcpy(f->dExposure, init, sizeof(init), cudaMemcpyHostToDevice));
+        }
+        CKF(cudaMemcpy(f->dRenderTarget, &f->buf[RB_OUTPUT].surf, sizeof(SurfObj), cudaMemcpyHostToDevice));
+        f->outW = outW; f->outH = outH;
+    }
+    PostProcessParams pp; pp.gain = params[0]; pp.maxWhite = params[1]; pp.gamma = params[2];
+    f->cbo.frameNum = frameNum;
+    const Int2 bufferDim(W, H), outputDim(outW, outH);
+    const dim3 blockDim8(8, 8, 1), gridDim8(divRoundUp(W, 8), divRoundUp(H, 8), 1), gridDim4(divRoundUp(s4.x, 8u), divRoundUp(s4.y, 8u), 1),
+               gridDim16(divRoundUp(s16.x, 8u), divRoundUp(s16.y, 8u), 1), scaleGrid(divRoundUp(outW, 8), divRoundUp(outH, 8), 1);
+    auto S = [&](int b) { return f->buf[b].surf; };
+    cudaEvent_t e0, e1; CKF(cudaEventCreate(&e0)); CKF(cudaEventCreate(&e1));
+    CKF(cudaMemset(f->dHistogram, 0, 64 * sizeof(uint)));                                             // src/kernel.cu:278
+    CKF(cudaDeviceSynchronize());
+    CKF(cudaEventRecord(e0));
+    DownScale4<<<gridDim8, blockDim8>>>(S(RB_COLOR), S(RB_COLOR4), bufferDim);
+    DownScale4<<<gridDim4, blockDim8>>>(S(RB_COLOR4), S(RB_COLOR16), Int2(s4.x, s4.y));
+    DownScale4<<<gridDim16, blockDim8>>>(S(RB_COLOR16), S(RB_COLOR64), Int2(s16.x, s16.y));
+    Histogram2<<<1, dim3(min(s64.x, 32u), min(s64.y, 32u), 1)>>>(f->dHistogram, S(RB_COLOR64), Int2(s64.x, s64.y));
+    AutoExposure<<<1, 1>>>(f->dExposure, f->dHistogram, (float)(s64.x * s64.y), deltaTime, pp.gain);
+    BicubicScale<<<scaleGrid, blockDim8>>>(S(RB_SCALED), S(RB_COLOR), outputDim, bufferDim);
+    SharpeningFilter<<<scaleGrid, blockDim8>>>(S(RB_SCALED), outputDim);
+    ToneMappingReinhardExtended<<<scaleGrid, blockDim8>>>(S(RB_SCALED), outputDim, f->dExposure, pp);
+    CopyToOutput<<<scaleGrid, blockDim8>>>(f->dRenderTarget, S(RB_SCALED), f->randGen, f->cbo, outputDim);
+    CKF(cudaEventRecord(e1));
+    CKF(cudaEventSynchronize(e1));
+    CKF(cudaGetLastError());
+    float ms = 0; CKF(cudaEventElapsedTime(&ms, e0, e1));
+    if (ms_out) ms_out[0] = ms;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+}
+
+int refcuda_frame_get_exposure(void* h, float* exposure4, unsigned int* histogram64) {
+    RefFrame* f = (RefFrame*)h;
+    if (!f->dExposure) return -2;
+    CKF(cudaMemcpy(exposure4, f->dExposure, 4 * sizeof(float), cudaMemcpyDeviceToHost));
+    CKF(cudaMemcpy(histogram64, f->dHistogram, 64 * sizeof(uint), cudaMemcpyDeviceToHost));
     return 0;
 }
 

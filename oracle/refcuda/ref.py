@@ -82,7 +82,8 @@ def traverse(bvh, rays, iterations=1, fmad=False):
 # ---------------------------------------------------------------------------------------------------------------------
 # stage 2 / 3 / sky: PathTrace, TemporalSpatialDenoising, Sky + SkySun + Scan (oracle/refcuda/harness_frame.cu)
 # ---------------------------------------------------------------------------------------------------------------------
-RB_COLOR, RB_ACCUM, RB_HISTORY, RB_NORMAL, RB_DEPTH, RB_HISTORY_DEPTH, RB_MOTION, RB_NOISE, RB_NOISE16, RB_SKY, RB_SUN, RB_ALBEDO = range(12)
+RB_COLOR, RB_ACCUM, RB_HISTORY, RB_NORMAL, RB_DEPTH, RB_HISTORY_DEPTH, RB_MOTION, RB_NOISE, RB_NOISE16, RB_SKY, RB_SUN, RB_ALBEDO, \
+    RB_COLOR4, RB_COLOR16, RB_COLOR64, RB_SCALED, RB_OUTPUT = range(17)
 COLOR_DTYPE = np.dtype([("rgb", "<f2", 3), ("mask", "<u2")])
 
 
@@ -174,14 +175,34 @@ class RefFrame:
                                                 C.c_void_p(pp.ctypes.data) if pp is not None else None, C.byref(ms)), "denoise")
         return ms.value
 
-    _SHAPES = {RB_COLOR: COLOR_DTYPE, RB_ACCUM: COLOR_DTYPE, RB_HISTORY: COLOR_DTYPE, RB_NORMAL: np.dtype(("<f2", 4)), RB_ALBEDO: np.dtype(("<f2", 4)),
+    def postprocess(self, frame_num, delta_time_ms=16.0, out_size=None, gain=40.0, max_white=7.0, gamma=2.2):
+        """PostProcessing (default passes) + CopyToOutput; returns the elapsed ms.  Read RB_OUTPUT / RB_SCALED / RB_COLOR64 afterwards."""
+        ow, oh = out_size or (self.W, self.H)
+        self.out_size = (ow, oh)
+        pp = np.array([gain, max_white, gamma], np.float32)
+        ms = C.c_float()
+        self._ck(self.lib.refcuda_frame_postprocess(self.h, C.c_int(frame_num), C.c_float(delta_time_ms), C.c_int(ow), C.c_int(oh),
+                                                    C.c_void_p(pp.ctypes.data), C.byref(ms)), "postprocess")
+        return ms.value
+
+    def exposure(self):
+        e = np.zeros(4, np.float32); hst = np.zeros(64, np.uint32)
+        self._ck(self.lib.refcuda_frame_get_exposure(self.h, C.c_void_p(e.ctypes.data), C.c_void_p(hst.ctypes.data)), "get_exposure")
+        return e, hst
+
+    _SHAPES = {RB_COLOR4: np.dtype(("<f2", 4)), RB_COLOR16: np.dtype(("<f2", 4)), RB_COLOR64: np.dtype(("<f2", 4)), RB_SCALED: np.dtype(("<f2", 4)),
+               RB_OUTPUT: np.dtype(("u1", 4)),
+               RB_COLOR: COLOR_DTYPE, RB_ACCUM: COLOR_DTYPE, RB_HISTORY: COLOR_DTYPE, RB_NORMAL: np.dtype(("<f2", 4)), RB_ALBEDO: np.dtype(("<f2", 4)),
                RB_DEPTH: np.dtype("<f2"), RB_HISTORY_DEPTH: np.dtype("<f2"), RB_MOTION: np.dtype(("<f2", 2)), RB_NOISE: np.dtype("<f2"),
                RB_NOISE16: np.dtype("<f2"), RB_SKY: np.dtype(("<f4", 4)), RB_SUN: np.dtype(("<f4", 4))}
 
     def _count(self, which):
         W, H = self.W, self.H
+        c4 = lambda v: (v + 3) // 4
+        ow, oh = getattr(self, "out_size", (W, H))
         return {RB_NOISE: ((W + 7) // 8) * ((H + 7) // 8), RB_NOISE16: ((W + 15) // 16) * ((H + 15) // 16), RB_SKY: 512 * 256,
-                RB_SUN: 32 * 32}.get(which, W * H)
+                RB_SUN: 32 * 32, RB_COLOR4: c4(W) * c4(H), RB_COLOR16: c4(c4(W)) * c4(c4(H)), RB_COLOR64: c4(c4(c4(W))) * c4(c4(c4(H))),
+                RB_SCALED: ow * oh, RB_OUTPUT: ow * oh}.get(which, W * H)
 
     def read(self, which):
         dt = self._SHAPES[which]

@@ -18,6 +18,7 @@ BUF_TRIANGLES, BUF_AABBS, BUF_MORTON_PRESORT, BUF_MORTON, BUF_REORDER_IDX, BUF_B
     BUF_TLAS_AABBS, BUF_TLAS_MORTON_PRESORT, BUF_TLAS_MORTON, BUF_TLAS_REORDER_IDX, BUF_TLAS_BVH_NODES, BUF_TRI_PERMUTATION = range(12)
 BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCUMULATION_COLOR, BUF_HISTORY_COLOR, \
     BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF, BUF_ACCUM_RADIANCE = range(32, 47)
+BUF_OUTPUT_RGBA8, BUF_COLOR64, BUF_EXPOSURE, BUF_HISTOGRAM = range(47, 51)
 BUF_WF_COUNTERS = 100
 
 
@@ -61,6 +62,12 @@ class PassSettings(C.Structure):   # src/settingParams.h:87-91
                                          "enableWideSpatialFilter", "enableTemporalDenoising2")]
 
 
+class PostprocessParams(C.Structure):   # src/settingParams.h:92-99, 112-116
+    _fields_ = [("exposure", C.c_float), ("gain", C.c_float), ("maxWhite", C.c_float), ("gamma", C.c_float),
+                ("enablePostProcess", C.c_int32), ("enableAutoExposure", C.c_int32), ("enableSharpening", C.c_int32),
+                ("enableToneMapping", C.c_int32)]
+
+
 # every symbol include/rtrt.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "rtrt_abi_version": (C.c_int, []),
@@ -99,6 +106,10 @@ SYMBOLS = {
     "rtrt_denoise": (C.c_int, [C.c_void_p]),
     "rtrt_render_frame": (C.c_int, [C.c_void_p]),
     "rtrt_accumulate": (C.c_int, [C.c_void_p, C.c_int]),
+    "rtrt_set_postprocess_params": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rtrt_set_output_size": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "rtrt_postprocess": (C.c_int, [C.c_void_p, C.c_float]),
+    "rtrt_write_ppm": (C.c_int, [C.c_void_p, C.c_char_p]),
     "rtrt_set_row_strips": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
 }
 

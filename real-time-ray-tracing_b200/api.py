@@ -39,7 +39,9 @@ for _b, _dt in ((L.BUF_RENDER_COLOR, COLOR_DTYPE), (L.BUF_NORMAL, np.dtype(("<f2
                 (L.BUF_ACCUMULATION_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_COLOR, COLOR_DTYPE), (L.BUF_HISTORY_DEPTH, np.dtype("<f2")),
                 (L.BUF_NOISE_LEVEL, np.dtype("<f2")), (L.BUF_NOISE_LEVEL_16, np.dtype("<f2")),
                 (L.BUF_SKY, np.dtype(("<f4", 4))), (L.BUF_SKY_CDF, np.dtype("<f4")), (L.BUF_SUN, np.dtype(("<f4", 4))),
-                (L.BUF_SUN_CDF, np.dtype("<f4")), (L.BUF_ACCUM_RADIANCE, np.dtype(("<f4", 4))), (L.BUF_WF_COUNTERS, np.dtype("<u4"))):
+                (L.BUF_SUN_CDF, np.dtype("<f4")), (L.BUF_ACCUM_RADIANCE, np.dtype(("<f4", 4))), (L.BUF_WF_COUNTERS, np.dtype("<u4")),
+                (L.BUF_OUTPUT_RGBA8, np.dtype(("u1", 4))), (L.BUF_COLOR64, np.dtype(("<f2", 4))), (L.BUF_EXPOSURE, np.dtype("<f4")),
+                (L.BUF_HISTOGRAM, np.dtype("<u4"))):
     BUFFER_DTYPES[_b] = _dt
 MAT_LAMBERTIAN_DIFFUSE, MAT_PERFECT_REFLECTION, MAT_GLASS, MAT_MICROFACET_REFLECTION, MAT_EMISSIVE, MAT_SKY = range(6)
 
@@ -225,6 +227,19 @@ class RayTracer:
     def accumulate(self, reset=False):
         """Progressive mode: add colour x albedo of the last path-traced frame to BUF_ACCUM_RADIANCE (rows of the row range)."""
         self._check(self._lib.rtrt_accumulate(self._h, int(reset)))
+
+    def set_postprocess_params(self, params=None):
+        self._check(self._lib.rtrt_set_postprocess_params(self._h, C.byref(params) if params is not None else None))
+
+    def set_output_size(self, w, h):
+        self._check(self._lib.rtrt_set_output_size(self._h, w, h))
+
+    def postprocess(self, delta_time_ms=16.0):
+        """RayTracer::PostProcessing (src/postprocessing.cu:5-160, default passes) + CopyToOutput (src/kernel.cu:26-59) -> BUF_OUTPUT_RGBA8."""
+        self._check(self._lib.rtrt_postprocess(self._h, float(delta_time_ms)))
+
+    def write_ppm(self, path):
+        self._check(self._lib.rtrt_write_ppm(self._h, str(path).encode()))
 
     def draw(self):
         """RayTracer::draw for the hot path: BuildBvhLevel1/2 -> PathTrace -> denoise, frameNum++ (src/kernel.cu:259-362)."""

@@ -98,6 +98,11 @@ static int ensure_ray_stage(Context& c, uint32_t n) {
 static void rtrt_set_sky_params_defaults(rtrt_sky_params* p) {       // src/settingParams.h:41-45
     p->timeOfDay = 0.25f; p->sunAxisAngle = 45.0f; p->skyScalar = 0.01f; p->sunScalar = 0.01f; p->sunAngle = 0.6f;
 }
+static void rtrt_postprocess_defaults(rtrt_postprocess_params* p) {          // src/settingParams.h:92-99, 112-116
+    p->exposure = 1.0f; p->gain = 40.0f; p->maxWhite = 7.0f; p->gamma = 2.2f;
+    p->enablePostProcess = 1; p->enableAutoExposure = 1; p->enableSharpening = 1; p->enableToneMapping = 1;
+}
+
 static void rtrt_set_denoise_defaults(rtrt_denoise_params* d, rtrt_pass_settings* s) {   // src/settingParams.h:144-157, 87-91
     d->local_denoise_sigma_normal = 100.0f; d->local_denoise_sigma_depth = 0.1f; d->local_denoise_sigma_material = 100.0f;
     d->large_denoise_sigma_normal = 100.0f; d->large_denoise_sigma_depth = 0.01f; d->large_denoise_sigma_material = 100.0f;
@@ -131,6 +136,7 @@ int rtrt_create(const rtrt_config* cfg, int device, rtrt_ctx** out) {
     c.width = c.cfg.width; c.height = c.cfg.height;
     rtrt_set_sky_params_defaults(&c.skyParams);
     rtrt_set_denoise_defaults(&c.denoiseParams, &c.passSettings);
+    rtrt_postprocess_defaults(&c.postParams);
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     if (cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     for (auto& e : c.ev) { cudaEventCreate(&e[0]); cudaEventCreate(&e[1]); }
@@ -333,6 +339,10 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         case RTRT_BUF_NOISE_LEVEL: p = c.dNoise; b = (size_t)((c.gbufW + 7) / 8) * ((c.gbufH + 7) / 8) * 2; break;
         case RTRT_BUF_NOISE_LEVEL_16: p = c.dNoise16; b = (size_t)((c.gbufW + 15) / 16) * ((c.gbufH + 15) / 16) * 2; break;
         case RTRT_BUF_ACCUM_RADIANCE: p = c.dAccumRadiance; b = px * 16; break;
+        case RTRT_BUF_OUTPUT_RGBA8: p = c.dOutRgba; b = (size_t)c.ppOutW * c.ppOutH * 4; break;
+        case RTRT_BUF_COLOR64: p = c.dColor64; b = (size_t)c.ppW64 * c.ppH64 * 8; break;
+        case RTRT_BUF_EXPOSURE: p = c.dExposure; b = c.dExposure ? 16 : 0; break;
+        case RTRT_BUF_HISTOGRAM: p = c.dExposure ? (void*)((float*)c.dExposure + 4) : nullptr; b = c.dExposure ? 256 : 0; break;
         case RTRT_BUF_WF_COUNTERS: p = c.dWf; b = c.dWf ? 256 : 0; break;
         case RTRT_BUF_SKY: p = c.dSky; b = sizeof(float) * 4 * kSkySize; break;
         case RTRT_BUF_SKY_CDF: p = c.dSkyCdf; b = sizeof(float) * kSkySize; break;
@@ -530,6 +540,46 @@ int rtrt_denoise(rtrt_ctx* ctx) {
     RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_DENOISE][1], c.stream));
     c.evPending[STAGE_DENOISE] = true;
     return RTRT_OK;
+}
+
+int rtrt_set_postprocess_params(rtrt_ctx* ctx, const rtrt_postprocess_params* p) {
+    CTX_OR_FAIL(ctx);
+    if (p) ctx->c.postParams = *p; else rtrt_postprocess_defaults(&ctx->c.postParams);
+    if (!(ctx->c.postParams.gamma > 0.0f)) { rtrt_postprocess_defaults(&ctx->c.postParams); return ctx->c.fail(RTRT_ERR_ARG, "rtrt_set_postprocess_params: gamma must be > 0"); }
+    return RTRT_OK;
+}
+
+int rtrt_set_output_size(rtrt_ctx* ctx, int32_t w, int32_t h) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (w < 8 || h < 8 || w > 16384 || h > 16384) return c.fail(RTRT_ERR_ARG, "rtrt_set_output_size: size out of range");
+    c.outW = w; c.outH = h;
+    return RTRT_OK;
+}
+
+int rtrt_postprocess(rtrt_ctx* ctx, float delta_time_ms) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    return launch_postprocess(c, delta_time_ms);
+}
+
+int rtrt_write_ppm(rtrt_ctx* ctx, const char* path) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    if (!path) return c.fail(RTRT_ERR_ARG, "rtrt_write_ppm: null path");
+    if (!c.dOutRgba) return c.fail(RTRT_ERR_STATE, "rtrt_write_ppm: no post-processed frame (call rtrt_postprocess)");
+    const size_t n = (size_t)c.ppOutW * c.ppOutH;
+    std::vector<unsigned char> rgba(n * 4), rgb(n * 3);
+    RTRT_CUDA(c, cudaMemcpyAsync(rgba.data(), c.dOutRgba, n * 4, cudaMemcpyDeviceToHost, c.stream));
+    RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
+    for (size_t i = 0; i < n; ++i) { rgb[3 * i] = rgba[4 * i]; rgb[3 * i + 1] = rgba[4 * i + 1]; rgb[3 * i + 2] = rgba[4 * i + 2]; }
+    FILE* f = fopen(path, "wb");
+    if (!f) return c.fail(RTRT_ERR_IO, "rtrt_write_ppm: cannot open file");
+    fprintf(f, "P6\n%d %d\n255\n", c.ppOutW, c.ppOutH);
+    const bool ok = fwrite(rgb.data(), 1, rgb.size(), f) == rgb.size();
+    fclose(f);
+    return ok ? RTRT_OK : c.fail(RTRT_ERR_IO, "rtrt_write_ppm: short write");
 }
 
 int rtrt_accumulate(rtrt_ctx* ctx, int reset) {

@@ -68,6 +68,10 @@ struct Context {
     void* dNoise = nullptr; void* dNoise16 = nullptr; void* dColorTmp = nullptr; void* dGuide = nullptr;
     int gbufW = 0, gbufH = 0;
     void* dAccumRadiance = nullptr; size_t accumRadiancePx = 0;      // progressive fp32 accumulation (rtrt_accumulate)
+    // post-processing (postprocess.cu): output (screen) size, RGBA8 frame, 1/64 colour, exposure[4] + histogram[64]
+    int outW = 0, outH = 0, ppOutW = 0, ppOutH = 0, ppW64 = 0, ppH64 = 0;
+    void* dOutRgba = nullptr; void* dColor64 = nullptr; void* dExposure = nullptr;
+    rtrt_postprocess_params postParams{};
     unsigned long long* dRayCounter = nullptr;
     rtrt_denoise_params denoiseParams{}; rtrt_pass_settings passSettings{};
 
@@ -103,6 +107,7 @@ int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int an
 int launch_pathtrace(Context& c);
 int launch_denoise(Context& c);
 int launch_accumulate(Context& c, int reset);
+int launch_postprocess(Context& c, float deltaTimeMs);   // postprocess.cu
 int local_rows(const Context& c);            // rows of the frame this context path-traces (band or strips)
 int ensure_frame_resources(Context& c);      // frame.cu: G-buffers, tables, default materials/textures, sky regeneration
 void free_frame_resources(Context& c);

@@ -224,6 +224,7 @@ void free_frame_resources(Context& c) {
     for (int t = 0; t < 2; ++t) { if (c.dTexMem[t]) cudaFree(c.dTexMem[t]); c.dTexMem[t] = nullptr; }
     dfree2(c.dRayCounter);
     if (c.dWf) { cudaFree(c.dWf); c.dWf = nullptr; c.wfBytes = 0; }
+    dfree2(c.dOutRgba); dfree2(c.dColor64); dfree2(c.dExposure);
 }
 
 // Texture slot upload + mip chain (2x2 box in float, truncating store: MipmapGen src/mipgen.cu:121-139; init-time work)

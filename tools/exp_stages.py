@@ -34,6 +34,8 @@ out["pathtrace_ms"] = timeit(pt)
 out["rays"] = rt.timings()["rays_traced"]
 def dn(i): rt.set_frame_number(2 + i); rt.denoise()
 out["denoise_ms"] = timeit(dn)
+def pp(i): rt.postprocess(16.0)
+out["postprocess_ms"] = timeit(pp)
 out["pathtrace_mrays_s"] = out["rays"] / out["pathtrace_ms"] / 1e3
 out["primary_mrays_s"] = rays.shape[0] / out["traverse_primary_ms"] / 1e3
 try:
@@ -63,6 +65,8 @@ try:
                         rf.pathtrace(cam, fr)
                         dn_ms.append(rf.denoise(fr))
                     out[tag + "denoise_ms"] = float(np.median(dn_ms[2:]))
+                    if hasattr(ref.load(), "refcuda_frame_postprocess"):
+                        out[tag + "postprocess_ms"] = float(np.median([rf.postprocess(fr, 16.0) for fr in range(1, 7)][2:]))
         if ref.available(fmad=True):
             rb2 = ref.build_bvh(pos, nrm, idx, iterations=6, fmad=True)
             _, ms2 = ref.traverse(rb2, rays, iterations=6, fmad=True)
