@@ -202,7 +202,17 @@ int rtrt_traverse_host(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_h
 int rtrt_set_camera(rtrt_ctx* ctx, const void* camera_blob, size_t bytes, int reset_history);
 int rtrt_load_camera_file(rtrt_ctx* ctx, const char* path);          /* LoadCameraFromFile src/inputControl.cu:133-150 */
 int rtrt_save_camera_file(rtrt_ctx* ctx, const char* path);          /* SaveCameraToFile   src/inputControl.cu:115-131 */
+/* renderWidth/renderHeight of the next frame (src/kernel.cu:74,100).  Storage is grow-only: any size up to the largest one seen
+ * (create the context at maxWidth x maxHeight like src/init.cu:55-61) re-uses the buffers and KEEPS the temporal history, which the
+ * next rtrt_denoise samples with its own size as `historyDim` (src/kernel.cu:83-84,266; src/temporalDenoising.cuh:812,837).
+ * Buffers read through rtrt_get_buffer are compact (row stride = the size they were written at). */
 int rtrt_set_render_size(rtrt_ctx* ctx, int32_t width, int32_t height);
+/* The dynamic-resolution controller of RayTracer::UpdateFrame (src/kernel.cu:78-101), as a pure function: given the current
+ * render width and the last frame time it returns the next render size (width snapped to 16, clamped to [minWidth, maxWidth],
+ * height = width/16*9).  With cfg->useDynamicResolution == 0 the size is returned unchanged (height from cur_height).
+ * The caller applies it with rtrt_set_render_size and must set Camera.resolution to match (src/kernel.cu:100-101). */
+int rtrt_dynamic_resolution_step(const rtrt_config* cfg, int32_t cur_width, int32_t cur_height, float delta_time_ms,
+                                 int32_t* new_width, int32_t* new_height);
 int rtrt_set_frame_number(rtrt_ctx* ctx, int32_t frame_num);         /* cbo.frameNum (seeds the blue-noise sample index) */
 int rtrt_set_sky_params(rtrt_ctx* ctx, const rtrt_sky_params* p);    /* NULL = defaults; sky maps regenerate lazily (src/kernel.cu:289-308) */
 int rtrt_get_sun(rtrt_ctx* ctx, float* sun_dir3, float* sun_angle_cos_theta_max);

@@ -3,8 +3,8 @@
 ORACLE — TEST INFRASTRUCTURE ONLY.
 Parity status: stage 1 (LBVH build) and the traversal are PINNED against the reference's own CUDA kernels compiled for
 sm_100 (oracle/refcuda -> oracle/_ref/librefcuda.so, tests/test_refcuda_gpu.py: bit-exact at 10 240 / 65 536 / 1 047 552
-triangles).  Shading (path trace) and denoise remain unpinned: the reference ships no golden vectors for them and their
-kernels need cudaArray surfaces + assets that are missing blobs.
+triangles); sky maps, one PathTrace launch and the denoiser sequence are pinned against the reference kernels within the
+tolerances of DESIGN.md §2 (oracle/refcuda/harness_frame.cu, tests/test_refcuda_frame_gpu.py).
 """
 import ctypes as C
 import os
@@ -249,14 +249,38 @@ DENOISE_DEFAULTS = np.array([100.0, 0.1, 100.0, 100.0, 0.01, 100.0, 100.0, 0.1, 
 
 
 class DenoiseState:
-    """History carried from frame to frame (AccumulationColorBuffer, HistoryColorBuffer, HistoryDepthBuffer)."""
+    """History carried from frame to frame (AccumulationColorBuffer, HistoryColorBuffer, HistoryDepthBuffer).
+    `resize` changes the render size of the next frames and keeps the history images at the size they were written
+    (historyRenderWidth/Height, src/kernel.cu:83-84,266)."""
 
     def __init__(self, width, height):
         n = width * height
         self.W, self.H = width, height
         self.accum = np.zeros(n, COLOR_DTYPE); self.history_color = np.zeros(n, COLOR_DTYPE); self.history_depth = np.zeros(n, np.float16)
-        self.noise8 = np.zeros(((height + 7) // 8) * ((width + 7) // 8), np.float16)
-        self.noise16 = np.zeros(((height + 15) // 16) * ((width + 15) // 16), np.float16)
+        self.accum_dim = (width, height); self.history_dim = (width, height)
+        self._alloc_noise()
+
+    def _alloc_noise(self):
+        self.noise8 = np.zeros(((self.H + 7) // 8) * ((self.W + 7) // 8), np.float16)
+        self.noise16 = np.zeros(((self.H + 15) // 16) * ((self.W + 15) // 16), np.float16)
+
+    def resize(self, width, height):
+        self.W, self.H = width, height
+        self._alloc_noise()
+
+
+def dynamic_resolution_step(cur_width, delta_time_ms, target_fps=60.0, min_width=640, max_width=3840):
+    """RayTracer::UpdateFrame's controller, src/kernel.cu:78-101, in float32 arithmetic: returns (renderWidth, renderHeight)."""
+    f32 = np.float32
+    dt, fps = f32(delta_time_ms), f32(target_fps)
+    w = int(cur_width)
+    high, low = f32(1000.0) / (fps - f32(2)), f32(1000.0) / (fps + f32(2))
+    if high < dt or low > dt:
+        ratio = np.sqrt((f32(1000.0) / fps) / dt, dtype=f32)
+        w = int(f32(w) * ratio)                              # int *= float truncates toward zero
+    w = w + (-(w % 16) if w % 16 < 8 else 16 - w % 16)
+    w = min(max(w, int(min_width)), int(max_width))          # clampi
+    return w, (w // 16) * 9
 
 
 def denoise(state, frame_num, color, normal, depth, motion, albedo, params=None, passes=(1, 1, 1, 1), threads=None):
@@ -268,9 +292,21 @@ def denoise(state, frame_num, color, normal, depth, motion, albedo, params=None,
     motion = np.ascontiguousarray(motion, np.float16); albedo = np.ascontiguousarray(albedo, np.float16)
     p = np.ascontiguousarray(DENOISE_DEFAULTS if params is None else params, np.float32)
     ps = np.ascontiguousarray(passes, np.int32)
-    rc = lib.orc_denoise(C.c_int(state.W), C.c_int(state.H), C.c_int(frame_num), _p(p), _p(ps), _p(out), _p(normal), _p(depth), _p(motion),
-                         _p(albedo), _p(state.accum), _p(state.history_color), _p(state.history_depth), _p(state.noise8), _p(state.noise16),
-                         C.c_int(threads or default_threads()))
+    n = state.W * state.H
+    assert out.size == n, "G-buffers must have the state's current render size"
+    same = state.accum_dim == (state.W, state.H) and state.history_dim == (state.W, state.H)
+    accum_out = state.accum if same else np.zeros(n, COLOR_DTYPE)
+    hist_out = state.history_color if same else np.zeros(n, COLOR_DTYPE)
+    hdepth_out = state.history_depth if same else np.zeros(n, np.float16)
+    if not same:                                             # passes that are switched off leave the old image (and its size) in place
+        if not passes[0]: accum_out = state.accum
+        if not passes[3]: hist_out = state.history_color; hdepth_out = state.history_depth
+    rc = lib.orc_denoise_hist(C.c_int(state.W), C.c_int(state.H), C.c_int(state.accum_dim[0]), C.c_int(state.accum_dim[1]),
+                              C.c_int(state.history_dim[0]), C.c_int(state.history_dim[1]), C.c_int(frame_num), _p(p), _p(ps), _p(out),
+                              _p(normal), _p(depth), _p(motion), _p(albedo), _p(state.accum), _p(state.history_color), _p(accum_out),
+                              _p(hist_out), _p(hdepth_out), _p(state.noise8), _p(state.noise16), C.c_int(threads or default_threads()))
+    if passes[0]: state.accum = accum_out; state.accum_dim = (state.W, state.H)
+    if passes[3]: state.history_color = hist_out; state.history_depth = hdepth_out; state.history_dim = (state.W, state.H)
     if rc:
         raise RuntimeError(f"orc_denoise failed: {rc}")
     return out

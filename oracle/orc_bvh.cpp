@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // Stage 1: two-level LBVH build, restating
 //   src/updateGeometry.cuh:13-27   MortonCode3D
 //   src/updateGeometry.cuh:65-262  UpdateSceneGeometry<256,4>

@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // Stage 3: the reference's temporal + spatial denoiser with PING-PONG semantics (the reference filters in place,
 // so its own output is race dependent — src/temporalDenoising.cuh:556,607), restating
 //   src/denoising.cu:48-186           pass sequence and toggles
@@ -295,9 +295,13 @@ extern "C" {
 // half4, depth = half, motion = half2.  color is filtered "in place" from the caller's point of view (final result is
 // written back to `color`); accum / historyColor / historyDepth are read as the previous frame's and overwritten.
 // passes: [enableTemporalDenoising, enableLocalSpatialFilter, enableWideSpatialFilter, enableTemporalDenoising2]
-int orc_denoise(int W, int H, int frameNum, const float* params11, const int* passes4,
-                void* color, const void* normal, const void* depth, const void* motion, const void* albedo,
-                void* accum, void* historyColor, void* historyDepth, void* noise8, void* noise16, int threads) {
+// Dynamic resolution (src/kernel.cu:83-84,266): accum / historyColor are the previous frame's images at THEIR sizes
+// (accumW x accumH, histW x histH = historyDim of src/denoising.cu:62,178); the images of this frame are written, compact at W x H,
+// to accumOut / historyColorOut / historyDepthOut (may alias the inputs only when the sizes are equal).
+int orc_denoise_hist(int W, int H, int accumW, int accumH, int histW, int histH, int frameNum, const float* params11, const int* passes4,
+                     void* color, const void* normal, const void* depth, const void* motion, const void* albedo,
+                     const void* accum, const void* historyColor, void* accumOut, void* historyColorOut, void* historyDepthOut,
+                     void* noise8, void* noise16, int threads) {
     DenoiseParams p{params11[0], params11[1], params11[2], params11[3], params11[4], params11[5], params11[6], params11[7], params11[8], params11[9], params11[10]};
     Frame f{W, H, (const Px4*)normal, (const h16*)depth, (const h16*)motion, (const Px4*)albedo};
     const size_t n = (size_t)W * H;
@@ -305,13 +309,13 @@ int orc_denoise(int W, int H, int frameNum, const float* params11, const int* pa
     std::vector<Px4> a((Px4*)color, (Px4*)color + n), b(n);
     Px4* cur = a.data(); Px4* nxt = b.data();
     auto swap = [&]() { Px4* t = cur; cur = nxt; nxt = t; };
-    Img accumImg{W, H, (const Px4*)accum}, histImg{W, H, (const Px4*)historyColor};
+    Img accumImg{accumW, accumH, (const Px4*)accum}, histImg{histW, histH, (const Px4*)historyColor};
     if (passes4[0] && frameNum != 1) { temporal_filter(f, Img{W, H, cur}, accumImg, nxt, p, threads); swap(); }
     if (passes4[1]) {
         noise_levels(f, Img{W, H, cur}, (h16*)noise8, (h16*)noise16);
         spatial7x7(f, Img{W, H, cur}, nxt, (const h16*)noise16, frameNum, p, threads); swap();
     }
-    if (passes4[0]) std::memcpy(accum, cur, n * sizeof(Px4));                          // CopyToHistoryColorBuffer
+    if (passes4[0]) std::memcpy(accumOut, cur, n * sizeof(Px4));                       // CopyToHistoryColorBuffer
     if (passes4[2]) {
         noise_levels(f, Img{W, H, cur}, (h16*)noise8, (h16*)noise16);
         for (int S : {3, 6, 12}) { spatial5x5(f, Img{W, H, cur}, nxt, (const h16*)noise16, S, p, threads); swap(); }
@@ -319,11 +323,18 @@ int orc_denoise(int W, int H, int frameNum, const float* params11, const int* pa
     apply_albedo(f, Img{W, H, cur}, nxt, threads); swap();
     if (passes4[3]) {
         if (frameNum != 1) { temporal_filter2(f, Img{W, H, cur}, histImg, nxt, threads); swap(); }
-        std::memcpy(historyColor, cur, n * sizeof(Px4));                                // CopyToHistoryColorDepthBuffer
-        std::memcpy(historyDepth, depth, n * sizeof(h16));
+        std::memcpy(historyColorOut, cur, n * sizeof(Px4));                             // CopyToHistoryColorDepthBuffer
+        std::memcpy(historyDepthOut, depth, n * sizeof(h16));
     }
     std::memcpy(color, cur, n * sizeof(Px4));
     return 0;
+}
+
+int orc_denoise(int W, int H, int frameNum, const float* params11, const int* passes4,
+                void* color, const void* normal, const void* depth, const void* motion, const void* albedo,
+                void* accum, void* historyColor, void* historyDepth, void* noise8, void* noise16, int threads) {
+    return orc_denoise_hist(W, H, W, H, W, H, frameNum, params11, passes4, color, normal, depth, motion, albedo, accum, historyColor,
+                            accum, historyColor, historyDepth, noise8, noise16, threads);
 }
 
 }  // extern "C"

@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // Stage 2: the path-trace megakernel, one pixel at a time on the CPU, restating
 //   src/pathtrace.cuh:11-128         PathTrace
 //   src/raygen.cuh:7-63              GenerateRay, GetRayConeWidth

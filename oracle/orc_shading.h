@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // Shading side of the path tracer: samplers, environment lookups, BSDFs, light sampling, restating
 //   src/sampler.cuh:293-341,498-584  boundary functors, SampleBicubicSmoothStep(+Lod)
 //   src/sky.cuh:33-88                EqualAreaMap / EqualAreaMapCone

@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // BSDFs + light sampling + blue noise: src/bsdf.cuh, src/light.cuh, src/blueNoiseRandGen.h:119-146
 #pragma once
 #include "orc_shading.h"

@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // Environment inputs of the path tracer (regenerated only when the sky parameters change), restating
 //   src/kernel.cu:121-124,289-308   sun direction, regeneration sequence, sunAngleCosThetaMax
 //   src/sky.cuh:91-319              Hosek-Wilkie sky radiance (10 bands), solar disc radiance, Sky / SkySun kernels

@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // C entry point for batched ray traversal: one TraverseBvh (src/traverse.h:107-253) per ray with the
 // state initialisation of RaySceneIntersect (src/traverse.cuh:86-101).
 #include "orc_traverse.h"

@@ -1,4 +1,4 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (parity unpinned; see orc_types.h header).
+// ORACLE — TEST INFRASTRUCTURE ONLY (parity pinned against oracle/_ref; see orc_types.h header).
 // Stage 2 core: two-level stack traversal + watertight triangle + robust box test, restating
 //   src/geometry.cuh:375-472   max_dim / sign_mask / xorf / RayTriangleWatertight
 //   src/geometry.cuh:497-616   RayBoxIntersectionHelper / RayAABBIntersect / RayAabbPairIntersect

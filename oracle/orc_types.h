@@ -1,5 +1,7 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY.  Parity status: UNPINNED (the reference ships no golden
-// vectors, KATs or runnable CPU path for this hot path).
+// ORACLE — TEST INFRASTRUCTURE ONLY.  Parity status: PINNED against the reference's own CUDA kernels compiled for sm_100
+// (oracle/refcuda -> oracle/_ref/librefcuda.so): build + traversal bit-exact, sky / PathTrace / denoise within the tolerances
+// of DESIGN.md §2 (tests/test_refcuda_gpu.py, tests/test_refcuda_frame_gpu.py).  The reference ships no golden vectors, KATs or
+// CPU path for this hot path.
 //
 // CPU restatement of the reference's hot-path arithmetic (wangkepfe/Real-Time-Ray-Tracing).
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may

@@ -32,7 +32,8 @@ enum RefBuf { RB_COLOR, RB_ACCUM, RB_HISTORY, RB_NORMAL, RB_DEPTH, RB_HISTORY_DE
 struct Surf { cudaArray* array = nullptr; SurfObj surf = 0; int w = 0, h = 0, bytes = 0; };
 
 struct RefFrame {
-    int W = 0, H = 0;
+    int W = 0, H = 0;                         // renderWidth/Height of the current frame (<= the surface size they were created with)
+    int histW = 0, histH = 0;                 // historyRenderWidth/Height (src/kernel.cu:83-84)
     Surf buf[RB_COUNT];
     // textures: slot -> mip levels (src/texture.h:14-25)
     cudaArray* texArray[MipmapTextureCount][Mipmap::numMipLevels] = {};
@@ -69,7 +70,7 @@ extern "C" {
 
 int refcuda_frame_create(int W, int H, void** out) {
     RefFrame* f = new RefFrame();
-    f->W = W; f->H = H;
+    f->W = W; f->H = H; f->histW = W; f->histH = H;
     const cudaChannelFormatDesc h4 = cudaCreateChannelDescHalf4(), h2 = cudaCreateChannelDescHalf2(), h1 = cudaCreateChannelDescHalf1(),
                                 f4 = cudaCreateChannelDesc<float4>();
     // src/init.cu:473-500
@@ -224,7 +225,7 @@ int refcuda_frame_pathtrace(void* h, const void* camera, const void* historyCame
 int refcuda_frame_denoise(void* h, int frameNum, const int* passes, const float* params, float* ms_out) {
     RefFrame* f = (RefFrame*)h;
     const int W = f->W, H = f->H;
-    const Int2 bufferDim(W, H), historyDim(W, H);
+    const Int2 bufferDim(W, H), historyDim(f->histW, f->histH);
     DenoisingParams dp;
     if (params) memcpy(&dp.local_denoise_sigma_normal, params, 11 * sizeof(float));
     f->cbo.frameNum = frameNum;
@@ -256,6 +257,7 @@ int refcuda_frame_denoise(void* h, int frameNum, const int* passes, const float*
             TemporalFilter2<<<gridDim8, blockDim8>>>(cbo, S(RB_COLOR), S(RB_HISTORY), S(RB_NORMAL), S(RB_DEPTH), S(RB_HISTORY_DEPTH), S(RB_MOTION), S(RB_NOISE), bufferDim, historyDim);
         CopyToHistoryColorDepthBuffer<<<gridDim8, blockDim8>>>(S(RB_COLOR), S(RB_DEPTH), S(RB_HISTORY), S(RB_HISTORY_DEPTH), bufferDim);
     }
+    f->histW = W; f->histH = H;               // historyRenderWidth/Height of the next frame (src/kernel.cu:83-84)
     CKF(cudaEventRecord(e1));
     CKF(cudaEventSynchronize(e1));
     CKF(cudaGetLastError());
@@ -319,6 +321,35 @@ int refcuda_frame_get_exposure(void* h, float* exposure4, unsigned int* histogra
     if (!f->dExposure) return -2;
     CKF(cudaMemcpy(exposure4, f->dExposure, 4 * sizeof(float), cudaMemcpyDeviceToHost));
     CKF(cudaMemcpy(histogram64, f->dHistogram, 64 * sizeof(uint), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+// Dynamic resolution: UpdateFrame (src/kernel.cu:83-101) keeps the surfaces at their creation size and renders the next frame into
+// their top-left renderWidth x renderHeight corner; the previous size becomes historyDim for TemporalSpatialDenoising (src/kernel.cu:266,360).
+int refcuda_frame_set_render_size(void* h, int W, int H) {
+    RefFrame* f = (RefFrame*)h;
+    if (W < 1 || H < 1 || W > f->buf[RB_COLOR].w || H > f->buf[RB_COLOR].h) return -2;
+    f->W = W; f->H = H;                      // historyDim stays the size of the last denoised frame (set at the end of refcuda_frame_denoise)
+    return 0;
+}
+
+// top-left w x hgt corner of a surface <-> compact host rows
+int refcuda_frame_read_region(void* h, int which, void* host, int w, int hgt) {
+    RefFrame* f = (RefFrame*)h;
+    if (which < 0 || which >= RB_COUNT) return -2;
+    const Surf& s = f->buf[which];
+    if (w < 1 || hgt < 1 || w > s.w || hgt > s.h) return -3;
+    CKF(cudaDeviceSynchronize());
+    CKF(cudaMemcpy2DFromArray(host, (size_t)w * s.bytes, s.array, 0, 0, (size_t)w * s.bytes, hgt, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int refcuda_frame_write_region(void* h, int which, const void* host, int w, int hgt) {
+    RefFrame* f = (RefFrame*)h;
+    if (which < 0 || which >= RB_COUNT) return -2;
+    const Surf& s = f->buf[which];
+    if (w < 1 || hgt < 1 || w > s.w || hgt > s.h) return -3;
+    CKF(cudaMemcpy2DToArray(s.array, 0, 0, host, (size_t)w * s.bytes, (size_t)w * s.bytes, hgt, cudaMemcpyHostToDevice));
     return 0;
 }
 

@@ -210,6 +210,21 @@ class RefFrame:
         self._ck(self.lib.refcuda_frame_read(self.h, C.c_int(which), C.c_void_p(out.ctypes.data), C.c_size_t(out.nbytes)), "read")
         return out
 
+    def set_render_size(self, w, h):
+        """Dynamic resolution: the next frames use the top-left w x h corner of the surfaces (src/kernel.cu:83-101)."""
+        self._ck(self.lib.refcuda_frame_set_render_size(self.h, C.c_int(w), C.c_int(h)), "set_render_size")
+        self.rW, self.rH = w, h
+
+    def read_region(self, which, w, h):
+        out = np.zeros(w * h, self._SHAPES[which])
+        self._ck(self.lib.refcuda_frame_read_region(self.h, C.c_int(which), C.c_void_p(out.ctypes.data), C.c_int(w), C.c_int(h)), "read_region")
+        return out
+
+    def write_region(self, which, data, w, h):
+        a = np.ascontiguousarray(data)
+        assert a.nbytes == w * h * np.dtype(self._SHAPES[which]).itemsize
+        self._ck(self.lib.refcuda_frame_write_region(self.h, C.c_int(which), C.c_void_p(a.ctypes.data), C.c_int(w), C.c_int(h)), "write_region")
+
     def write(self, which, data):
         a = np.ascontiguousarray(data)
         self._ck(self.lib.refcuda_frame_write(self.h, C.c_int(which), C.c_void_p(a.ctypes.data), C.c_size_t(a.nbytes)), "write")

@@ -94,6 +94,7 @@ SYMBOLS = {
     "rtrt_load_camera_file": (C.c_int, [C.c_void_p, C.c_char_p]),
     "rtrt_save_camera_file": (C.c_int, [C.c_void_p, C.c_char_p]),
     "rtrt_set_render_size": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "rtrt_dynamic_resolution_step": (C.c_int, [C.POINTER(Config), C.c_int32, C.c_int32, C.c_float, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "rtrt_set_frame_number": (C.c_int, [C.c_void_p, C.c_int32]),
     "rtrt_set_sky_params": (C.c_int, [C.c_void_p, C.POINTER(SkyParams)]),
     "rtrt_get_sun": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),

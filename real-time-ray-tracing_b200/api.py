@@ -71,6 +71,15 @@ def config_defaults():
     return cfg
 
 
+def dynamic_resolution_step(cfg, cur_width, cur_height, delta_time_ms):
+    """The dynamic-resolution controller of RayTracer::UpdateFrame (src/kernel.cu:78-101): next (width, height)."""
+    w, h = C.c_int32(0), C.c_int32(0)
+    rc = L.load().rtrt_dynamic_resolution_step(C.byref(cfg), int(cur_width), int(cur_height), float(delta_time_ms), C.byref(w), C.byref(h))
+    if rc:
+        raise RtrtError(rc, "rtrt_dynamic_resolution_step: bad argument")
+    return w.value, h.value
+
+
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 

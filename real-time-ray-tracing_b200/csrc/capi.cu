@@ -451,6 +451,23 @@ int rtrt_set_render_size(rtrt_ctx* ctx, int32_t w, int32_t h) {
     return RTRT_OK;
 }
 
+// src/kernel.cu:78-101 (int *= float truncates; clampi; height follows the width at 16:9)
+int rtrt_dynamic_resolution_step(const rtrt_config* cfg, int32_t curW, int32_t curH, float deltaTime, int32_t* outW, int32_t* outH) {
+    if (!cfg || !outW || !outH || curW <= 0 || !(deltaTime > 0.0f) || !(cfg->targetFps > 2.0f)) return RTRT_ERR_ARG;
+    if (!cfg->useDynamicResolution) { *outW = curW; *outH = curH; return RTRT_OK; }
+    int renderWidth = curW;
+    const float targetFrameTimeHigh = 1000.0f / (cfg->targetFps - 2), targetFrameTimeLow = 1000.0f / (cfg->targetFps + 2);
+    if (targetFrameTimeHigh < deltaTime || targetFrameTimeLow > deltaTime) {
+        float ratio = (1000.0f / cfg->targetFps) / deltaTime;
+        ratio = sqrtf(ratio);
+        renderWidth = (int)((float)renderWidth * ratio);
+    }
+    renderWidth = renderWidth + ((renderWidth % 16 < 8) ? (-renderWidth % 16) : (16 - renderWidth % 16));
+    renderWidth = renderWidth < cfg->minWidth ? cfg->minWidth : (renderWidth > cfg->maxWidth ? cfg->maxWidth : renderWidth);
+    *outW = renderWidth; *outH = (renderWidth / 16) * 9;
+    return RTRT_OK;
+}
+
 int rtrt_set_frame_number(rtrt_ctx* ctx, int32_t n) { CTX_OR_FAIL(ctx); ctx->c.frameNum = n; return RTRT_OK; }
 
 int rtrt_set_sky_params(rtrt_ctx* ctx, const rtrt_sky_params* p) {

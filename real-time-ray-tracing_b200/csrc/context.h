@@ -66,11 +66,13 @@ struct Context {
     void* dColor = nullptr; void* dNormal = nullptr; void* dAlbedo = nullptr; void* dDepth = nullptr; void* dMotion = nullptr;
     void* dAccum = nullptr; void* dHistoryColor = nullptr; void* dHistoryDepth = nullptr; void* dHistoryAlbedo = nullptr;
     void* dNoise = nullptr; void* dNoise16 = nullptr; void* dColorTmp = nullptr; void* dGuide = nullptr;
-    int gbufW = 0, gbufH = 0;
+    int gbufW = 0, gbufH = 0;                 // layout (row stride) of the current frame's buffers
+    int gbufCapW = 0, gbufCapH = 0;           // allocated capacity; a smaller render size re-uses the storage and keeps the history
+    int accumW = 0, accumH = 0, histW = 0, histH = 0;   // sizes the two history images were written at (historyDim, src/kernel.cu:83-84,266)
     void* dAccumRadiance = nullptr; size_t accumRadiancePx = 0;      // progressive fp32 accumulation (rtrt_accumulate)
     // post-processing (postprocess.cu): output (screen) size, RGBA8 frame, 1/64 colour, exposure[4] + histogram[64]
     int outW = 0, outH = 0, ppOutW = 0, ppOutH = 0, ppW64 = 0, ppH64 = 0;
-    void* dOutRgba = nullptr; void* dColor64 = nullptr; void* dExposure = nullptr;
+    void* dOutRgba = nullptr; void* dColor64 = nullptr; void* dExposure = nullptr; size_t ppCap64 = 0;
     rtrt_postprocess_params postParams{};
     unsigned long long* dRayCounter = nullptr;
     rtrt_denoise_params denoiseParams{}; rtrt_pass_settings passSettings{};

@@ -20,6 +20,7 @@ namespace rtrt {
 
 struct DnParams {
     int W, H, frameNum;
+    int aW, aH, hW, hH;                       // historyDim of the accumulation / history colour images (src/denoising.cu:62,178)
     int by0;                                  // first 16-row block row this launch covers (row-band mode; 0 = whole frame)
     float local_n, local_d, local_m, large_n, large_d, large_m, temp_n, temp_d, temp_m, thr_local, thr_large;
     const ushort4* __restrict__ normal; const __half* __restrict__ depth; const __half2* __restrict__ motion;
@@ -198,15 +199,15 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
             if (huv.x < 0 || huv.y < 0 || huv.x > 1.0f || huv.y > 1.0f) {
                 result = px_pack(filtered, maskValue);
             } else {
-                Float3 hist = sample_history(accum, P.W, P.H, huv);
+                Float3 hist = sample_history(accum, P.aW, P.aH, huv);
                 Float3 hy = rgb_to_ycocg(hist);
                 hy = Float3{clampf(hy.x, nMin.x, nMax.x), clampf(hy.y, nMin.y, nMax.y), clampf(hy.z, nMin.z, nMax.z)};
                 hist = ycocg_to_rgb(hy);
                 const float lumaCurrent = rgb_to_ycocg(colorValue).x;
                 float discard = 0.0f;
-                const int hx = (int)floorf(huv.x * P.W), hyy = (int)floorf(huv.y * P.H);
+                const int hx = (int)floorf(huv.x * P.aW), hyy = (int)floorf(huv.y * P.aH);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) discard += (maskValue != ld_px(accum, P.W, P.H, hx + (i & 1), hyy + (i >> 1)).w) ? 1.0f : 0.0f;
+                for (int i = 0; i < 4; ++i) discard += (maskValue != ld_px(accum, P.aW, P.aH, hx + (i & 1), hyy + (i >> 1)).w) ? 1.0f : 0.0f;
                 discard /= 4.0f;
                 hist = hist * (1.0f - discard) + filtered * discard;
                 const float lumaHistory = rgb_to_ycocg(hist).x;
@@ -367,15 +368,15 @@ __global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort
         const float2 mv = __half22float2(__ldg(P.motion + (size_t)y * P.W + x));
         const Float2 huv = (Float2{(float)x, (float)y} + 0.5f) * Float2{1.0f / (float)P.W, 1.0f / (float)P.H} + (Float2{mv.x, mv.y} - 0.5f);
         if (!(huv.x < 0 || huv.y < 0 || huv.x > 1.0f || huv.y > 1.0f)) {
-            Float3 ch = sample_history(histPrev, P.W, P.H, huv);
+            Float3 ch = sample_history(histPrev, P.hW, P.hH, huv);
             Float3 hy = rgb_to_ycocg(ch);
             hy = Float3{clampf(hy.x, nMin.x, nMax.x), clampf(hy.y, nMin.y, nMax.y), clampf(hy.z, nMin.z, nMax.z)};
             ch = ycocg_to_rgb(hy);
             const float lumaCurrent = rgb_to_ycocg(colorValue).x;
             float discard = 0.0f;
-            const int hx = (int)floorf(huv.x * P.W), hyy = (int)floorf(huv.y * P.H);
+            const int hx = (int)floorf(huv.x * P.hW), hyy = (int)floorf(huv.y * P.hH);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) discard += (kOne != ld_px(histPrev, P.W, P.H, hx + (i & 1), hyy + (i >> 1)).w) ? 1.0f : 0.0f;
+            for (int i = 0; i < 4; ++i) discard += (kOne != ld_px(histPrev, P.hW, P.hH, hx + (i & 1), hyy + (i >> 1)).w) ? 1.0f : 0.0f;
             discard /= 4.0f;
             if (discard != 1.0f) {
                 ch = ch * (1.0f - discard) + colorValue * discard;
@@ -438,6 +439,8 @@ int launch_denoise(Context& c) {
     if (!c.dColor || c.gbufW != c.width || c.gbufH != c.height) return c.fail(RTRT_ERR_STATE, "rtrt_denoise: no path-traced frame to denoise");
     DnParams P{};
     P.W = c.width; P.H = c.height; P.frameNum = c.frameNum;
+    P.aW = c.accumW ? c.accumW : c.width; P.aH = c.accumH ? c.accumH : c.height;
+    P.hW = c.histW ? c.histW : c.width; P.hH = c.histH ? c.histH : c.height;
     const rtrt_denoise_params& d = c.denoiseParams;
     P.local_n = d.local_denoise_sigma_normal; P.local_d = d.local_denoise_sigma_depth; P.local_m = d.local_denoise_sigma_material;
     P.large_n = d.large_denoise_sigma_normal; P.large_d = d.large_denoise_sigma_depth; P.large_m = d.large_denoise_sigma_material;
@@ -495,6 +498,8 @@ int launch_denoise(Context& c) {
     else k_dn_final<false><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, tf2 ? histNext : nullptr, reinterpret_cast<__half*>(c.dHistoryDepth));
     swap(); c.launches++;
     if (band && tf2) RTRT_CUDA(c, cudaMemcpyAsync(c.dHistoryDepth, c.dDepth, (size_t)c.width * c.height * sizeof(__half), cudaMemcpyDeviceToDevice, c.stream));
+    if (temporal) { c.accumW = c.width; c.accumH = c.height; }
+    if (tf2) { c.histW = c.width; c.histH = c.height; }
     if (tf2) { void* t = c.dHistoryColor; c.dHistoryColor = c.dHistoryAlbedo; c.dHistoryAlbedo = t; }       // history ping-pong
     (void)bytes;
     c.dColor = cur; c.dColorTmp = oth;          // RTRT_BUF_RENDER_COLOR now names the denoised frame

@@ -213,7 +213,8 @@ static void free_gbuffers(Context& c) {
                      &c.dHistoryAlbedo, &c.dNoise, &c.dNoise16, &c.dColorTmp, &c.dGuide};
     for (void** b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
     if (c.dAccumRadiance) { cudaFree(c.dAccumRadiance); c.dAccumRadiance = nullptr; c.accumRadiancePx = 0; }
-    c.gbufW = c.gbufH = 0;
+    c.gbufW = c.gbufH = c.gbufCapW = c.gbufCapH = 0;
+    c.accumW = c.accumH = c.histW = c.histH = 0;
 }
 
 void free_frame_resources(Context& c) {
@@ -337,11 +338,13 @@ int ensure_frame_resources(Context& c) {
             int rc = set_texture(c, t, 1, 1, t == 0 ? a : n);
             if (rc) return rc;
         }
-    if (c.gbufW != c.width || c.gbufH != c.height) {
+    if (c.width > c.gbufCapW || c.height > c.gbufCapH) {
+        // grow: capacity = the largest size seen so far (create the context at maxWidth x maxHeight to avoid this, src/init.cu:55-61)
         RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
+        const int capW = c.width > c.gbufCapW ? c.width : c.gbufCapW, capH = c.height > c.gbufCapH ? c.height : c.gbufCapH;
         free_gbuffers(c);
-        const size_t px = (size_t)c.width * c.height;
-        const size_t n8 = (size_t)((c.width + 7) / 8) * ((c.height + 7) / 8), n16 = (size_t)((c.width + 15) / 16) * ((c.height + 15) / 16);
+        const size_t px = (size_t)capW * capH;
+        const size_t n8 = (size_t)((capW + 7) / 8) * ((capH + 7) / 8), n16 = (size_t)((capW + 15) / 16) * ((capH + 15) / 16);
         struct { void** p; size_t bytes; } plan[] = {
             {&c.dColor, px * 8}, {&c.dNormal, px * 8}, {&c.dAlbedo, px * 8}, {&c.dDepth, px * 2}, {&c.dMotion, px * 4},
             {&c.dAccum, px * 8}, {&c.dHistoryColor, px * 8}, {&c.dHistoryDepth, px * 2}, {&c.dHistoryAlbedo, px * 8},
@@ -350,8 +353,11 @@ int ensure_frame_resources(Context& c) {
             RTRT_CUDA(c, cudaMalloc(e.p, e.bytes));
             RTRT_CUDA(c, cudaMemsetAsync(*e.p, 0, e.bytes, c.stream));
         }
-        c.gbufW = c.width; c.gbufH = c.height;
+        c.gbufCapW = capW; c.gbufCapH = capH;
     }
+    // Dynamic resolution (src/kernel.cu:78-101): within the capacity a new render size only changes the row stride of the buffers
+    // written from now on; the history images keep the layout they were written with (accumW x accumH, histW x histH).
+    c.gbufW = c.width; c.gbufH = c.height;
     if (c.rowEnd <= c.rowBegin || c.rowEnd > c.height) { c.rowBegin = 0; c.rowEnd = c.height; }
     return RTRT_OK;
 }

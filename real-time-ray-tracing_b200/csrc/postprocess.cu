@@ -254,14 +254,19 @@ int launch_postprocess(Context& c, float deltaTimeMs) {
     if (!c.dColor || c.gbufW != c.width || c.gbufH != c.height) return c.fail(RTRT_ERR_STATE, "rtrt_postprocess: no frame to process");
     const int oW = c.outW > 0 ? c.outW : c.width, oH = c.outH > 0 ? c.outH : c.height;
     const int w1 = (c.width + 3) / 4, h1 = (c.height + 3) / 4, w2 = (w1 + 3) / 4, h2 = (h1 + 3) / 4, w3 = (w2 + 3) / 4, h3 = (h2 + 3) / 4;
-    if (!c.dOutRgba || c.ppOutW != oW || c.ppOutH != oH || c.ppW64 != w3 || c.ppH64 != h3) {
+    if (!c.dOutRgba || c.ppOutW != oW || c.ppOutH != oH) {
         if (c.dOutRgba) cudaFree(c.dOutRgba);
-        if (c.dColor64) cudaFree(c.dColor64);
-        c.dOutRgba = c.dColor64 = nullptr;
+        c.dOutRgba = nullptr;
         RTRT_CUDA(c, cudaMalloc(&c.dOutRgba, (size_t)oW * oH * 4));
-        RTRT_CUDA(c, cudaMalloc(&c.dColor64, (size_t)w3 * h3 * 8));
-        c.ppOutW = oW; c.ppOutH = oH; c.ppW64 = w3; c.ppH64 = h3;
+        c.ppOutW = oW; c.ppOutH = oH;
     }
+    if (!c.dColor64 || (size_t)w3 * h3 > c.ppCap64) {                                   // grow-only: the render size may change every frame
+        if (c.dColor64) cudaFree(c.dColor64);
+        c.dColor64 = nullptr;
+        RTRT_CUDA(c, cudaMalloc(&c.dColor64, (size_t)w3 * h3 * 8));
+        c.ppCap64 = (size_t)w3 * h3;
+    }
+    c.ppW64 = w3; c.ppH64 = h3;
     if (!c.dExposure) {
         RTRT_CUDA(c, cudaMalloc(&c.dExposure, 4 * sizeof(float) + 64 * sizeof(uint32_t)));
         const float init[4] = {1.0f, 1.0f, 1.0f, 1.0f};                                  // src/init.cu:331-333

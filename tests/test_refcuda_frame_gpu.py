@@ -188,3 +188,62 @@ def test_denoise_pass_toggles_match_reference_kernels(pkg, orc, ref, scene):
                 rf.write(ref.RB_DEPTH, g["depth"]); rf.write(ref.RB_MOTION, g["motion"])
                 rt.denoise(); rf.denoise(frame, passes=passes)
                 assert rel_rmse(rt.read_buffer(pkg.BUF_RENDER_COLOR)["rgb"].astype(np.float32), rf.read(ref.RB_COLOR)["rgb"].astype(np.float32)) <= 2e-2, (passes, frame)
+
+
+def test_dynamic_resolution_history_rescale_matches_reference_kernels(pkg, orc, ref, scene):
+    """the render size changes between frames (src/kernel.cu:78-101) while the temporal history keeps the size it was
+    written at; TemporalFilter / TemporalFilter2 sample it with historyDim (src/temporalDenoising.cuh:812,837,1028,1053).
+    The reference keeps its surfaces at the maximum size and filters the top-left corner, so near the right / bottom edge of a
+    shrunk frame its spatial filters and bicubic history taps read stale texels of older, larger frames (surface clamp addressing
+    clamps to the SURFACE, not to bufferDim); the product and the oracle clamp to the image.  Interior pixels are compared."""
+    maxW, maxH = 640, 360
+    sizes = [(640, 360), (640, 360), (480, 270), (480, 270), (560, 315), (640, 360), (640, 360)]
+    pos, nrm, idx, ob, rb = scene
+    st = orc.DenoiseState(maxW, maxH)
+    margin = 64
+    with pkg.RayTracer(maxW, maxH) as rt, ref.RefFrame(maxW, maxH) as rf:
+        rt.set_mesh(pos, idx, nrm); rt.build_bvh()
+        shrunk = False
+        for frame, (w, h) in enumerate(sizes, start=1):
+            rt.set_render_size(w, h); rf.set_render_size(w, h); st.resize(w, h)
+            cam = pkg.scenes.make_camera((0.3 * frame, 30, -60 + 0.2 * frame), 0.01 * frame, -0.4, w, h)
+            rt.set_camera(cam, reset_history=(frame == 1)); rt.set_frame_number(frame)
+            rt.pathtrace()
+            g = product_gbuffers(rt, pkg)
+            assert g["color"].size == w * h
+            for which, key in [(ref.RB_COLOR, "color"), (ref.RB_NORMAL, "normal"), (ref.RB_ALBEDO, "albedo"), (ref.RB_DEPTH, "depth"), (ref.RB_MOTION, "motion")]:
+                rf.write_region(which, g[key], w, h)
+            rt.denoise(); rf.denoise(frame)
+            o = orc.denoise(st, frame, g["color"].view(orc.COLOR_DTYPE), g["normal"], g["depth"], g["motion"], g["albedo"])
+            shrunk = shrunk or (w, h) != (maxW, maxH)
+            m = margin if shrunk else 0
+            crop = lambda a: a.reshape(h, w, -1)[: h - m, : w - m].astype(np.float32)
+            for name, pb, rb_ in [("colour", pkg.BUF_RENDER_COLOR, ref.RB_COLOR), ("accum", pkg.BUF_ACCUMULATION_COLOR, ref.RB_ACCUM),
+                                  ("history", pkg.BUF_HISTORY_COLOR, ref.RB_HISTORY)]:
+                got = rt.read_buffer(pb); want = rf.read_region(rb_, w, h)
+                assert got.size == w * h
+                assert np.isfinite(want["rgb"].astype(np.float32)).all()
+                assert rel_rmse(crop(got["rgb"]), crop(want["rgb"])) <= 2e-2, f"product {name}, frame {frame} at {w}x{h}"
+            assert rel_rmse(crop(o["rgb"]), crop(rf.read_region(ref.RB_COLOR, w, h)["rgb"])) <= 2e-2, f"oracle, frame {frame} at {w}x{h}"
+            # product and oracle clamp alike: they must agree over the whole image, edges included
+            assert rel_rmse(rt.read_buffer(pkg.BUF_RENDER_COLOR)["rgb"].astype(np.float32), o["rgb"].astype(np.float32)) <= 2e-2, f"product vs oracle, frame {frame}"
+            np.testing.assert_array_equal(rt.read_buffer(pkg.BUF_HISTORY_DEPTH), rf.read_region(ref.RB_HISTORY_DEPTH, w, h))
+
+
+def test_render_size_change_keeps_history(pkg, scene):
+    """A size change inside the allocated capacity must not reset the temporal history (the old behaviour re-allocated and zeroed)."""
+    pos, nrm, idx, ob, rb = scene
+    out = {}
+    for keep in (True, False):
+        with pkg.RayTracer(320, 180) as rt:
+            rt.set_mesh(pos, idx, nrm); rt.build_bvh()
+            for frame, (w, h) in enumerate([(320, 180), (320, 180), (256, 144)], start=1):
+                rt.set_render_size(w, h)
+                rt.set_camera(pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, w, h), reset_history=(frame == 1)); rt.set_frame_number(frame)
+                rt.pathtrace()
+                if frame == 3 and not keep:
+                    rt.set_frame_number(1)           # frameNum 1 = "no history" (src/denoising.cu:50)
+                rt.denoise()
+            out[keep] = rt.read_buffer(pkg.BUF_RENDER_COLOR)["rgb"].astype(np.float32)
+    assert out[True].shape == (256 * 144, 3)
+    assert rel_rmse(out[True], out[False]) > 1e-2        # the history did contribute to the resized frame
