@@ -158,9 +158,22 @@ int rtrt_set_mesh(rtrt_ctx* ctx, const float* pos, const float* nrm_or_null, con
  * vertex buffer in place every frame, cf. MeshDisplace src/kernel.cu:139-226).  Pointers are borrowed. */
 int rtrt_set_mesh_device(rtrt_ctx* ctx, const float* d_pos, const float* d_nrm, const uint32_t* d_idx,
                          uint32_t num_vertices, uint32_t num_triangles);
-/* Mesh file of LoadScene-era format `uint32 triCount; Triangle[triCount]` (src/init.cu:28-50,
- * tool/meshProcessor.cpp:204-208), 128-byte triangles. */
+/* Mesh file `uint32 triCount; Triangle[triCount]` (LoadTrianglesFromFile src/init.cu:28-50, written by
+ * tool/meshProcessor.cpp:204-208): 128-byte triangles, or the legacy 64-byte layout (positions only, e.g. the shipped
+ * resources/models/test.bin; vertex normals are then generated) — told apart by the file size. */
 int rtrt_set_mesh_bin(rtrt_ctx* ctx, const char* path);
+/* Wavefront OBJ (the reference reads it through Assimp: LoadScene src/fileUtils.cu:16-80): v / vn / f, corners v, v/vt, v//vn,
+ * v/vt/vn, negative indices, polygons fanned from the first corner; triangles in file order; normals used only when every
+ * corner has one (mesh->HasNormals()), else generated.  RTRT_ERR_IO with the line number on malformed input. */
+int rtrt_set_mesh_obj(rtrt_ctx* ctx, const char* path);
+/* The offline mesh tool (tool/meshProcessor.cpp:146-215): writes the current mesh as a `.bin`.  presort != 0 orders the triangles by
+ * the 60-bit Morton code of their centroid (computed and sorted on the device, stable); legacy64 != 0 writes the 64-byte layout. */
+int rtrt_write_mesh_bin(rtrt_ctx* ctx, const char* path, int presort, int legacy64);
+/* The two readers without a context (pure host code, usable without a GPU): `.obj` by extension, anything else `.bin`.
+ * On success *tri_pos (and *tri_nrm, NULL when the file carries no normals) are malloc'ed arrays of 9 floats per triangle,
+ * released with rtrt_mesh_file_free.  On failure the message is copied to err (may be NULL). */
+int rtrt_mesh_file_read(const char* path, float** tri_pos, float** tri_nrm, uint32_t* num_tris, char* err, size_t err_len);
+void rtrt_mesh_file_free(void* p);
 /* Per-frame vertex animation from HOST arrays: replaces the contents of the vertex (and, if non-NULL, normal)
  * buffer of the current mesh, V x 3 floats each, asynchronously on the context stream (pinned memory makes the
  * copy overlap).  Topology is unchanged; call rtrt_build_bvh / rtrt_render_frame afterwards.  This is the

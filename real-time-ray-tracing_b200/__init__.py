@@ -7,7 +7,7 @@ The directory name is not a Python identifier; import it with
 """
 from . import _lib  # noqa: F401
 from .api import (RayTracer, RtrtError, load_config, config_defaults, TRIANGLE_DTYPE, AABB_DTYPE, BVHNODE_DTYPE,
-                  RAY_DTYPE, HIT_DTYPE, RAY_MAX, MATERIAL_DTYPE, COLOR_DTYPE, dynamic_resolution_step)  # noqa: F401
+                  RAY_DTYPE, HIT_DTYPE, RAY_MAX, MATERIAL_DTYPE, COLOR_DTYPE, dynamic_resolution_step, read_mesh_file)  # noqa: F401
 from ._lib import *  # noqa: F401,F403  (BUF_* ids, ctypes structs)
 from . import scenes  # noqa: F401
 from . import parallel  # noqa: F401

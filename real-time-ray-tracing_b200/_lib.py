@@ -79,6 +79,10 @@ SYMBOLS = {
     "rtrt_set_mesh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
     "rtrt_set_mesh_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
     "rtrt_set_mesh_bin": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_set_mesh_obj": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "rtrt_write_mesh_bin": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int]),
+    "rtrt_mesh_file_read": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_uint32), C.c_char_p, C.c_size_t]),
+    "rtrt_mesh_file_free": (None, [C.c_void_p]),
     "rtrt_update_vertices": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "rtrt_set_option_i": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "rtrt_build_bvh": (C.c_int, [C.c_void_p]),

@@ -80,6 +80,25 @@ def dynamic_resolution_step(cfg, cur_width, cur_height, delta_time_ms):
     return w.value, h.value
 
 
+def read_mesh_file(path):
+    """`.obj` (LoadScene, src/fileUtils.cu:16-80) or `.bin` (LoadTrianglesFromFile, src/init.cu:28-50; 128-byte and legacy 64-byte
+    triangles) -> (pos [n,3,3] float32, nrm [n,3,3] float32 or None).  Pure host code: works without a GPU."""
+    lib = L.load()
+    pp, pn, n = C.POINTER(C.c_float)(), C.POINTER(C.c_float)(), C.c_uint32(0)
+    err = C.create_string_buffer(256)
+    rc = lib.rtrt_mesh_file_read(str(path).encode(), C.byref(pp), C.byref(pn), C.byref(n), err, 256)
+    if rc:
+        raise RtrtError(rc, f"{path}: {err.value.decode()}")
+    try:
+        pos = np.ctypeslib.as_array(pp, shape=(n.value, 3, 3)).copy()
+        nrm = np.ctypeslib.as_array(pn, shape=(n.value, 3, 3)).copy() if pn else None
+    finally:
+        lib.rtrt_mesh_file_free(pp)
+        if pn:
+            lib.rtrt_mesh_file_free(pn)
+    return pos, nrm
+
+
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
@@ -154,6 +173,14 @@ class RayTracer:
 
     def set_mesh_bin(self, path):
         self._check(self._lib.rtrt_set_mesh_bin(self._h, str(path).encode()))
+
+    def set_mesh_obj(self, path):
+        """LoadScene (src/fileUtils.cu:16-80) for Wavefront OBJ: triangles in file order, polygons fanned."""
+        self._check(self._lib.rtrt_set_mesh_obj(self._h, str(path).encode()))
+
+    def write_mesh_bin(self, path, presort=True, legacy64=False):
+        """tool/meshProcessor.cpp:146-215: the current mesh as `uint32 n; Triangle[n]`, optionally in 60-bit Morton order."""
+        self._check(self._lib.rtrt_write_mesh_bin(self._h, str(path).encode(), int(bool(presort)), int(bool(legacy64))))
 
     def set_option(self, name, value):
         self._check(self._lib.rtrt_set_option_i(self._h, name.encode(), int(value)))

@@ -10,7 +10,6 @@
 
 using namespace rtrt;
 
-struct rtrt_ctx { Context c; };
 
 namespace rtrt {
 
@@ -204,32 +203,6 @@ int rtrt_set_mesh_device(rtrt_ctx* ctx, const float* d_pos, const float* d_nrm, 
     if (rc) return rc;
     RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
     return RTRT_OK;
-}
-
-int rtrt_set_mesh_bin(rtrt_ctx* ctx, const char* path) {
-    CTX_OR_FAIL(ctx);
-    Context& c = ctx->c;
-    if (!path) return c.fail(RTRT_ERR_ARG, "rtrt_set_mesh_bin: null path");
-    FILE* f = fopen(path, "rb");
-    if (!f) return c.fail(RTRT_ERR_IO, "rtrt_set_mesh_bin: cannot open file");
-    uint32_t n = 0;
-    if (fread(&n, sizeof(n), 1, f) != 1 || n == 0) { fclose(f); return c.fail(RTRT_ERR_IO, "rtrt_set_mesh_bin: bad header"); }
-    std::vector<Triangle> tris(n);
-    if (fread(tris.data(), sizeof(Triangle), n, f) != n) { fclose(f); return c.fail(RTRT_ERR_IO, "rtrt_set_mesh_bin: truncated file (legacy 64-byte layout?)"); }
-    fclose(f);
-    // un-indexed triangle soup -> indexed buffers (3 vertices per triangle)
-    std::vector<float> pos((size_t)9 * n), nrm((size_t)9 * n);
-    std::vector<uint32_t> idx((size_t)3 * n);
-    for (uint32_t i = 0; i < n; ++i) {
-        const Float3* v[3] = {&tris[i].v1, &tris[i].v2, &tris[i].v3};
-        const Float3* m[3] = {&tris[i].n1, &tris[i].n2, &tris[i].n3};
-        for (int k = 0; k < 3; ++k) {
-            std::memcpy(&pos[(size_t)9 * i + 3 * k], v[k], 12);
-            std::memcpy(&nrm[(size_t)9 * i + 3 * k], m[k], 12);
-            idx[(size_t)3 * i + k] = 3 * i + k;
-        }
-    }
-    return rtrt_set_mesh(ctx, pos.data(), nrm.data(), idx.data(), 3 * n, n);
 }
 
 int rtrt_update_vertices(rtrt_ctx* ctx, const float* pos, const float* nrm, uint32_t V) {

@@ -117,3 +117,6 @@ int set_texture(Context& c, int slot, int w, int h, const uint16_t* rgba);
 int set_materials(Context& c, const void* materials, int numMaterials, const int* materialsIdx, int numIdx);
 
 }  // namespace rtrt
+
+// the opaque handle of include/rtrt.h
+struct rtrt_ctx { rtrt::Context c; };
