@@ -70,6 +70,7 @@ typedef struct rtrt_timings {
     uint64_t rays_traced;         /* TraverseBvh calls executed by the last pathtrace / traverse */
     uint64_t node_visits;         /* inner-node visits / leaf (triangle) tests of the last pathtrace; only counted  */
     uint64_t leaf_tests;          /* when option "count_visits" = 1 (adds register pressure, off by default)        */
+    uint64_t rays_traced_total;   /* TraverseBvh calls of all rtrt_pathtrace calls since rtrt_create (device-side sum)  */
 } rtrt_timings;
 
 /* Buffers observable through rtrt_get_buffer.  The first block are the DebugPrintFile observation
@@ -271,6 +272,16 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which /* rtrt_buffer */, void** dptr, siz
 int rtrt_read_buffer(rtrt_ctx* ctx, int which, void* dst, size_t dst_bytes);
 
 int rtrt_get_counts(rtrt_ctx* ctx, uint32_t* num_triangles, uint32_t* num_batches, uint32_t* num_batches_padded);
+/* Frames in flight.  rtrt_update_vertices and rtrt_read_buffer_async run their PCIe copies on a second (copy) stream, ordered
+ * against the kernels by events: the upload waits for the last build to have consumed the vertex buffers and the next
+ * rtrt_build_bvh waits for the upload; the read-back takes a device-side snapshot of the buffer on the main stream (after the
+ * kernels that produce it) and copies the snapshot to `dst` on the copy stream while the next frame is already running.
+ * `dst` (pinned memory for a real overlap) is valid after rtrt_sync, or after a stream/event wait that follows rtrt_join.
+ * One read-back may be in flight per context; a second one waits for the first.  rtrt_join makes the main stream wait for all
+ * queued copies, rtrt_sync blocks the host until both streams are idle.  (The reference presents through Vulkan interop and
+ * never reads a frame back; this is the headless replacement of that hand-over, src/main.cu:1295-1395.) */
+int rtrt_read_buffer_async(rtrt_ctx* ctx, int which, void* dst, size_t dst_bytes);
+int rtrt_join(rtrt_ctx* ctx);
 int rtrt_sync(rtrt_ctx* ctx);
 int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out);   /* synchronises the stream */
 /* the cudaStream_t all work is enqueued on, as an opaque pointer (for event timing by the caller) */

@@ -41,7 +41,7 @@ class Config(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("build_bvh_ms", C.c_float), ("traverse_ms", C.c_float), ("pathtrace_ms", C.c_float),
                 ("denoise_ms", C.c_float), ("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64),
-                ("node_visits", C.c_uint64), ("leaf_tests", C.c_uint64)]
+                ("node_visits", C.c_uint64), ("leaf_tests", C.c_uint64), ("rays_traced_total", C.c_uint64)]
 
 
 class SkyParams(C.Structure):      # src/settingParams.h:41-45
@@ -92,6 +92,8 @@ SYMBOLS = {
     "rtrt_read_buffer": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "rtrt_get_counts": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "rtrt_sync": (C.c_int, [C.c_void_p]),
+    "rtrt_join": (C.c_int, [C.c_void_p]),
+    "rtrt_read_buffer_async": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "rtrt_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "rtrt_get_stream": (C.c_void_p, [C.c_void_p]),
     "rtrt_set_camera": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),

@@ -303,6 +303,15 @@ class RayTracer:
         """Synchronous copy of a buffer into caller-owned (ideally pinned) host memory at address `host_ptr`."""
         self._check(self._lib.rtrt_read_buffer(self._h, which, C.c_void_p(host_ptr), nbytes))
 
+    def read_buffer_async(self, which, host_ptr, nbytes):
+        """Frames in flight: snapshot on the main stream, D2H on the copy stream (overlaps the next frame's kernels).
+        The host memory is valid after sync() (or after join() + a wait on the main stream)."""
+        self._check(self._lib.rtrt_read_buffer_async(self._h, which, C.c_void_p(host_ptr), nbytes))
+
+    def join(self):
+        """Main stream waits for every copy queued on the copy stream (uploads and read-backs)."""
+        self._check(self._lib.rtrt_join(self._h))
+
     def sync(self):
         self._check(self._lib.rtrt_sync(self._h))
 

@@ -54,10 +54,9 @@ struct SegSmem {
         AABB     nodeBox[kSeg];
     } scratch;                                 // 24 KB
     uint32_t keys[2][kSeg];                    //  8 KB  ping-pong; after the sort keys[1] is reused as the refit rendezvous counters
-    uint16_t ids[2][kSeg];                     //  4 KB
+    uint16_t ids[2][kSeg];                     //  4 KB  ping-pong; after the sort ids[1] holds leafParent: parent of the leaf at sorted position p
     uint32_t childL[kSeg], childR[kSeg];       //  8 KB  link | kLeafBit
     uint16_t parent[kSeg];                     //  2 KB  parent of internal node
-    uint16_t leafParent[kSeg];                 //  2 KB  parent of the leaf at sorted position p
     uint32_t digitBase[256];                   //  1 KB
     uint32_t warpSum[8];
     float    red[6][32];                       //  block AABB reduction
@@ -204,9 +203,9 @@ __device__ __forceinline__ void block_karras(SegSmem& s, int n) {
             if (t <= 1) break;
         }
         const int gamma = i + sp * d + min(d, 0);
-        if (min(i, j) == gamma) { s.childL[i] = (uint32_t)s.ids[0][gamma] | kLeafBit; s.leafParent[gamma] = (uint16_t)i; }
+        if (min(i, j) == gamma) { s.childL[i] = (uint32_t)s.ids[0][gamma] | kLeafBit; s.ids[1][gamma] = (uint16_t)i; }
         else                    { s.childL[i] = (uint32_t)gamma; s.parent[gamma] = (uint16_t)i; }
-        if (max(i, j) == gamma + 1) { s.childR[i] = (uint32_t)s.ids[0][gamma + 1] | kLeafBit; s.leafParent[gamma + 1] = (uint16_t)i; }
+        if (max(i, j) == gamma + 1) { s.childR[i] = (uint32_t)s.ids[0][gamma + 1] | kLeafBit; s.ids[1][gamma + 1] = (uint16_t)i; }
         else                        { s.childR[i] = (uint32_t)(gamma + 1); s.parent[gamma + 1] = (uint16_t)i; }
     }
 }
@@ -227,7 +226,7 @@ __device__ __forceinline__ void block_refit(SegSmem& s, int n) {
     for (int i = threadIdx.x; i < n - 1; i += NT) arrive[i] = 0u;
     __syncthreads();
     for (int p = threadIdx.x; p < n; p += NT) {
-        uint32_t cur = s.leafParent[p];
+        uint32_t cur = s.ids[1][p];
         while (true) {
             __threadfence_block();
             if (atomicAdd(&arrive[cur], 1u) == 0u) break;      // first arrival: sibling subtree pending

@@ -15,6 +15,9 @@
 namespace rtrt {
 
 constexpr int kBuildThreads = 512;
+#ifndef RTRT_BUILD_MINB
+#define RTRT_BUILD_MINB 3          // 3 CTAs/SM: <= 40 registers/thread and <= 75 KB shared memory per CTA
+#endif
 
 struct BuildParams {
     const float* __restrict__ pos;       // V x 3
@@ -68,7 +71,7 @@ __device__ void tlas_build_block(SegSmem& s, const BuildParams& p) {
 
 // ---- one CTA per batch ----
 template <int NT>
-__global__ void __launch_bounds__(NT, NT == 1024 ? 2 : 1) k_build_blas(const BuildParams p) {
+__global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SegSmem& s = *reinterpret_cast<SegSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -150,6 +153,7 @@ __global__ void __launch_bounds__(NT) k_build_tlas(const BuildParams p) {
 // ------------------------------------------------------------------------------------------------
 int launch_build_bvh(Context& c) {
     if (c.numTris == 0) return c.fail(RTRT_ERR_STATE, "rtrt_build_bvh: no mesh set");
+    { int rc = wait_geometry(c); if (rc) return rc; }       // a pending rtrt_update_vertices upload (copy stream)
     if (c.globalSort) { int rc = launch_presort(c); if (rc) return rc; }
     BuildParams p{};
     p.pos = c.dPos; p.nrm = c.dNrm; p.idx = c.globalSort ? c.dIdxSorted : c.dIdx; p.numTris = c.numTris; p.numBatches = c.numBatches;
@@ -165,11 +169,13 @@ int launch_build_bvh(Context& c) {
     if (!attrSet) {
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_tlas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));   // 3 x 73 KB per SM
         attrSet = true;
     }
     RTRT_CUDA(c, cudaMemsetAsync(c.dTicket, 0, sizeof(uint32_t), c.stream));
     k_build_blas<kBuildThreads><<<c.numBatches, kBuildThreads, smem, c.stream>>>(p);
     c.launches += 1;
+    { int rc = geometry_consumed(c); if (rc) return rc; }   // the vertex buffers may be overwritten from here on
     if (!p.fuseTlas) {
         int rc = launch_build_tlas_global(c);     // B > 1024: multi-CTA top level (bvh_tlas_global.cu)
         if (rc) return rc;

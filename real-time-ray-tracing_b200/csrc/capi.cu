@@ -138,6 +138,9 @@ int rtrt_create(const rtrt_config* cfg, int device, rtrt_ctx** out) {
     rtrt_postprocess_defaults(&c.postParams);
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     if (cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&c.copyStream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&c.uploadStream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
+    for (cudaEvent_t* e : {&c.evGeomReady, &c.evGeomFree, &c.evStaged, &c.evReadDone}) cudaEventCreateWithFlags(e, cudaEventDisableTiming);
     for (auto& e : c.ev) { cudaEventCreate(&e[0]); cudaEventCreate(&e[1]); }
     if (cudaMalloc((void**)&c.dTicket, 64) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     *out = h;
@@ -149,13 +152,19 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     Context& c = ctx->c;
     cudaSetDevice(c.device);
     cudaStreamSynchronize(c.stream);
+    if (c.copyStream) cudaStreamSynchronize(c.copyStream);
+    if (c.uploadStream) cudaStreamSynchronize(c.uploadStream);
     free_mesh(c);
     free_frame_resources(c);
+    dfree(c.dStage);
     dfree(c.dRayStage); dfree(c.dHitStage); dfree(c.dTicket);
     for (auto& e : c.ev) { if (e[0]) cudaEventDestroy(e[0]); if (e[1]) cudaEventDestroy(e[1]); }
     for (auto& st : c.chunkStream) if (st) cudaStreamDestroy(st);
     for (auto& ev : c.chunkJoin) if (ev) cudaEventDestroy(ev);
     if (c.chunkFork) cudaEventDestroy(c.chunkFork);
+    for (cudaEvent_t e : {c.evGeomReady, c.evGeomFree, c.evStaged, c.evReadDone}) if (e) cudaEventDestroy(e);
+    if (c.copyStream) cudaStreamDestroy(c.copyStream);
+    if (c.uploadStream) cudaStreamDestroy(c.uploadStream);
     if (c.stream) cudaStreamDestroy(c.stream);
     delete ctx;
     return RTRT_OK;
@@ -213,11 +222,30 @@ int rtrt_update_vertices(rtrt_ctx* ctx, const float* pos, const float* nrm, uint
     if (!c.ownsMesh) return c.fail(RTRT_ERR_STATE, "rtrt_update_vertices: mesh buffers are caller-owned (rtrt_set_mesh_device)");
     if (V != c.numVerts) return c.fail(RTRT_ERR_ARG, "rtrt_update_vertices: vertex count differs from the mesh");
     RTRT_CUDA(c, cudaSetDevice(c.device));
-    RTRT_CUDA(c, cudaMemcpyAsync(c.dPos, pos, (size_t)3 * V * sizeof(float), cudaMemcpyHostToDevice, c.stream));
-    if (nrm) RTRT_CUDA(c, cudaMemcpyAsync(c.dNrm, nrm, (size_t)3 * V * sizeof(float), cudaMemcpyHostToDevice, c.stream));
+    // upload stream: starts once the last build has consumed the previous contents, overlaps whatever the main stream runs
+    // (path trace / denoise of the frame in flight read the Triangle array, not the vertex buffers)
+    if (c.geomFreeValid) RTRT_CUDA(c, cudaStreamWaitEvent(c.uploadStream, c.evGeomFree, 0));
+    RTRT_CUDA(c, cudaMemcpyAsync(c.dPos, pos, (size_t)3 * V * sizeof(float), cudaMemcpyHostToDevice, c.uploadStream));
+    if (nrm) RTRT_CUDA(c, cudaMemcpyAsync(c.dNrm, nrm, (size_t)3 * V * sizeof(float), cudaMemcpyHostToDevice, c.uploadStream));
+    RTRT_CUDA(c, cudaEventRecord(c.evGeomReady, c.uploadStream));
+    c.geomPending = true;
     c.bvhValid = false;
     return RTRT_OK;
 }
+
+}  // extern "C" (helpers below have C++ linkage)
+namespace rtrt {
+int wait_geometry(Context& c) {
+    if (c.geomPending) { RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.evGeomReady, 0)); c.geomPending = false; }
+    return RTRT_OK;
+}
+int geometry_consumed(Context& c) {
+    RTRT_CUDA(c, cudaEventRecord(c.evGeomFree, c.stream));
+    c.geomFreeValid = true;
+    return RTRT_OK;
+}
+}  // namespace rtrt
+extern "C" {
 
 int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     CTX_OR_FAIL(ctx);
@@ -341,6 +369,42 @@ int rtrt_read_buffer(rtrt_ctx* ctx, int which, void* dst, size_t dst_bytes) {
     return RTRT_OK;
 }
 
+// Frames in flight: D2D snapshot on the main stream (ordered after the kernels that produce the buffer), D2H of the snapshot
+// on the copy stream, so the next frame's kernels overlap the transfer.
+int rtrt_read_buffer_async(rtrt_ctx* ctx, int which, void* dst, size_t dst_bytes) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    void* p; size_t b;
+    int rc = rtrt_get_buffer(ctx, which, &p, &b);
+    if (rc) return rc;
+    if (!dst || dst_bytes < b) return c.fail(RTRT_ERR_ARG, "rtrt_read_buffer_async: destination too small");
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    if (c.stageBytes < b) {
+        RTRT_CUDA(c, cudaStreamSynchronize(c.copyStream));
+        dfree(c.dStage); c.stageBytes = 0;
+        RTRT_CUDA(c, cudaMalloc(&c.dStage, b));
+        c.stageBytes = b;
+    }
+    if (c.readPending) RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.evReadDone, 0));      // the previous read-back still owns the snapshot
+    RTRT_CUDA(c, cudaMemcpyAsync(c.dStage, p, b, cudaMemcpyDeviceToDevice, c.stream));
+    RTRT_CUDA(c, cudaEventRecord(c.evStaged, c.stream));
+    RTRT_CUDA(c, cudaStreamWaitEvent(c.copyStream, c.evStaged, 0));
+    RTRT_CUDA(c, cudaMemcpyAsync(dst, c.dStage, b, cudaMemcpyDeviceToHost, c.copyStream));
+    RTRT_CUDA(c, cudaEventRecord(c.evReadDone, c.copyStream));
+    c.readPending = true;
+    return RTRT_OK;
+}
+
+// Main stream waits for everything queued on the copy stream (so an event recorded on rtrt_get_stream afterwards covers it).
+int rtrt_join(rtrt_ctx* ctx) {
+    CTX_OR_FAIL(ctx);
+    Context& c = ctx->c;
+    RTRT_CUDA(c, cudaSetDevice(c.device));
+    if (c.readPending) RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.evReadDone, 0));
+    if (c.geomPending) RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.evGeomReady, 0));
+    return RTRT_OK;
+}
+
 int rtrt_get_counts(rtrt_ctx* ctx, uint32_t* nt, uint32_t* nb, uint32_t* nbp) {
     CTX_OR_FAIL(ctx);
     if (nt) *nt = ctx->c.numTris;
@@ -354,6 +418,9 @@ int rtrt_sync(rtrt_ctx* ctx) {
     Context& c = ctx->c;
     RTRT_CUDA(c, cudaSetDevice(c.device));
     RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
+    RTRT_CUDA(c, cudaStreamSynchronize(c.copyStream));
+    RTRT_CUDA(c, cudaStreamSynchronize(c.uploadStream));
+    c.readPending = false;
     return RTRT_OK;
 }
 
@@ -371,9 +438,10 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
             c.evPending[s] = false;
         }
     if (c.raysOnDevice && c.dRayCounter) {
-        unsigned long long r[3] = {0, 0, 0};
+        unsigned long long r[5] = {0, 0, 0, 0, 0};
         RTRT_CUDA(c, cudaMemcpy(r, c.dRayCounter, sizeof(r), cudaMemcpyDeviceToHost));
         c.timings.rays_traced = r[0]; c.timings.node_visits = r[1]; c.timings.leaf_tests = r[2]; c.raysOnDevice = false;
+        c.timings.rays_traced_total = r[4];
     }
     c.timings.kernel_launches = c.launches;
     *out = c.timings;

@@ -77,6 +77,13 @@ struct Context {
     unsigned long long* dRayCounter = nullptr;
     rtrt_denoise_params denoiseParams{}; rtrt_pass_settings passSettings{};
 
+    // ---- copy engine (frames in flight): a second stream carries the host<->device copies of rtrt_update_vertices and
+    // rtrt_read_buffer_async so that they overlap the kernels of the neighbouring frames; ordering is by events only.
+    cudaStream_t copyStream = nullptr, uploadStream = nullptr;      // read-backs / uploads (PCIe is full duplex: one in-order stream each)
+    cudaEvent_t evGeomReady = nullptr, evGeomFree = nullptr, evStaged = nullptr, evReadDone = nullptr;
+    bool geomPending = false, geomFreeValid = false, readPending = false;
+    void* dStage = nullptr; size_t stageBytes = 0;       // device staging copy of the buffer being read back
+
     // ---- bookkeeping ----
     unsigned long long launches = 0;                     // kernels launched by this library
     cudaEvent_t ev[4][2] = {};                           // [build, traverse, pathtrace, denoise][begin, end]
@@ -105,6 +112,8 @@ enum { STAGE_BUILD = 0, STAGE_TRAVERSE = 1, STAGE_PATHTRACE = 2, STAGE_DENOISE =
 int launch_build_bvh(Context& c);
 int launch_build_tlas_global(Context& c);
 int launch_presort(Context& c);             // bvh_presort.cu
+int wait_geometry(Context& c);              // capi.cu: main stream waits for a pending rtrt_update_vertices upload
+int geometry_consumed(Context& c);          // capi.cu: records that the main stream has read the vertex buffers
 int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int anyHit, unsigned long long* dCounters);
 int launch_pathtrace(Context& c);
 int launch_denoise(Context& c);

@@ -304,7 +304,7 @@ int ensure_frame_resources(Context& c) {
     RTRT_CUDA(c, cudaSetDevice(c.device));
     if (c.width <= 0 || c.height <= 0) return c.fail(RTRT_ERR_STATE, "render size not set");
     if (c.dataDir.empty()) c.dataDir = default_data_dir();
-    if (!c.dRayCounter) RTRT_CUDA(c, cudaMalloc((void**)&c.dRayCounter, 64));
+    if (!c.dRayCounter) { RTRT_CUDA(c, cudaMalloc((void**)&c.dRayCounter, 64)); RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 64, c.stream)); }
     if (!c.dBlueNoise) {
         std::vector<uint8_t> bn(65536 + 131072 + 131072);
         if (!read_file(c.dataDir + "/blue_noise_4spp.bin", bn.data(), bn.size())) return c.fail(RTRT_ERR_IO, "cannot read data/blue_noise_4spp.bin (rtrt_set_data_dir?)");

@@ -191,6 +191,7 @@ int rtrt_write_mesh_bin(rtrt_ctx* ctx, const char* path, int presort, int legacy
     const uint32_t N = c.numTris, V = c.numVerts;
     std::vector<float> pos((size_t)3 * V), nrm((size_t)3 * V);
     std::vector<uint32_t> idx((size_t)3 * N), perm;
+    { int rc = wait_geometry(c); if (rc) return rc; }
     if (presort) {
         int rc = launch_presort(c);                                                  // k_ps_bounds -> k_ps_codes -> radix sort -> k_ps_gather
         if (rc) return rc;

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kPtThreads) k_pathtrace(const PathTraceParams 
     for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
     if ((tid & 31) == 0) atomicAdd(&sRays, rays);
     __syncthreads();
-    if (tid == 0 && P.rayCounter) atomicAdd(P.rayCounter, (unsigned long long)sRays);
+    if (tid == 0 && P.rayCounter) { atomicAdd(P.rayCounter, (unsigned long long)sRays); atomicAdd(P.rayCounter + 4, (unsigned long long)sRays); }
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
         if ((tid & 31) == 0 && P.rayCounter) { atomicAdd(P.rayCounter + 1, (unsigned long long)nodeVisits); atomicAdd(P.rayCounter + 2, (unsigned long long)leafTests); }

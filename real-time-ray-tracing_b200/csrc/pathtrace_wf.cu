@@ -329,7 +329,9 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParam
 
 // rays traced = pixels + every queued ray (src/traverse.cuh:64-72: one TraverseBvh per passed guard)
 __global__ void k_pt_count_rays(const uint32_t* __restrict__ counters, unsigned long long pixels, unsigned long long* out) {
-    atomicAdd(out, pixels + counters[0] + counters[1] + counters[2] + counters[3]);      // one add per chunk of the frame
+    const unsigned long long n = pixels + counters[0] + counters[1] + counters[2] + counters[3];
+    atomicAdd(out, n);                                                                  // one add per chunk of the frame
+    atomicAdd(out + 4, n);                                                              // cumulative since rtrt_create (never reset)
 }
 
 SceneView make_scene_view(const Context& c);   // traverse.cu
