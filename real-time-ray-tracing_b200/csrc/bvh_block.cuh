@@ -53,10 +53,9 @@ struct SegSmem {
         uint16_t hist[32][256];
         AABB     nodeBox[kSeg];
     } scratch;                                 // 24 KB
-    uint32_t keys[2][kSeg];                    //  8 KB  ping-pong; after the sort keys[1] is reused as the refit rendezvous counters
-    uint16_t ids[2][kSeg];                     //  4 KB  ping-pong; after the sort ids[1] holds leafParent: parent of the leaf at sorted position p
+    uint32_t keys[2][kSeg];                    //  8 KB  ping-pong; after the sort keys[1] holds the rendezvous slots of the emit
+    uint16_t ids[2][kSeg];                     //  4 KB  ping-pong
     uint32_t childL[kSeg], childR[kSeg];       //  8 KB  link | kLeafBit
-    uint16_t parent[kSeg];                     //  2 KB  parent of internal node
     uint32_t digitBase[256];                   //  1 KB
     uint32_t warpSum[8];
     float    red[6][32];                       //  block AABB reduction
@@ -179,35 +178,23 @@ __device__ __forceinline__ int seg_delta(const uint32_t* keys, int n, int i, uin
     return x ? __clz(x) : 32 + __clz((uint32_t)i ^ (uint32_t)j);
 }
 
-// ---- Karras hierarchy emit over the n sorted keys in s.keys[0] (src/buildBVH.cuh:60-134) ----
-// Leaf links carry the ORIGINAL item id (s.ids[0][gamma] = reorderIdx) like the reference.
-template <int NT>
-__device__ __forceinline__ void block_karras(SegSmem& s, int n) {
-    const uint32_t* keys = s.keys[0];
-    for (int i = threadIdx.x; i < n - 1; i += NT) {
-        const uint32_t ki = keys[i];
-        const int dl = seg_delta(keys, n, i, ki, i - 1), dr = seg_delta(keys, n, i, ki, i + 1);
-        const int d = (dr - dl) >= 0 ? 1 : -1;
-        const int dmin = seg_delta(keys, n, i, ki, i - d);
-        int lmax = 2;
-        while (seg_delta(keys, n, i, ki, i + lmax * d) > dmin) lmax <<= 1;
-        int l = 0;
-        for (int t = lmax >> 1; t >= 1; t >>= 1)
-            if (seg_delta(keys, n, i, ki, i + (l + t) * d) > dmin) l += t;
-        const int j = i + l * d;
-        const int dnode = seg_delta(keys, n, i, ki, j);
-        int sp = 0;
-        for (int div = 2;; div <<= 1) {
-            const int t = (l + div - 1) / div;
-            if (seg_delta(keys, n, i, ki, i + (sp + t) * d) > dnode) sp += t;
-            if (t <= 1) break;
-        }
-        const int gamma = i + sp * d + min(d, 0);
-        if (min(i, j) == gamma) { s.childL[i] = (uint32_t)s.ids[0][gamma] | kLeafBit; s.ids[1][gamma] = (uint16_t)i; }
-        else                    { s.childL[i] = (uint32_t)gamma; s.parent[gamma] = (uint16_t)i; }
-        if (max(i, j) == gamma + 1) { s.childR[i] = (uint32_t)s.ids[0][gamma + 1] | kLeafBit; s.ids[1][gamma + 1] = (uint16_t)i; }
-        else                        { s.childR[i] = (uint32_t)(gamma + 1); s.parent[gamma + 1] = (uint16_t)i; }
-    }
+// ---- hierarchy emit + refit in ONE bottom-up pass (replaces src/buildBVH.cuh:60-134 emit + :138-267 refit) ----
+// The binary radix tree over the sorted keys (Karras 2012, what the reference's top-down BuildLBVH emits) is unique, so it can be
+// grown from the leaves (Apetrei 2014): a finished range [f,l] joins the neighbour it shares the longer prefix with —
+//   delta(f-1,f) > delta(l,l+1)  -> it is the RIGHT child of the node that splits at gamma = f-1,
+//   otherwise                     -> it is the LEFT  child of the node that splits at gamma = l
+// (the two are never equal for distinct keys, and seg_delta's index tie-break makes equal keys distinct).  The first child to
+// reach a split leaves its outer bound there; the second completes the range, and with it everything Karras' numbering needs:
+// a left child is numbered by the END of its range, a right child by its START, the root is 0; the children of the node that
+// splits at gamma are therefore gamma and gamma+1 (or the leaf items there).  Same topology, same indices, same links as the
+// top-down emit — and the node box is merged on the way up, so there is no separate refit walk and no parent table.
+// One walker per leaf, ~2 key comparisons per level instead of ~30 binary-search probes per node.
+__device__ __forceinline__ int seg_bound(const uint32_t* keys, int j) {                  // delta(j, j+1)
+    const uint32_t x = keys[j] ^ keys[j + 1];
+    return x ? __clz(x) : 32 + __clz((uint32_t)j ^ (uint32_t)(j + 1));
+}
+__device__ __forceinline__ bool seg_joins_left(const uint32_t* keys, int n, int f, int l) {
+    return l == n - 1 || (f > 0 && seg_bound(keys, f - 1) > seg_bound(keys, l));
 }
 
 __device__ __forceinline__ AABB child_box(const SegSmem& s, uint32_t link) {
@@ -218,26 +205,35 @@ __device__ __forceinline__ AABB child_box(const SegSmem& s, uint32_t link) {
     return b;
 }
 
-// ---- bottom-up refit in shared memory (src/buildBVH.cuh:138-267): one walker per leaf; the second
-// walker to reach a node merges its children.  Boxes are exact unions => order independent. ----
 template <int NT>
-__device__ __forceinline__ void block_refit(SegSmem& s, int n) {
-    uint32_t* arrive = s.keys[1];              // dead after block_sort_1024 (the sorted keys live in keys[0])
-    for (int i = threadIdx.x; i < n - 1; i += NT) arrive[i] = 0u;
+__device__ __forceinline__ void block_emit_refit(SegSmem& s, int n) {
+    const uint32_t* keys = s.keys[0];
+    uint32_t* slot = s.keys[1];                // dead after block_sort_1024 (the sorted keys live in keys[0])
+    constexpr uint32_t kEmpty = 0xFFFFFFFFu;
+    for (int i = threadIdx.x; i < n - 1; i += NT) slot[i] = kEmpty;
     __syncthreads();
     for (int p = threadIdx.x; p < n; p += NT) {
-        uint32_t cur = s.ids[1][p];
+        int f = p, l = p;
+        bool left = seg_joins_left(keys, n, f, l);
         while (true) {
+            const int gamma = left ? f - 1 : l;
+            __threadfence_block();                                             // my nodeBox / links are visible before the hand-over
+            const uint32_t other = atomicExch(&slot[gamma], (uint32_t)(left ? l : f));
+            if (other == kEmpty) break;                                        // first arrival: the sibling subtree is pending
             __threadfence_block();
-            if (atomicAdd(&arrive[cur], 1u) == 0u) break;      // first arrival: sibling subtree pending
-            __threadfence_block();
-            AABB b = child_box(s, s.childL[cur]);
-            aabb_grow(b, child_box(s, s.childR[cur]));
-            volatile AABB* o = &s.scratch.nodeBox[cur];
+            if (left) f = (int)other; else l = (int)other;
+            const bool root = f == 0 && l == n - 1;
+            int idx = 0;
+            if (!root) { left = seg_joins_left(keys, n, f, l); idx = left ? f : l; }
+            const uint32_t L = (f == gamma) ? ((uint32_t)s.ids[0][gamma] | kLeafBit) : (uint32_t)gamma;
+            const uint32_t R = (gamma + 1 == l) ? ((uint32_t)s.ids[0][gamma + 1] | kLeafBit) : (uint32_t)(gamma + 1);
+            s.childL[idx] = L; s.childR[idx] = R;
+            AABB b = child_box(s, L);
+            aabb_grow(b, child_box(s, R));
+            volatile AABB* o = &s.scratch.nodeBox[idx];
             o->min.x = b.min.x; o->min.y = b.min.y; o->min.z = b.min.z;
             o->max.x = b.max.x; o->max.y = b.max.y; o->max.z = b.max.z;
-            if (cur == 0u) break;
-            cur = s.parent[cur];
+            if (root) break;
         }
     }
     __syncthreads();
@@ -286,9 +282,7 @@ __device__ __forceinline__ void block_build_segment(SegSmem& s, int n, uint32_t*
         if (threadIdx.x == 0) write_single_leaf_node(s.leafBox[0], gNodes);
         return;
     }
-    block_karras<NT>(s, n);
-    __syncthreads();
-    block_refit<NT>(s, n);
+    block_emit_refit<NT>(s, n);
     block_write_nodes<NT>(s, n, gNodes);
 }
 

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     // rows: 0..2 = v1..v3, 3 = v4 (unused), 4..6 = n1..n3, 7 = n4 (unused)          src/updateGeometry.cuh:131-137
     const int sub = lane & 7, grp = lane >> 3;
     float4* tri4 = reinterpret_cast<float4*>(p.triangles + base);
-    AABB mine = aabb_empty();
+    float accMin = FLT_MAX, accMax = -FLT_MAX;           // this lane's axis of the batch box
 #pragma unroll 4
     for (int it = 0; it < kSeg / (NW * 4); ++it) {
         const uint32_t i = (uint32_t)(it * NW + warp) * 4u + grp;          // batch-local item
@@ -101,19 +101,25 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
         const Float3 v1{__shfl_sync(0xffffffffu, val.x, l0), __shfl_sync(0xffffffffu, val.y, l0), __shfl_sync(0xffffffffu, val.z, l0)};
         const Float3 v2{__shfl_sync(0xffffffffu, val.x, l0 + 1), __shfl_sync(0xffffffffu, val.y, l0 + 1), __shfl_sync(0xffffffffu, val.z, l0 + 1)};
         const Float3 v3{__shfl_sync(0xffffffffu, val.x, l0 + 2), __shfl_sync(0xffffffffu, val.y, l0 + 2), __shfl_sync(0xffffffffu, val.z, l0 + 2)};
-        if (on && sub == 0) {
-            AABB bx;                                                                          // :172-177
-            bx.min.x = sel_min(v1.x, sel_min(v2.x, v3.x)); bx.min.y = sel_min(v1.y, sel_min(v2.y, v3.y)); bx.min.z = sel_min(v1.z, sel_min(v2.z, v3.z));
-            bx.max.x = sel_max(v1.x, sel_max(v2.x, v3.x)); bx.max.y = sel_max(v1.y, sel_max(v2.y, v3.y)); bx.max.z = sel_max(v1.z, sel_max(v2.z, v3.z));
+        if (on && sub < 3) {
+            // lanes 0..2 of the group take one axis each (x, y, z): a third of the arithmetic per lane, three times the active lanes
+            const float a = sub == 0 ? v1.x : (sub == 1 ? v1.y : v1.z);
+            const float b = sub == 0 ? v2.x : (sub == 1 ? v2.y : v2.z);
+            const float c = sub == 0 ? v3.x : (sub == 1 ? v3.y : v3.z);
+            const float mn = sel_min(a, sel_min(b, c));                                       // :172-177
+            float mx = sel_max(a, sel_max(b, c));
             const float eps = 1.1920928955078125e-07f;                                        // MachineEpsilon()
-            bx.max.x = bx.min.x + sel_max(bx.max.x - bx.min.x, eps * bx.max.x);
-            bx.max.y = bx.min.y + sel_max(bx.max.y - bx.min.y, eps * bx.max.y);
-            bx.max.z = bx.min.z + sel_max(bx.max.z - bx.min.z, eps * bx.max.z);
-            s.leafBox[i] = bx;
-            s.scratch.centre[i] = Float3{((v1.x + v2.x) + v3.x) / 3.0f, ((v1.y + v2.y) + v3.y) / 3.0f, ((v1.z + v2.z) + v3.z) / 3.0f};  // :180
-            aabb_grow(mine, bx);
+            mx = mn + sel_max(mx - mn, eps * mx);
+            float* lb = reinterpret_cast<float*>(&s.leafBox[i]);                              // AABB = {min.xyz, max.xyz}
+            lb[sub] = mn; lb[3 + sub] = mx;
+            reinterpret_cast<float*>(&s.scratch.centre[i])[sub] = ((a + b) + c) / 3.0f;       // :180
+            accMin = sel_min(accMin, mn); accMax = sel_max(accMax, mx);
         }
     }
+    AABB mine = aabb_empty();
+    if (sub == 0) { mine.min.x = accMin; mine.max.x = accMax; }
+    else if (sub == 1) { mine.min.y = accMin; mine.max.y = accMax; }
+    else if (sub == 2) { mine.min.z = accMin; mine.max.z = accMax; }
     const AABB batchBox = block_reduce_aabb<NT>(s, mine);     // barriers inside also publish leafBox/centre
 
     // ---- per-item AABB array (24 KB contiguous per batch) + Morton keys ----
