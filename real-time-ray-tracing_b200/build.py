@@ -19,7 +19,7 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "--fmad=false", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-Wno-unused-function",
     "-Xptxas", "-v" if os.environ.get("RTRT_PTXAS_V") else "-O3",
-]
+] + os.environ.get("RTRT_NVCC_EXTRA", "").split()      # experiment knobs, e.g. RTRT_NVCC_EXTRA="-DRTRT_GATHER_UNROLL=8"
 
 
 def sources():

@@ -15,6 +15,10 @@
 namespace rtrt {
 
 constexpr int kBuildThreads = 512;
+#ifndef RTRT_GATHER_UNROLL
+#define RTRT_GATHER_UNROLL 4
+#endif
+constexpr int kGatherUnroll = RTRT_GATHER_UNROLL;
 #ifndef RTRT_BUILD_MINB
 #define RTRT_BUILD_MINB 3          // 3 CTAs/SM: <= 40 registers/thread and <= 75 KB shared memory per CTA
 #endif
@@ -85,15 +89,23 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     // rows: 0..2 = v1..v3, 3 = v4 (unused), 4..6 = n1..n3, 7 = n4 (unused)          src/updateGeometry.cuh:131-137
     const int sub = lane & 7, grp = lane >> 3;
     float4* tri4 = reinterpret_cast<float4*>(p.triangles + base);
+    // ---- stage the batch's 3 x 1024 vertex indices in shared memory: one fully coalesced 12-KB read instead of a 4-byte load per
+    // lane in front of every dependent vertex load (pad items read index 0, src/init.cu:103-115).  Lives in the upper half of
+    // `scratch`, which nothing else touches before the sort (the centres occupy the lower 12 KB).
+    uint32_t* sIdx = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(&s.scratch) + sizeof(Float3) * kSeg);
+    {
+        const size_t lim = (size_t)3 * p.numTris, off = (size_t)3 * base;
+        for (uint32_t e = tid; e < 3u * kSeg; e += NT) sIdx[e] = (off + e < lim) ? __ldg(p.idx + off + e) : 0u;
+    }
+    __syncthreads();
     float accMin = FLT_MAX, accMax = -FLT_MAX;           // this lane's axis of the batch box
-#pragma unroll 4
+#pragma unroll(kGatherUnroll)
     for (int it = 0; it < kSeg / (NW * 4); ++it) {
         const uint32_t i = (uint32_t)(it * NW + warp) * 4u + grp;          // batch-local item
-        const uint32_t g = base + i;
         const bool on = i < active;
         Float3 val{0.0f, 0.0f, 0.0f};
         if (on && (sub & 3) != 3) {
-            const uint32_t vid = (g < p.numTris) ? __ldg(p.idx + 3 * (size_t)g + (sub & 3)) : 0u;   // pad indices are 0 (src/init.cu:103-115)
+            const uint32_t vid = sIdx[3u * i + (sub & 3)];
             val = ld3(sub < 4 ? p.pos : p.nrm, vid);
         }
         if (on) tri4[(size_t)i * 8 + sub] = make_float4(val.x, val.y, val.z, 0.0f);
