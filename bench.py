@@ -183,6 +183,26 @@ class DevView:
                                          "strides": None}
 
 
+class quiet_stdout:
+    """The reference's traversal kernel printf()s "push to full stack" from the device for a few rays per frame; stdout of this
+    program must stay ONE JSON line, so fd 1 points at /dev/null while those kernels run (device printf is flushed by the sync)."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+        return self
+
+    def __exit__(self, *exc):
+        try:
+            import torch
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(self.saved, 1); os.close(self.saved); os.close(self.null)
+        return False
+
+
 def reference_kernels(pkg, rt, pos, nrm, idx, cam, rays_per_frame):
     """The reference's own CUDA kernels (oracle/_ref/librefcuda.so, built for sm_100 from /root/reference by oracle/refcuda/build_ref.py)
     timed on this GPU on the same scene: the baseline north_star asks to report next to the CPU one.  Baseline leg only."""
@@ -494,7 +514,8 @@ def main():
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_ref_kernels:
-            line["reference_kernels"] = reference_kernels(pkg, rt, pos, nrm, idx, cam, rays / args.steps)
+            with quiet_stdout():
+                line["reference_kernels"] = reference_kernels(pkg, rt, pos, nrm, idx, cam, rays / args.steps)
         if not args.no_cpu_baseline and world == 1:
             _, _, line["cpu_baseline"] = CpuArm(pkg).baseline(steps=1, warmup=0)
         print(json.dumps(line), flush=True)

@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librtrt.so")
+LIB_PATH = os.environ.get("RTRT_LIB") or os.path.join(HERE, "librtrt.so")     # RTRT_LIB: A/B builds of the same library (experiments)
 
 RTRT_OK = 0
 STATUS_NAMES = {0: "RTRT_OK", -1: "RTRT_ERR_ARG", -2: "RTRT_ERR_CUDA", -3: "RTRT_ERR_CAPACITY",

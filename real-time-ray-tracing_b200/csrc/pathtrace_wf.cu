@@ -22,7 +22,10 @@ namespace rtrt {
 
 constexpr int kTraceThreads = 128;
 constexpr int kLogicThreads = 128;
-constexpr int kRefillIdle = 8;        // refill a warp once this many of its lanes are idle
+#ifndef RTRT_REFILL_IDLE
+#define RTRT_REFILL_IDLE 8
+#endif
+constexpr int kRefillIdle = RTRT_REFILL_IDLE;   // refill a warp once this many of its lanes are idle
 
 struct WfBuffers {
     float4* st0; float4* st1; float4* st2; float4* st3; float4* st4; float4* hit;

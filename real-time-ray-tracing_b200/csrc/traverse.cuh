@@ -229,27 +229,29 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, const RayPrep& r,
     } else {
         float4 n0 = make_float4(0, 0, 0, 0), n1 = n0, n2 = n0, n3 = n0;
         const uint32_t idx = cur & 0x3FFFFFFFu;
-        if (cur & kLinkBlas) {
-            if (idx < numTri) { const float4* row = sc.nodeRows + (size_t)idx * 4; n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
-        } else {
-            if (idx < sc.numBatches) { const float4* row = sc.tlasRows + (size_t)idx * 4; n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
+        {   // one load sequence for both levels: base pointer and SAFE_LOAD limit are selected, not branched on (src/traverse.h:205-209)
+            const bool blas = (cur & kLinkBlas) != 0u;
+            const float4* row = (blas ? sc.nodeRows : sc.tlasRows) + (size_t)idx * 4;
+            if (idx < (blas ? numTri : sc.numBatches)) { n0 = __ldg(row); n1 = __ldg(row + 1); n2 = __ldg(row + 2); n3 = __ldg(row + 3); }
         }
         if (COUNT) s.nodeVisits++;
         float t1, t2;
         const bool i1 = ray_box(r, n1.x, n1.y, n1.z, n0.x, n0.y, n0.z, t1);           // left : min = row1.xyz, max = row0.xyz
         const bool i2 = ray_box(r, n0.w, n1.w, n2.w, n2.x, n2.y, n2.z, t2);           // right: min = (row0.w,row1.w,row2.w), max = row2.xyz
         const uint32_t up = (cur & kLinkBlas) ? (cur & (kLinkBlas | 0x3FFFFC00u)) : 0u;   // keep isBlas + blasOffset
-        const uint32_t L = up | __float_as_uint(n3.x) | (__float_as_uint(n3.z) ? kLinkLeaf : 0u);
-        const uint32_t R = up | __float_as_uint(n3.y) | (__float_as_uint(n3.w) ? kLinkLeaf : 0u);
-        if (!i1 && !i2) pop = true;
-        else if (i1 && !i2) { s.cur = L; s.curT = t1; }
-        else if (!i1 && i2) { s.cur = R; s.curT = t2; }
-        else {
-            uint32_t farL; float farT;
-            if (t1 < t2) { farL = R; farT = t2; s.cur = L; s.curT = t1; }
-            else         { farL = L; farT = t1; s.cur = R; s.curT = t2; }
-            if (s.top < cap - 1) { ++s.top; stackLink[s.top * stride] = farL; stackT[s.top * stride] = farT; }   // dropped when full (src/traverse.h:32-40)
-        }
+        // isLeftLeaf / isRightLeaf are written as exactly 0 or 1 by the build (bvh_block.cuh: block_write_nodes) -> bit 31 by a shift
+        const uint32_t L = up | __float_as_uint(n3.x) | (__float_as_uint(n3.z) << 31);
+        const uint32_t R = up | __float_as_uint(n3.y) | (__float_as_uint(n3.w) << 31);
+        // near / far by selects instead of a four-way branch: the right child goes first when only it is hit, or when both are hit
+        // and !(t1 < t2) (src/traverse.h:214-243: "t1 < t2 ? left first : right first")
+        const bool both = i1 && i2;
+        const bool rightFirst = both ? !(t1 < t2) : !i1;
+        if (i1 || i2) {
+            s.cur = rightFirst ? R : L; s.curT = rightFirst ? t2 : t1;
+            if (both && s.top < cap - 1) {                                             // dropped when full (src/traverse.h:32-40)
+                ++s.top; stackLink[s.top * stride] = rightFirst ? L : R; stackT[s.top * stride] = rightFirst ? t1 : t2;
+            }
+        } else pop = true;
     }
     if (pop) {                                                                         // TestForFinish (src/traverse.h:88-105)
         do {
