@@ -183,6 +183,15 @@ class DevView:
                                          "strides": None}
 
 
+def ncu_traffic(key):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture (profiles/ncu_traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f)[key]["dram_bytes"]
+    except Exception:
+        return None
+
+
 class quiet_stdout:
     """The reference's traversal kernel printf()s "push to full stack" from the device for a few rays per frame; stdout of this
     program must stay ONE JSON line, so fd 1 points at /dev/null while those kernels run (device printf is flushed by the sync)."""
@@ -434,13 +443,16 @@ def main():
         barrier()
         lbefore = rt.timings()["kernel_launches"]
         evs, rays = [], 0
+        kms.clear()
         for _ in range(steps):
             with torch.cuda.stream(stream):
                 flush.zero_()                                            # L2 flush, outside the event pair
             e = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
             step_fn(e)
             evs.append(e)
-            rays += rt.timings()["rays_traced"]                          # synchronises the stream (outside the event pair)
+            tmg = rt.timings()                                           # synchronises the stream (outside the event pair)
+            rays += tmg["rays_traced"]
+            kms.append(tmg["pt_kernel_ms"])
         barrier()
         nl = rt.timings()["kernel_launches"] - lbefore
         tot = float(np.sum([e[0].elapsed_time(e[5]) for e in evs]))
@@ -449,8 +461,12 @@ def main():
             stages = [float(np.mean([e[k].elapsed_time(e[k + 1]) for e in evs])) for k in range(5)]
         return tot, stages, int(nl), int(rays)
 
+    kms = []                                    # per step: CUDA-event times of the path-trace kernels (library option kernel_timing)
+    rt.set_option("kernel_timing", 1)
     sampler = ClockSampler(local); sampler.start()
     total_ms, stages, launches, rays = timed(step_device, args.steps, args.warmup)
+    kernel_ms = np.mean(np.asarray(kms, np.float64), axis=0) if kms and not by_rows else np.zeros(6)
+    rt.set_option("kernel_timing", 0)
     sampler.stop_flag = True; sampler.join()
     e2e_steps = max(3, args.steps // 2)
     e2e_ms, e2e_rays = timed_e2e(e2e_steps, 3)
@@ -460,6 +476,7 @@ def main():
     rt.set_frame_number(2); rt.pathtrace()
     tm = rt.timings()
     node_visits, leaf_tests, rays_cnt = tm["node_visits"], tm["leaf_tests"], tm["rays_traced"]
+    r1_nodes, r1_leaves, r1_rays = tm["round_node_visits"][0], tm["round_leaf_tests"][0], tm["round_rays"][0]
     rt.set_option("count_visits", 0)
 
     t = torch.tensor([total_ms, e2e_ms] + stages, dtype=torch.float64, device="cuda")
@@ -479,6 +496,18 @@ def main():
         dn_gbs = DENOISE_BYTES_PER_PX * WIDTH * rows_n / (dn_ms * 1e-3) / 1e9
         pt_bytes = node_visits * NODE_BYTES + leaf_tests * TRI_BYTES + GBUF_BYTES_PER_PX * WIDTH * rows_n
         pt_gbs = pt_bytes / (pt_ms * 1e-3) / 1e9
+        # the dominant kernel: k_pt_trace of bounce round 1 (incoherent bounce / shadow rays).  Algorithmic bytes per launch = its own node
+        # visits x 64 B + leaf tests x 128 B (counted on the device in an untimed frame) + ray fetch 32 B + hit record 16 B + 2 queue words
+        # per ray; duration = CUDA events recorded by the library around that launch, averaged over the timed steps.
+        tr_bytes = r1_nodes * NODE_BYTES + r1_leaves * TRI_BYTES + r1_rays * (32 + 16 + 8)
+        tr_ms = float(kernel_ms[2])
+        tr_gbs = tr_bytes / (tr_ms * 1e-3) / 1e9 if tr_ms > 0 else 0.0
+        trace_roofline = {"kernel": "k_pt_trace, bounce round 1 (%.0f%% of the step)" % (100 * tr_ms / max(ms_step, 1e-9)), "bound": "hbm",
+                          "achieved": tr_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": tr_gbs / hbm_peak, "traffic": ncu_traffic("k_pt_trace_round1"),
+                          "peak_kind": peak_kind, "algorithmic_bytes_per_launch": int(tr_bytes), "ms_per_launch": tr_ms,
+                          "rays_per_launch": int(r1_rays), "node_visits_per_ray": r1_nodes / max(r1_rays, 1), "leaf_tests_per_ray": r1_leaves / max(r1_rays, 1),
+                          "note": "pointer-chasing BVH traversal without RT cores: bound by the dependent node-fetch chain (L1 hit 77 %, L2 hit 80 %, "
+                                  "14 of 32 lanes active), not by HBM; `traffic` = dram bytes of one launch from profiles/ncu_traffic.json (ncu --set full)"}
         par = (f"sample-partitioned x{world}, BVH rebuilt per GPU, NCCL all-reduce of the frame" if not by_rows else
                f"row bands x{world}, BVH {args.bvh}, NCCL all-gather of the G-buffers (30 B/px) and of the denoised frame + history (24 B/px), "
                f"denoise of band + 80-row halo")
@@ -492,13 +521,16 @@ def main():
                        "stages_ms": {"build_bvh": build_ms, "pathtrace": pt_ms, "exchange_gbuffers": xch_ms, "denoise": dn_ms, "combine": comb_ms},
                        "pathtrace_mrays_s": rays / args.steps / (pt_ms * 1e-3) / 1e6,
                        "build_mtris_s": n_tris / (build_ms * 1e-3) / 1e6},
-            "roofline": {"kernel": "k_pt_primary + k_pt_logic_first + 4 x (k_pt_trace, k_pt_logic): the path-trace stage, %.0f%% of the step"
+            "roofline": trace_roofline,
+            "roofline_pathtrace_stage": {"kernel": "k_pt_primary + k_pt_logic_first + 4 x (k_pt_trace, k_pt_logic): the path-trace stage, %.0f%% of the step"
                                    % (100 * pt_ms / max(ms_step, 1e-9)), "bound": "hbm",
                          "achieved": pt_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pt_gbs / hbm_peak, "traffic": None,
                          "peak_kind": peak_kind, "algorithmic_bytes_per_launch": int(pt_bytes),
                          "note": "latency/divergence-bound traversal (no RT cores); bytes = node visits x 64 + leaf tests x 128 + 30 B/px G-buffer "
                                  "(reference layout, SURVEY 8d 'secondary'); most of them are L1/L2 hits, see profiles/ for dram__bytes",
-                         "node_visits_per_ray": node_visits / max(rays_cnt, 1), "leaf_tests_per_ray": leaf_tests / max(rays_cnt, 1)},
+                         "node_visits_per_ray": node_visits / max(rays_cnt, 1), "leaf_tests_per_ray": leaf_tests / max(rays_cnt, 1),
+                         "kernels_ms": {"k_pt_primary": kernel_ms[0], "k_pt_logic_first": kernel_ms[1], "k_pt_trace_round1": kernel_ms[2],
+                                        "k_pt_logic_round1": kernel_ms[3], "k_pt_trace_round2": kernel_ms[4], "rest": kernel_ms[5]}},
             "roofline_build": {"kernel": "k_build_blas (gather+AABB+Morton+sort+Karras+refit+TLAS, one launch)", "bound": "hbm",
                                "achieved": build_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": build_gbs / hbm_peak,
                                "algorithmic_bytes_per_launch": BUILD_BYTES_PER_TRI * n_tris},

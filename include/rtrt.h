@@ -71,6 +71,12 @@ typedef struct rtrt_timings {
     uint64_t node_visits;         /* inner-node visits / leaf (triangle) tests of the last pathtrace; only counted  */
     uint64_t leaf_tests;          /* when option "count_visits" = 1 (adds register pressure, off by default)        */
     uint64_t rays_traced_total;   /* TraverseBvh calls of all rtrt_pathtrace calls since rtrt_create (device-side sum)  */
+    /* option "kernel_timing" = 1: CUDA-event times of the kernels of the last rtrt_pathtrace (wavefront path):
+     * [0] k_pt_primary  [1] k_pt_logic_first  [2] k_pt_trace round 1  [3] k_pt_logic round 1  [4] k_pt_trace round 2  [5] rest */
+    float pt_kernel_ms[6];
+    /* option "count_visits" = 1: node visits / leaf tests of the bounce rounds 1..4 of the last rtrt_pathtrace */
+    uint32_t round_node_visits[4], round_leaf_tests[4], round_rays[4];
+    uint32_t reserved_;
 } rtrt_timings;
 
 /* Buffers observable through rtrt_get_buffer.  The first block are the DebugPrintFile observation

@@ -318,7 +318,7 @@ class RayTracer:
     def timings(self):
         t = L.Timings()
         self._check(self._lib.rtrt_get_timings(self._h, C.byref(t)))
-        return {k: getattr(t, k) for k, _ in L.Timings._fields_}
+        return {k: (list(getattr(t, k)) if hasattr(getattr(t, k), "__len__") else getattr(t, k)) for k, _ in L.Timings._fields_ if k != "reserved_"}
 
     @property
     def stream(self):

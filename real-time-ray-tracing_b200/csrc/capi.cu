@@ -159,6 +159,7 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     dfree(c.dStage);
     dfree(c.dRayStage); dfree(c.dHitStage); dfree(c.dTicket);
     for (auto& e : c.ev) { if (e[0]) cudaEventDestroy(e[0]); if (e[1]) cudaEventDestroy(e[1]); }
+    for (auto& e : c.kev) if (e) cudaEventDestroy(e);
     for (auto& st : c.chunkStream) if (st) cudaStreamDestroy(st);
     for (auto& ev : c.chunkJoin) if (ev) cudaEventDestroy(ev);
     if (c.chunkFork) cudaEventDestroy(c.chunkFork);
@@ -257,6 +258,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
+    if (!strcmp(name, "kernel_timing")) { c.kernelTiming = value != 0; return RTRT_OK; }
     if (!strcmp(name, "pt_chunks")) { if (value < 1 || value > Context::kMaxChunks) return c.fail(RTRT_ERR_ARG, "pt_chunks must be 1..8"); c.ptChunks = (int)value; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }
     return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: unknown option");
@@ -442,6 +444,18 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
         RTRT_CUDA(c, cudaMemcpy(r, c.dRayCounter, sizeof(r), cudaMemcpyDeviceToHost));
         c.timings.rays_traced = r[0]; c.timings.node_visits = r[1]; c.timings.leaf_tests = r[2]; c.raysOnDevice = false;
         c.timings.rays_traced_total = r[4];
+    }
+    if (c.kevPending) {
+        for (int k = 0; k < 6; ++k) {
+            float ms = 0.0f;
+            c.timings.pt_kernel_ms[k] = (cudaEventElapsedTime(&ms, c.kev[k], c.kev[k + 1]) == cudaSuccess) ? ms : 0.0f;
+        }
+        c.kevPending = false;
+    }
+    if (c.countVisits && c.dWf) {                        // per-round diagnostics of the wavefront counters (pathtrace_wf.cu)
+        uint32_t w[64];
+        RTRT_CUDA(c, cudaMemcpy(w, c.dWf, sizeof(w), cudaMemcpyDeviceToHost));
+        for (int r = 0; r < 4; ++r) { c.timings.round_rays[r] = w[r]; c.timings.round_node_visits[r] = w[56 + r]; c.timings.round_leaf_tests[r] = w[60 + r]; }
     }
     c.timings.kernel_launches = c.launches;
     *out = c.timings;

@@ -88,6 +88,7 @@ struct Context {
     unsigned long long launches = 0;                     // kernels launched by this library
     cudaEvent_t ev[4][2] = {};                           // [build, traverse, pathtrace, denoise][begin, end]
     bool evPending[4] = {false, false, false, false};
+    bool kernelTiming = false; cudaEvent_t kev[7] = {}; bool kevPending = false;   // option kernel_timing: boundaries of the path-trace kernels
     bool raysOnDevice = false;                           // rays_traced of the last pathtrace still in dRayCounter
     rtrt_timings timings{};
 

@@ -238,6 +238,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
                     if (COUNT) {
                         nodeVisits += s.nodeVisits; leafTests += s.leafTests;
                         atomicMax(fetchPtr + 32, (uint32_t)s.it); atomicAdd(fetchPtr + 40, (uint32_t)s.it);      // diagnostics: [40+r] max, [48+r] sum of iterations
+                        atomicAdd(fetchPtr + 48, s.nodeVisits); atomicAdd(fetchPtr + 52, s.leafTests);          // [56+r] node visits, [60+r] leaf tests of the round
                     }
                     active = false; finishedNow = true;
                 }
@@ -374,11 +375,18 @@ static int chunk_rows(int localRows, int K, int k) {
 static void launch_chunk(Context& c, const PathTraceParams& P, const WfBuffers& B, cudaStream_t st, int smCount) {
     const int rows = P.chunkRows;
     const dim3 grid((c.width + kPtBlockX - 1) / kPtBlockX, (rows + kPtBlockY - 1) / kPtBlockY), block(kPtBlockX, kPtBlockY);
+    const bool kt = c.kernelTiming && P.chunks == 1;
+    if (kt) {
+        for (auto& e : c.kev) if (!e) cudaEventCreate(&e);
+        cudaEventRecord(c.kev[0], st);
+    }
     if (c.countVisits) k_pt_primary<true><<<grid, block, 0, st>>>(P, B);
     else k_pt_primary<false><<<grid, block, 0, st>>>(P, B);
+    if (kt) cudaEventRecord(c.kev[1], st);
     const int tiles = ((c.width + 7) / 8) * ((rows + 3) / 4);
     k_pt_logic_first<<<(tiles + kLogicThreads / 32 - 1) / (kLogicThreads / 32), kLogicThreads, 0, st>>>(P, B, B.counters + 0);
     c.launches += 2;
+    if (kt) cudaEventRecord(c.kev[2], st);
     // persistent grids sized for the chunk: at most one CTA per 128 pixels, never more than are resident at once
     static int traceResident = 0;
     if (!traceResident) {
@@ -393,11 +401,14 @@ static void launch_chunk(Context& c, const PathTraceParams& P, const WfBuffers& 
         uint32_t* cnt = B.counters;
         if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
         else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
+        if (kt && round < 2) cudaEventRecord(c.kev[3 + 2 * round], st);
         k_pt_logic<<<logicGrid, kLogicThreads, 0, st>>>(P, B, cnt + 16 + round, cnt + 24 + round, cnt + round + 1);
+        if (kt && round == 0) cudaEventRecord(c.kev[4], st);
         c.launches += 2;
     }
     k_pt_count_rays<<<1, 1, 0, st>>>(B.counters, (unsigned long long)c.width * rows, c.dRayCounter);
     c.launches += 1;
+    if (kt) { cudaEventRecord(c.kev[6], st); c.kevPending = true; }
 }
 
 int launch_pathtrace_wavefront(Context& c) {
