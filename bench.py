@@ -172,7 +172,7 @@ def run_reference(args, rank, world):
             "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": arm.sample},
             "cpu_baseline": cb, "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
 
 
 class DevView:
@@ -181,6 +181,25 @@ class DevView:
     def __init__(self, ptr, nbytes, typestr="<f2", itemsize=2):
         self.__cuda_array_interface__ = {"shape": (nbytes // itemsize,), "typestr": typestr, "data": (ptr, False), "version": 3,
                                          "strides": None}
+
+
+# stdout carries exactly ONE JSON line: everything else that writes to fd 1 while the program runs (NCCL's version banner, the
+# reference kernels' device printf) is sent to stderr; the line itself goes to the saved descriptor.
+_REAL_STDOUT = None
+
+
+def divert_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
 def ncu_traffic(key):
@@ -316,7 +335,7 @@ def run_c5(args, rank, world, local, torch, dist, pkg):
                 "e2e": {"value": rays_step / (e2e_step * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_step, "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": int(h_out.numel()), "note": "static scene: no per-step upload; the accumulated frame is read back"},
                 "gpu_launches": int(res["device"][2]), "clocks": sampler.summary()}
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     rt.cleanup()
 
 
@@ -334,6 +353,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-kernels", action="store_true")
     args = ap.parse_args()
+    divert_stdout()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -550,7 +570,7 @@ def main():
                 line["reference_kernels"] = reference_kernels(pkg, rt, pos, nrm, idx, cam, rays / args.steps)
         if not args.no_cpu_baseline and world == 1:
             _, _, line["cpu_baseline"] = CpuArm(pkg).baseline(steps=1, warmup=0)
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     rt.cleanup()
     if world > 1:
         dist.destroy_process_group()
