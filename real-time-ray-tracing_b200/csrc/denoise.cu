@@ -129,12 +129,20 @@ __device__ __forceinline__ void block_noise_levels(const DnParams& P, const usho
 // the difference is one ulp of a value that is then raised to a power with 1e-4 relative error anyway)
 VD float dot_plain(Float3 a, Float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
-VD float bilateral_weight(Float3 n0, Float3 n1, float d0, float d1, bool maskDiffers, float sigN, float sigD, float sigM, float floorDot, float g) {
-    float w = 1.0f;
-    w *= __powf(sel_max(dot_plain(n0, n1), floorDot), sigN);
-    const float dd = (d0 - d1) / sigD;
-    w *= __expf(-0.5f * dd * dd);
-    w *= maskDiffers ? 1.0f / sigM : 1.0f;
+// The two factors share one exponential:  max(dot,floor)^sigN * exp(-dd^2/2) = 2^(sigN*log2(max(dot,floor)) - (log2 e / 2) dd^2)
+// with dd = (d0 - d1) * (1/sigD): one MUFU.LG2, one MUFU.EX2 and no division per tap.  BilateralK holds the per-filter constants
+// (1/sigD and 1/sigM are rounded once per thread; the reference divides per tap, which differs by an ulp of dd — far inside 2e-2).
+struct BilateralK { float sigN, invD, invM, floorDot; };
+VD BilateralK bilateral_k(float sigN, float sigD, float sigM, float floorDot) { return BilateralK{sigN, 1.0f / sigD, 1.0f / sigM, floorDot}; }
+VD float fast_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+VD float fast_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+VD float bilateral_weight(Float3 n0, Float3 n1, float d0, float d1, bool maskDiffers, const BilateralK& k, float g) {
+    const float dn = sel_max(dot_plain(n0, n1), k.floorDot);
+    const float ln = (k.sigN == 0.0f) ? 0.0f : k.sigN * fast_lg2(dn);            // x^0 = 1 also for x = 0 (log2 0 = -inf)
+    const float dd = (d0 - d1) * k.invD;
+    float w = fast_ex2(ln - 0.72134752044448170368f * (dd * dd));                // log2(e) / 2
+    w *= maskDiffers ? k.invM : 1.0f;
     w *= g;
     return w;
 }
@@ -179,6 +187,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
         const float depthValue = h2f(cg.w);
         const unsigned short maskValue = result.w;
         if (!(depthValue >= kRayMax)) {
+            const BilateralK bk = bilateral_k(P.temp_n, P.temp_d, P.temp_m, 0.0f);
             Float3 nMax = rgb_to_ycocg(colorValue), nMin = nMax, filtered = f3(0.0f);
             float wsum = 0.0f;
 #pragma unroll
@@ -187,7 +196,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
                 const int si = (threadIdx.y + yo) * T + threadIdx.x + xo;
                 const ushort4 q = sC[si], g = sG[si];
                 const Float3 color = px_rgb(q);
-                const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, P.temp_n, P.temp_d, P.temp_m, 0.0f, cG3[j]);
+                const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, bk, cG3[j]);
                 filtered = filtered + color * w; wsum += w;
                 const Float3 nc = rgb_to_ycocg(color);
                 nMax = max3f(nMax, nc); nMin = min3f(nMin, nc);
@@ -260,6 +269,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
         const float depthValue = h2f(cg.w);
         const unsigned short maskValue = result.w;
         if (!(depthValue >= kRayMax)) {
+            const BilateralK bk = bilateral_k(P.local_n, P.local_d, P.local_m, 0.0001f);
             Float3 sumC = f3(0.0f); float sumW = 0.0f;
             int j = P.frameNum % 2;
 #pragma unroll 4
@@ -267,7 +277,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
                 const int xo = j % 7, yo = j / 7;
                 const int si = (threadIdx.y + yo) * T + threadIdx.x + xo;
                 const ushort4 q = sC[si], g = sG[si];
-                const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, P.local_n, P.local_d, P.local_m, 0.0001f, cG7[j]);
+                const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, bk, cG7[j]);
                 sumC = sumC + px_rgb(q) * w; sumW += w;
                 j += 2;
             }
@@ -305,6 +315,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ush
         const float depthValue = h2f(cg.w);
         const unsigned short maskValue = result.w;
         if (!(depthValue >= 10e9f)) {
+            const BilateralK bk = bilateral_k(P.large_n, P.large_d, P.large_m, 0.0f);
             Float3 sumC = f3(0.0f); float sumW = 0.0f;
 #pragma unroll 5
             for (int k = 0; k < 25; ++k) {
@@ -313,8 +324,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ush
                 const size_t g = (size_t)sy * P.W + sx;
                 const ushort4 q = __ldg(in + g), gg = __ldg(P.guide + g);
                 Float3 color = px_rgb(q);
-                float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w,
-                                           P.large_n, P.large_d, P.large_m, 0.0f, cG5[k]);
+                float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w, bk, cG5[k]);
                 if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
                 sumC = sumC + color * w; sumW += w;
             }
