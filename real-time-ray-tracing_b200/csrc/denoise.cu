@@ -317,16 +317,22 @@ __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ush
         if (!(depthValue >= 10e9f)) {
             const BilateralK bk = bilateral_k(P.large_n, P.large_d, P.large_m, 0.0f);
             Float3 sumC = f3(0.0f); float sumW = 0.0f;
-#pragma unroll 5
-            for (int k = 0; k < 25; ++k) {
-                const int i = k % 5, j = k / 5;
-                const int sx = clampi(x + (i - 2) * S, 0, P.W - 1), sy = clampi(y + (j - 2) * S, 0, P.H - 1);
-                const size_t g = (size_t)sy * P.W + sx;
-                const ushort4 q = __ldg(in + g), gg = __ldg(P.guide + g);
-                Float3 color = px_rgb(q);
-                float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w, bk, cG5[k]);
-                if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
-                sumC = sumC + color * w; sumW += w;
+            // rows outside, columns inside, both fully unrolled: tap offsets and Gaussian weights are immediates, the row clamp and the
+            // row base are computed 5 times instead of 25 (same tap order k = 5 j + i as the reference loop)
+#pragma unroll
+            for (int j = 0; j < 5; ++j) {
+                const int sy = clampi(y + (j - 2) * S, 0, P.H - 1);
+                const size_t row = (size_t)sy * P.W;
+#pragma unroll
+                for (int i = 0; i < 5; ++i) {
+                    const int sx = clampi(x + (i - 2) * S, 0, P.W - 1);
+                    const size_t g = row + sx;
+                    const ushort4 q = __ldg(in + g), gg = __ldg(P.guide + g);
+                    Float3 color = px_rgb(q);
+                    float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w, bk, cG5[5 * j + i]);
+                    if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
+                    sumC = sumC + color * w; sumW += w;
+                }
             }
             if (isnan3(sumC)) sumC = f3(0.0f);
             if (sumW != sumW) sumW = 0.0f;
