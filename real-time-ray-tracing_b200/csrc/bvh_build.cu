@@ -15,10 +15,6 @@
 namespace rtrt {
 
 constexpr int kBuildThreads = 512;
-#ifndef RTRT_GATHER_UNROLL
-#define RTRT_GATHER_UNROLL 4
-#endif
-constexpr int kGatherUnroll = RTRT_GATHER_UNROLL;
 #ifndef RTRT_BUILD_MINB
 #define RTRT_BUILD_MINB 3          // 3 CTAs/SM: <= 40 registers/thread and <= 75 KB shared memory per CTA
 #endif
@@ -85,9 +81,6 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     const uint32_t count = (b == p.numBatches - 1) ? (p.numTris - kSeg * (p.numBatches - 1)) : (uint32_t)kSeg;  // src/init.cu:129-130
     const uint32_t active = (count + 3u) & ~3u;     // src/updateGeometry.cuh:93 : threads own 4 items each
 
-    // ---- gather + Triangle emit: 8 lanes per triangle, one 16-byte row each -> 512 contiguous bytes per warp store.
-    // rows: 0..2 = v1..v3, 3 = v4 (unused), 4..6 = n1..n3, 7 = n4 (unused)          src/updateGeometry.cuh:131-137
-    const int sub = lane & 7, grp = lane >> 3;
     float4* tri4 = reinterpret_cast<float4*>(p.triangles + base);
     // ---- stage the batch's 3 x 1024 vertex indices in shared memory: one fully coalesced 12-KB read instead of a 4-byte load per
     // lane in front of every dependent vertex load (pad items read index 0, src/init.cu:103-115).  Lives in the upper half of
@@ -99,35 +92,71 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     }
     __syncthreads();
     float accMin = FLT_MAX, accMax = -FLT_MAX;           // this lane's axis of the batch box
-#pragma unroll(kGatherUnroll)
-    for (int it = 0; it < kSeg / (NW * 4); ++it) {
-        const uint32_t i = (uint32_t)(it * NW + warp) * 4u + grp;          // batch-local item
-        const bool on = i < active;
-        Float3 val{0.0f, 0.0f, 0.0f};
-        if (on && (sub & 3) != 3) {
-            const uint32_t vid = sIdx[3u * i + (sub & 3)];
-            val = ld3(sub < 4 ? p.pos : p.nrm, vid);
+    // ---- gather + Triangle emit (src/updateGeometry.cuh:100-184).  One FLOAT per lane: three consecutive lanes read the x, y, z of
+    // one vertex, so a warp-wide load touches 10 vertices (about one L1 wavefront each) instead of one component of 24 different
+    // vertices three times over.  A warp step covers 8 triangles = 48 vertices = 5 loads per lane; the floats are staged in a
+    // per-warp shared-memory tile of 8 x 6 float4 rows (w stays 0), from which the per-axis AABB lanes and the two fully coalesced
+    // 512-byte Triangle stores of the step read.  The tile lives in keys[]/ids[] (12 KB), which nothing touches before the Morton
+    // keys are written.  (Measured on B200, 1 M triangles: row-per-lane gather 0.173 ms -> 0.166 ms; keeping the next step's loads
+    // in flight in registers gained nothing — 48 warps per SM already cover the latency.)
+    constexpr int kTps = 8, kSteps = kSeg / (NW * kTps);
+    static_assert(NW * kTps * 6 * sizeof(float4) <= sizeof(s.keys) + sizeof(s.ids), "gather tile");
+    float4* stageAll = reinterpret_cast<float4*>(&s.keys[0][0]);
+    float4* stageW = stageAll + warp * (kTps * 6);
+    for (int e = lane; e < kTps * 6; e += 32) stageW[e] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float* stageF = reinterpret_cast<float*>(stageW);
+    const float4* stageR = stageW;
+    __syncwarp();
+    // Three lanes per vertex (x, y, z), ten vertices per warp-wide load; the 48 vertex slots of a step are numbered row-major
+    // (slot = 8 r6 + t: r6 = 0..2 positions v1..v3, 3..5 normals n1..n3 of triangle t), so slot -> (t, r6) is a shift and a mask.
+    const int vl = lane / 3, vc = lane - 3 * vl;
+    auto issue = [&](int st, float (&v)[5]) {
+        const uint32_t i0 = (uint32_t)(st * NW + warp) * kTps;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const int vs = 10 * j + vl, t = vs & 7, r6 = vs >> 3;
+            v[j] = 0.0f;
+            if (vl < 10 && vs < kTps * 6) {     // items past `active` read index 0 like the pad items (sIdx holds 0 there)
+                const uint32_t vid = sIdx[3u * (i0 + t) + (r6 >= 3 ? r6 - 3 : r6)];
+                v[j] = __ldg((r6 < 3 ? p.pos : p.nrm) + (3u * vid + vc));
+            }
         }
-        if (on) tri4[(size_t)i * 8 + sub] = make_float4(val.x, val.y, val.z, 0.0f);
-        const int l0 = lane & ~7;
-        const Float3 v1{__shfl_sync(0xffffffffu, val.x, l0), __shfl_sync(0xffffffffu, val.y, l0), __shfl_sync(0xffffffffu, val.z, l0)};
-        const Float3 v2{__shfl_sync(0xffffffffu, val.x, l0 + 1), __shfl_sync(0xffffffffu, val.y, l0 + 1), __shfl_sync(0xffffffffu, val.z, l0 + 1)};
-        const Float3 v3{__shfl_sync(0xffffffffu, val.x, l0 + 2), __shfl_sync(0xffffffffu, val.y, l0 + 2), __shfl_sync(0xffffffffu, val.z, l0 + 2)};
-        if (on && sub < 3) {
-            // lanes 0..2 of the group take one axis each (x, y, z): a third of the arithmetic per lane, three times the active lanes
-            const float a = sub == 0 ? v1.x : (sub == 1 ? v1.y : v1.z);
-            const float b = sub == 0 ? v2.x : (sub == 1 ? v2.y : v2.z);
-            const float c = sub == 0 ? v3.x : (sub == 1 ? v3.y : v3.z);
-            const float mn = sel_min(a, sel_min(b, c));                                       // :172-177
-            float mx = sel_max(a, sel_max(b, c));
-            const float eps = 1.1920928955078125e-07f;                                        // MachineEpsilon()
-            mx = mn + sel_max(mx - mn, eps * mx);
-            float* lb = reinterpret_cast<float*>(&s.leafBox[i]);                              // AABB = {min.xyz, max.xyz}
-            lb[sub] = mn; lb[3 + sub] = mx;
-            reinterpret_cast<float*>(&s.scratch.centre[i])[sub] = ((a + b) + c) / 3.0f;       // :180
-            accMin = sel_min(accMin, mn); accMax = sel_max(accMax, mx);
+    };
+    float cur[5];
+#pragma unroll 2
+    for (int st = 0; st < kSteps; ++st) {
+        issue(st, cur);
+        const uint32_t i0 = (uint32_t)(st * NW + warp) * kTps;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const int vs = 10 * j + vl, t = vs & 7, r6 = vs >> 3;
+            if (vl < 10 && vs < kTps * 6) stageF[(t * 6 + r6) * 4 + vc] = cur[j];
         }
+        __syncwarp();
+        {   // per-axis AABB / centre: lane = 4 t + axis
+            const int t = lane >> 2, ax = lane & 3;
+            const uint32_t i = i0 + t;
+            if (ax < 3 && i < active) {
+                const float a = stageF[(t * 6 + 0) * 4 + ax], b = stageF[(t * 6 + 1) * 4 + ax], c = stageF[(t * 6 + 2) * 4 + ax];
+                const float mn = sel_min(a, sel_min(b, c));                                       // src/updateGeometry.cuh:172-177
+                float mx = sel_max(a, sel_max(b, c));
+                const float eps = 1.1920928955078125e-07f;                                        // MachineEpsilon()
+                mx = mn + sel_max(mx - mn, eps * mx);
+                float* lb = reinterpret_cast<float*>(&s.leafBox[i]);                              // AABB = {min.xyz, max.xyz}
+                lb[ax] = mn; lb[3 + ax] = mx;
+                reinterpret_cast<float*>(&s.scratch.centre[i])[ax] = ((a + b) + c) / 3.0f;       // :180
+                accMin = sel_min(accMin, mn); accMax = sel_max(accMax, mx);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {       // Triangle emit: rows 0..2 = v1..v3, 3 = v4 (unused), 4..6 = n1..n3, 7 = n4 (unused)   :131-137
+            const int q = 32 * k + lane, t = q >> 3, r = q & 7;
+            const uint32_t i = i0 + t;
+            if (i < active) tri4[(size_t)i * 8 + r] = (r & 3) == 3 ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : stageR[t * 6 + (r < 4 ? r : r - 1)];
+        }
+        __syncwarp();
     }
+    const int sub = lane & 3;               // the axis this lane accumulated
     AABB mine = aabb_empty();
     if (sub == 0) { mine.min.x = accMin; mine.max.x = accMax; }
     else if (sub == 1) { mine.min.y = accMin; mine.max.y = accMax; }
@@ -135,7 +164,11 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     const AABB batchBox = block_reduce_aabb<NT>(s, mine);     // barriers inside also publish leafBox/centre
 
     // ---- per-item AABB array (24 KB contiguous per batch) + Morton keys ----
-    {
+    if (active == (uint32_t)kSeg) {                          // 24 KB = 1536 float4, three per thread
+        const float4* lb = reinterpret_cast<const float4*>(s.leafBox);
+        float4* ga = reinterpret_cast<float4*>(p.aabbs + base);
+        for (int e = tid; e < kSeg * 6 / 4; e += NT) ga[e] = lb[e];
+    } else {
         const float* lb = reinterpret_cast<const float*>(s.leafBox);
         float* ga = reinterpret_cast<float*>(p.aabbs + base);
         for (uint32_t e = tid; e < active * 6u; e += NT) ga[e] = lb[e];

@@ -159,27 +159,79 @@ __global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict
 }
 
 // -------------------------------------------------------------------------------------------------------------------
+// Tile staging through the TMA unit.  The two spatially filtered passes with a shared-memory tile (TemporalFilter: 16x16 pixels
+// + 1-pixel halo, SpatialFilter7x7: + 3-pixel halo) read their colour and guide tiles with one bulk asynchronous copy
+// (cp.async.bulk, global -> shared, completion on an mbarrier) per tile row and image instead of two loads, two stores and the
+// clamp arithmetic per pixel and thread.  A bulk copy needs 16-byte aligned addresses and sizes and the pixels are 8 bytes, so the
+// staged row starts one pixel left of the halo (an even x) and is T + 2 pixels long; the tile is addressed with that pitch (TP)
+// and offset (OX = 1) on both paths.  Rows are clamped to the image per copy (surface clamp addressing in y); CTAs whose row
+// range crosses the left / right image border need per-pixel clamping in x and take the per-thread path, as do gated tiles of
+// SpatialFilter7x7 (they only need their own 16x16 pixels) and images with an odd width.
+// -------------------------------------------------------------------------------------------------------------------
+VD uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+template <int T, int HALO>
+struct TileStage {
+    static_assert((HALO & 1) == 1 && (T & 1) == 0, "the aligned row start below assumes an odd halo and an even tile size");
+    static constexpr int OX = 1, TP = T + 2;
+    static constexpr uint32_t kRowBytes = TP * sizeof(ushort4);
+    // lo..hi = the part of the tile (in tile coordinates) that the per-thread path must fill
+    static __device__ __forceinline__ void load(const DnParams& P, const ushort4* __restrict__ in, ushort4* sC, ushort4* sG, unsigned long long* mbar,
+                                                int tid, int bx, int by, int lo, int hi, bool wantTma) {
+        const int x0 = bx * 16 - HALO, y0 = by * 16 - HALO, xa = x0 - OX;
+        const bool tma = wantTma && (P.W & 1) == 0 && xa >= 0 && xa + TP <= P.W &&
+                         ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(P.guide)) & 15) == 0;      // uniform per CTA
+        if (tma) {
+            if (tid == 0) {
+                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(mbar)));
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            }
+            __syncthreads();
+            if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(mbar)), "r"(2u * T * kRowBytes) : "memory");
+            if (tid < 2 * T) {
+                const int img = tid >= T, ly = tid - img * T;
+                const int gy = clampi(y0 + ly, 0, P.H - 1);
+                const ushort4* src = (img ? P.guide : in) + (size_t)gy * P.W + xa;
+                ushort4* dst = (img ? sG : sC) + ly * TP;
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"(smem_u32(dst)), "l"(src), "r"(kRowBytes), "r"(smem_u32(mbar)) : "memory");
+            }
+            uint32_t done = 0;
+            while (!done) {
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(smem_u32(mbar)) : "memory");
+            }
+        } else {
+            for (int i = tid; i < T * T; i += 256) {
+                const int lx = i % T, ly = i / T;
+                if (lx < lo || lx >= hi || ly < lo || ly >= hi) continue;
+                const int gx = clampi(x0 + lx, 0, P.W - 1), gy = clampi(y0 + ly, 0, P.H - 1);
+                const size_t g = (size_t)gy * P.W + gx;
+                sC[ly * TP + lx + OX] = __ldg(in + g);
+                sG[ly * TP + lx + OX] = __ldg(P.guide + g);
+            }
+            __syncthreads();
+        }
+    }
+};
+
+// -------------------------------------------------------------------------------------------------------------------
 // Pass A: TemporalFilter (+ tile noise of its output).  16x16 pixels per CTA, 18x18 staged tile.
 // -------------------------------------------------------------------------------------------------------------------
 template <bool FILTER>
 __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ushort4* __restrict__ in, const ushort4* __restrict__ accum, ushort4* __restrict__ out) {
     constexpr int T = 18;
-    __shared__ ushort4 sC[T * T];
-    __shared__ ushort4 sG[T * T];            // normal.xyz (half) + depth (half)
+    using Stage = TileStage<T, 1>;
+    constexpr int TP = Stage::TP, OX = Stage::OX;
+    __shared__ __align__(128) ushort4 sC[T * TP];
+    __shared__ __align__(128) ushort4 sG[T * TP];            // normal.xyz (half) + depth (half)
+    __shared__ __align__(8) unsigned long long mbar;
     __shared__ ushort4 sOut[256];
     __shared__ unsigned short sDepth[256];
     __shared__ float sN8[4];
     const int tid = threadIdx.y * 16 + threadIdx.x;
-    const int x0 = blockIdx.x * 16 - 1, y0 = (blockIdx.y + P.by0) * 16 - 1;
-    for (int i = tid; i < T * T; i += 256) {
-        const int gx = clampi(x0 + i % T, 0, P.W - 1), gy = clampi(y0 + i / T, 0, P.H - 1);
-        const size_t g = (size_t)gy * P.W + gx;
-        sC[i] = __ldg(in + g);
-        sG[i] = __ldg(P.guide + g);
-    }
-    __syncthreads();
+    Stage::load(P, in, sC, sG, &mbar, tid, blockIdx.x, blockIdx.y + P.by0, 0, T, true);
     const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
-    const int ci = (threadIdx.y + 1) * T + threadIdx.x + 1;
+    const int ci = (threadIdx.y + 1) * TP + threadIdx.x + 1 + OX;
     ushort4 result = sC[ci];
     const ushort4 cg = sG[ci];
     if (FILTER && x < P.W && y < P.H) {
@@ -193,7 +245,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
 #pragma unroll
             for (int j = 0; j < 9; ++j) {
                 const int xo = j % 3, yo = j / 3;
-                const int si = (threadIdx.y + yo) * T + threadIdx.x + xo;
+                const int si = (threadIdx.y + yo) * TP + threadIdx.x + xo + OX;
                 const ushort4 q = sC[si], g = sG[si];
                 const Float3 color = px_rgb(q);
                 const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, bk, cG3[j]);
@@ -241,27 +293,21 @@ template <bool FILTER>
 __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, ushort4* __restrict__ accumOut,
                                                      const __half* __restrict__ gate16, int wantNoise) {
     constexpr int T = 22;
-    __shared__ ushort4 sC[T * T];
-    __shared__ ushort4 sG[T * T];
+    using Stage = TileStage<T, 3>;
+    constexpr int TP = Stage::TP, OX = Stage::OX;
+    __shared__ __align__(128) ushort4 sC[T * TP];
+    __shared__ __align__(128) ushort4 sG[T * TP];
+    __shared__ __align__(8) unsigned long long mbar;
     __shared__ ushort4 sOut[256];
     __shared__ unsigned short sDepth[256];
     __shared__ float sN8[4];
     const int tid = threadIdx.y * 16 + threadIdx.x;
-    const int x0 = blockIdx.x * 16 - 3, y0 = (blockIdx.y + P.by0) * 16 - 3;
     bool active = FILTER;
     if (FILTER) active = !(__half2float(__ldg(gate16 + (size_t)(blockIdx.y + P.by0) * ((P.W + 15) / 16) + blockIdx.x)) < P.thr_local);
     const int lo = active ? 0 : 3, hi = active ? T : T - 3;          // gated tiles only need their own 16x16 pixels
-    for (int i = tid; i < T * T; i += 256) {
-        const int lx = i % T, ly = i / T;
-        if (lx < lo || lx >= hi || ly < lo || ly >= hi) continue;
-        const int gx = clampi(x0 + lx, 0, P.W - 1), gy = clampi(y0 + ly, 0, P.H - 1);
-        const size_t g = (size_t)gy * P.W + gx;
-        sC[i] = __ldg(in + g);
-        sG[i] = __ldg(P.guide + g);
-    }
-    __syncthreads();
+    Stage::load(P, in, sC, sG, &mbar, tid, blockIdx.x, blockIdx.y + P.by0, lo, hi, active);
     const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
-    const int ci = (threadIdx.y + 3) * T + threadIdx.x + 3;
+    const int ci = (threadIdx.y + 3) * TP + threadIdx.x + 3 + OX;
     ushort4 result = sC[ci];
     const ushort4 cg = sG[ci];
     if (active && x < P.W && y < P.H) {
@@ -275,7 +321,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
 #pragma unroll 4
             for (int i = 0; i < 24; ++i) {
                 const int xo = j % 7, yo = j / 7;
-                const int si = (threadIdx.y + yo) * T + threadIdx.x + xo;
+                const int si = (threadIdx.y + yo) * TP + threadIdx.x + xo + OX;
                 const ushort4 q = sC[si], g = sG[si];
                 const float w = bilateral_weight(normalValue, px_rgb(g), depthValue, h2f(g.w), maskValue != q.w, bk, cG7[j]);
                 sumC = sumC + px_rgb(q) * w; sumW += w;
