@@ -195,6 +195,10 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
  *   "pt_chunks"           1    : rtrt_pathtrace splits the frame into this many independent sets of 8-row strips and runs their
  *                                wavefront pipelines on side streams, so that the latency tail of one set's bounce rounds overlaps
  *                                the bulk of another's (1..8; results do not depend on it; measured slower than 1 on B200, kept for experiments)
+ *   "any_hit_rays"        1    : inside rtrt_pathtrace (wavefront path), shadow rays and the rays of the last path segment stop at
+ *                                the first accepted triangle: only "reaches the sky or not" is used of them (the reference completes
+ *                                the closest-hit search and classifies afterwards, src/traverse.cuh:37-48).  Frame outputs are
+ *                                identical with 0 and 1; 0 reproduces the reference's per-ray visit counts
  *   "assume_bvh_valid"    0/1  : mark the BVH arrays as built (they were filled from outside, e.g. an NCCL broadcast from
  *                                the rank that built them) or as stale
  *   "global_sort"         0/1  : rtrt_build_bvh first sorts the triangles by the 60-bit Morton code of their centroid in the

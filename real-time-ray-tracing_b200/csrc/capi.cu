@@ -258,6 +258,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }
+    if (!strcmp(name, "any_hit_rays")) { c.anyHitRays = value != 0; return RTRT_OK; }
     if (!strcmp(name, "kernel_timing")) { c.kernelTiming = value != 0; return RTRT_OK; }
     if (!strcmp(name, "pt_chunks")) { if (value < 1 || value > Context::kMaxChunks) return c.fail(RTRT_ERR_ARG, "pt_chunks must be 1..8"); c.ptChunks = (int)value; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }

@@ -41,6 +41,7 @@ struct Context {
     bool countVisits = false;
     bool wavefront = true;                 // path-trace driver: wavefront queues (default) or the single megakernel
     void* dWf = nullptr; size_t wfBytes = 0;   // wavefront path state + queues (pathtrace_wf.cu)
+    bool anyHitRays = true;                    // option any_hit_rays: shadow / last-segment rays stop at the first accepted triangle
     int ptChunks = 1;                          // option pt_chunks: independent pixel chunks of one frame, pipelined on side streams
     static constexpr int kMaxChunks = 8;
     cudaStream_t chunkStream[kMaxChunks] = {}; cudaEvent_t chunkFork = nullptr; cudaEvent_t chunkJoin[kMaxChunks] = {};

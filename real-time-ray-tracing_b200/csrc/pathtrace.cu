@@ -113,6 +113,7 @@ void fill_pathtrace_params(Context& c, PathTraceParams& P) {
     P.rowBegin = c.rowBegin; P.rowEnd = c.rowEnd;
     P.stripH = c.stripH; P.stripShards = c.stripShards; P.stripShard = c.stripShard; P.localRows = local_rows(c);
     P.chunks = 1; P.chunk = 0; P.chunkRows = P.localRows;
+    P.anyHitRays = c.anyHitRays ? 1 : 0;
     P.color = reinterpret_cast<ushort4*>(c.dColor); P.normal = reinterpret_cast<ushort4*>(c.dNormal);
     P.albedo = reinterpret_cast<ushort4*>(c.dAlbedo); P.depth = reinterpret_cast<__half*>(c.dDepth);
     P.motion = reinterpret_cast<__half2*>(c.dMotion);

@@ -22,6 +22,7 @@ struct PathTraceParams {
     int chunks, chunk, chunkRows;                          // this launch covers the local 8-row strips s with s % chunks == chunk
     ushort4* color; ushort4* normal; ushort4* albedo; __half* depth; __half2* motion;
     unsigned long long* rayCounter;
+    int anyHitRays;                                        // option any_hit_rays (wavefront path): see kAnyHitBit in pathtrace_wf.cu
 };
 
 // row jj of this launch's chunk (0 .. chunkRows-1) -> local row of the context (0 .. localRows-1)

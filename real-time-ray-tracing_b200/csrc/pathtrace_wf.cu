@@ -121,15 +121,25 @@ VD void finalize_path(const PathTraceParams& P, const RayState& r, unsigned shor
 }
 
 // warp-aggregated append of this lane's pixel to a queue; must be reached by every lane of the warp
-VD void queue_append(bool emit, uint32_t pix, uint32_t* queue, uint32_t* counter, int lane) {
+VD void queue_append(bool emit, uint32_t entry, uint32_t* queue, uint32_t* counter, int lane) {
     const unsigned m = __ballot_sync(0xffffffffu, emit);
     if (m == 0u) return;
     const int leader = __ffs(m) - 1;
     uint32_t base = 0;
     if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
-    if (emit) queue[base + __popc(m & ((1u << lane) - 1u))] = pix;
+    if (emit) queue[base + __popc(m & ((1u << lane) - 1u))] = entry;
 }
+
+// Ray-queue entry = pixel id | kAnyHitBit.  The bit marks rays for which only "does the ray reach the sky" matters, so the traversal
+// may stop at the first accepted triangle instead of completing the closest-hit search (the reference always completes it,
+// src/traverse.cuh:37-48, and classifies afterwards):
+//   * shadow rays: any geometry in the way sets isOccluded (the sampled light is always the environment, kEnvLightId), which
+//     turns every later segment into a no-op and the radiance into 0;
+//   * every ray of the last segment (intersect #4): nothing follows but GetLightSource, which is 0 unless the ray missed.
+// The traversal is the reference's up to the first acceptance, so "hit anything" is decided identically (iteration cap and
+// dropped pushes included) and all frame outputs are unchanged; only the hit record of such a ray is not the closest one.
+constexpr uint32_t kAnyHitBit = 0x80000000u;
 
 VD AABB scene_box(const SceneView& sc) {                     // merged box of TLAS node 0 (src/traverse.h:127-129)
     const float4 a = __ldg(sc.tlasRows), b = __ldg(sc.tlasRows + 1), c = __ldg(sc.tlasRows + 2);
@@ -204,6 +214,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
     const int refillIdle = perWarp >= 32u ? kRefillIdle : 1;
     bool active = false, exhausted = false;
     uint32_t pix = 0;
+    int anyHit = 0;
     RayPrep rp; TravState s;
     uint32_t nodeVisits = 0, leafTests = 0;
     trav_init(s);
@@ -219,7 +230,8 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
             if (!active && ((idle >> lane) & 1u)) {
                 const uint32_t q = base + __popc(idle & ((1u << lane) - 1u));
                 if (q < n) {
-                    pix = __ldg(queue + q);
+                    const uint32_t entry = __ldg(queue + q);
+                    pix = entry & ~kAnyHitBit; anyHit = (int)(entry >> 31);
                     const float4 o = B.st0[pix], d = B.st1[pix];
                     rp = prepare_ray(Float3{o.x, o.y, o.z}, Float3{d.x, d.y, d.z}, sceneBox);
                     trav_init(s);
@@ -233,7 +245,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
         while (true) {
             bool finishedNow = false;
             if (active) {
-                if (trav_step<COUNT>(sc, rp, s, 0, cap, numTri, maxLoop, stL, stT, kTraceThreads)) {
+                if (trav_step<COUNT>(sc, rp, s, anyHit, cap, numTri, maxLoop, stL, stT, kTraceThreads)) {
                     B.hit[pix] = make_float4(s.t, s.ua, s.va, __int_as_float(s.tri));
                     if (COUNT) {
                         nodeVisits += s.nodeVisits; leafTests += s.leafTests;
@@ -273,7 +285,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, 
 // (same sampler values as k_pt_primary) and the segment-0 outputs (depth, motion vector, material mask) are written.
 // Otherwise: one thread per entry of the shade queue (grid-stride over the device-side counts).
 // ---------------------------------------------------------------------------------------------------------------------
-VD void logic_body(const PathTraceParams& P, const WfBuffers& B, uint32_t pix, bool first, bool& emit) {
+VD void logic_body(const PathTraceParams& P, const WfBuffers& B, uint32_t pix, bool first, bool& emit, uint32_t& entry) {
     const int iy = (int)(pix / (uint32_t)P.width), ix = (int)(pix - (uint32_t)iy * (uint32_t)P.width);
     RayState r; int seg = 0; unsigned short mask = 0; Float2 sampleUv{0.0f, 0.0f};
     if (first) init_path(P, r, sampleUv, ix, iy);
@@ -296,8 +308,10 @@ VD void logic_body(const PathTraceParams& P, const WfBuffers& B, uint32_t pix, b
         P.motion[pix] = __float22half2_rn(make_float2(motion.x, motion.y));
     }
     emit = advance_path(P, r, seg, ix, iy, P.normal);
-    if (emit) { r.isHitProcessed = false; save_state(B, pix, r, seg, mask); }
-    else finalize_path(P, r, mask, ix, iy);
+    if (emit) {
+        r.isHitProcessed = false; save_state(B, pix, r, seg, mask);
+        entry = pix | ((P.anyHitRays && (r.isShadowRay || seg == 4)) ? kAnyHitBit : 0u);
+    } else finalize_path(P, r, mask, ix, iy);
 }
 
 __global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTraceParams P, const WfBuffers B, uint32_t* countOut) {
@@ -308,8 +322,9 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTrac
     const int ix = (tile % tilesX) * 8 + (lane & 7), jc = (tile / tilesX) * 4 + (lane >> 3), jy = chunk_row(P, jc), iy = frame_row(P, jy);
     bool emit = false;
     const uint32_t pix = (uint32_t)((size_t)iy * P.width + ix);
-    if (ix < P.width && jc < P.chunkRows && jy < P.localRows) logic_body(P, B, pix, true, emit);
-    queue_append(emit, pix, B.rayQueue, countOut, lane);
+    uint32_t entry = pix;
+    if (ix < P.width && jc < P.chunkRows && jy < P.localRows) logic_body(P, B, pix, true, emit, entry);
+    queue_append(emit, entry, B.rayQueue, countOut, lane);
 }
 
 __global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParams P, const WfBuffers B, const uint32_t* __restrict__ hitCount,
@@ -325,9 +340,9 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParam
         uint32_t slot;
         if (q0 < padHit) { valid = q < nHit; slot = q; }
         else { valid = q < total; slot = B.capacity - 1u - (q - padHit); }
-        uint32_t pix = 0;
-        if (valid) { pix = B.shadeQueue[slot]; logic_body(P, B, pix, false, emit); }
-        queue_append(emit, pix, B.rayQueue, countOut, lane);
+        uint32_t pix = 0, entry = 0;
+        if (valid) { pix = B.shadeQueue[slot]; logic_body(P, B, pix, false, emit, entry); }
+        queue_append(emit, entry, B.rayQueue, countOut, lane);
     }
 }
 

@@ -126,6 +126,35 @@ def test_pathtrace_mixed_materials_textures_motion(pkg, orc, scene):
         assert np.abs(f.motion - 0.5).max() > 1e-3                                      # the camera did move
 
 
+def test_any_hit_rays_leave_every_output_unchanged(pkg, orc, scene):
+    """Option any_hit_rays (shadow rays and last-segment rays stop at the first accepted triangle): all G-buffers and the ray count
+    are BIT-IDENTICAL to the closest-hit search of the reference (any_hit_rays = 0); only the visit counters may shrink.
+    Mixed materials (incl. the EMISSIVE and glass types) so that specular chains and the last segment are exercised."""
+    pos, nrm, idx, ob = scene
+    mats = orc.default_materials()
+    midx = np.array([3, 4, 5, 1, 7, 0, 2], np.int32)[np.arange(idx.shape[0]) % 7]
+    tex = [noise_texture(1), noise_texture(2, normal_map=True)]
+    bufs = (pkg.BUF_RENDER_COLOR, pkg.BUF_NORMAL, pkg.BUF_ALBEDO, pkg.BUF_DEPTH, pkg.BUF_MOTION_VECTOR)
+    outs = {}
+    for any_hit in (0, 1):
+        with pkg.RayTracer(W, H) as rt:
+            rt.set_option("any_hit_rays", any_hit); rt.set_option("count_visits", 1)
+            rt.set_mesh(pos, idx, nrm); rt.build_bvh()
+            rt.set_materials(mats.view(pkg.MATERIAL_DTYPE), midx)
+            rt.set_texture(0, tex[0]); rt.set_texture(1, tex[1])
+            got = []
+            for frame, campos in ((3, (0, 30, -60)), (4, (-2, 12, -2))):
+                rt.set_camera(pkg.scenes.make_camera(campos, 0.3 * frame, -0.3, W, H), reset_history=True)
+                rt.set_frame_number(frame); rt.pathtrace()
+                t = rt.timings()
+                got.append(([rt.read_buffer(b).tobytes() for b in bufs], t["rays_traced"], t["node_visits"]))
+            outs[any_hit] = got
+    for (b0, r0, v0), (b1, r1, v1) in zip(outs[0], outs[1]):
+        assert r0 == r1
+        assert all(x == y for x, y in zip(b0, b1)), "a frame output changed with any_hit_rays"
+        assert v1 <= v0
+
+
 def test_camera_file_roundtrip(pkg, tmp_path):
     cam = pkg.scenes.make_camera((1, 2, 3), 0.3, -0.1, 640, 480)
     with pkg.RayTracer(640, 480) as rt:
