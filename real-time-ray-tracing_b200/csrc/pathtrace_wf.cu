@@ -20,10 +20,25 @@
 
 namespace rtrt {
 
-constexpr int kTraceThreads = 128;
-constexpr int kLogicThreads = 128;
+#ifndef RTRT_TRACE_THREADS
+#define RTRT_TRACE_THREADS 128
+#endif
+#ifndef RTRT_LOGIC_THREADS
+#define RTRT_LOGIC_THREADS 128
+#endif
+constexpr int kTraceThreads = RTRT_TRACE_THREADS;
+constexpr int kLogicThreads = RTRT_LOGIC_THREADS;
+#ifndef RTRT_PRIMARY_MINB
+#define RTRT_PRIMARY_MINB 1
+#endif
+#ifndef RTRT_TRACE_MINB
+#define RTRT_TRACE_MINB 6        // measured: 2.80 -> 2.73 ms per path-traced 1080p frame against no bound (4, 5: no change; 8: 2.75)
+#endif
+#ifndef RTRT_LOGIC_MINB
+#define RTRT_LOGIC_MINB 5      // <= 102 registers, 5 CTAs/SM: measured 2.83 -> 2.71 ms per path-traced 1080p frame against ptxas' own choice (128 registers, 4 CTAs/SM); 6 is the same, 3 no change
+#endif
 #ifndef RTRT_REFILL_IDLE
-#define RTRT_REFILL_IDLE 8
+#define RTRT_REFILL_IDLE 12
 #endif
 constexpr int kRefillIdle = RTRT_REFILL_IDLE;   // refill a warp once this many of its lanes are idle
 
@@ -165,7 +180,7 @@ VD void init_path(const PathTraceParams& P, RayState& r, Float2& sampleUv, int i
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams P, const WfBuffers B) {
+__global__ void __launch_bounds__(kPtThreads, RTRT_PRIMARY_MINB) k_pt_primary(const PathTraceParams P, const WfBuffers B) {
     __shared__ uint32_t sLink[16 * kPtThreads];
     __shared__ float sT[16 * kPtThreads];
     const int tid = threadIdx.y * kPtBlockX + threadIdx.x, lane = tid & 31;
@@ -192,7 +207,7 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_primary(const PathTraceParams
 // k_pt_trace: persistent wavefront traversal with lane refill.  Queue entries are pixel ids; rays come from st0/st1.
 // ---------------------------------------------------------------------------------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(kTraceThreads) k_pt_trace(const SceneView sc, const WfBuffers B, const uint32_t* __restrict__ countPtr,
+__global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(const SceneView sc, const WfBuffers B, const uint32_t* __restrict__ countPtr,
                                                             uint32_t* fetchPtr, uint32_t* hitCount, uint32_t* missCount, unsigned long long* visitCounters) {
     const uint32_t* __restrict__ queue = B.rayQueue;
     __shared__ uint32_t sLink[16 * kTraceThreads];
@@ -314,7 +329,7 @@ VD void logic_body(const PathTraceParams& P, const WfBuffers& B, uint32_t pix, b
     } else finalize_path(P, r, mask, ix, iy);
 }
 
-__global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTraceParams P, const WfBuffers B, uint32_t* countOut) {
+__global__ void __launch_bounds__(kLogicThreads, RTRT_LOGIC_MINB) k_pt_logic_first(const PathTraceParams P, const WfBuffers B, uint32_t* countOut) {
     // 8x4-pixel warps like the primary kernel (sky / terrain coherence)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tilesX = (P.width + 7) / 8;
@@ -327,7 +342,7 @@ __global__ void __launch_bounds__(kLogicThreads) k_pt_logic_first(const PathTrac
     queue_append(emit, entry, B.rayQueue, countOut, lane);
 }
 
-__global__ void __launch_bounds__(kLogicThreads) k_pt_logic(const PathTraceParams P, const WfBuffers B, const uint32_t* __restrict__ hitCount,
+__global__ void __launch_bounds__(kLogicThreads, RTRT_LOGIC_MINB) k_pt_logic(const PathTraceParams P, const WfBuffers B, const uint32_t* __restrict__ hitCount,
                                                             const uint32_t* __restrict__ missCount, uint32_t* countOut) {
     const uint32_t nHit = *hitCount, nMiss = *missCount;
     const uint32_t padHit = (nHit + 31u) & ~31u, total = padHit + nMiss;
