@@ -204,6 +204,8 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
  *   "global_sort"         0/1  : rtrt_build_bvh first sorts the triangles by the 60-bit Morton code of their centroid in the
  *                                mesh bounding box (the offline step of tool/meshProcessor.cpp:146-200, on the device, per
  *                                call); triangle ids reported by the library are then positions in that order
+ *   "morton_bits"         60   : code width of the global pre-sort: 60 = the reference tool's (20 bits per axis, two interleaved 30-bit
+ *                                halves, tool/meshProcessor.cpp:52-62), 63 = 21 bits per axis in one interleave
  *   "wavefront"           1/0  : path-trace driver: wavefront ray queues with persistent traversal (default) or one megakernel
  *   "count_visits"        0/1  : rtrt_pathtrace also counts node visits / leaf tests (rtrt_timings)         */
 

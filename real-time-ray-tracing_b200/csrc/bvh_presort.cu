@@ -4,7 +4,8 @@
 // (tool/meshProcessor.cpp:35-62,146-200: 60-bit Morton code of the centroid = 20 bits per axis in the mesh bounding box,
 // std::sort, triangles rewritten in that order).  For dynamic or unsorted geometry (BASELINE config 3) that step has to
 // run per frame on the GPU: option "global_sort" = 1 makes rtrt_build_bvh run
-//     k_ps_bounds (vertex bounding box) -> k_ps_codes (60-bit code per triangle) -> device radix sort of (code, id),
+//     k_ps_bounds (vertex bounding box) -> k_ps_codes (60-bit code per triangle; 63-bit = 21 bits per axis with option
+//     "morton_bits" = 63) -> device radix sort of (code, id),
 //     8 x 8-bit passes (radix_sort.cuh) -> k_ps_gather (index buffer in sorted order)
 // in front of the batch build.  Sorted position -> original triangle id is observable as RTRT_BUF_TRI_PERMUTATION.
 // Semantics = stable sort of the ids by code (equal codes keep input order).
@@ -46,8 +47,28 @@ __device__ __forceinline__ uint32_t quant20(float c, float lo, float hi) {
     return __float2uint_rz(u);
 }
 
+// 63-bit mode (option "morton_bits" = 63; generalisation rule B7): 21 bits per axis, one interleave x | y << 1 | z << 2.
+// Same quantisation rule as the tool's with 2^21 - 1 in place of 2^20 - 1 (float32: 24 mantissa bits cover 21).
+__device__ __forceinline__ uint32_t quant21(float c, float lo, float hi) {
+    float ext = hi - lo;
+    if (!(ext > 0.0f)) ext = 1.0f;
+    const float scale = 2097151.0f;
+    float u = (c - lo) / ext * scale;
+    u = fminf(fmaxf(u, 0.0f), scale);
+    return __float2uint_rz(u);
+}
+__device__ __forceinline__ unsigned long long expand21(uint32_t v) {        // 21 bits -> every third bit of 63
+    unsigned long long x = v & 0x1FFFFFull;
+    x = (x | (x << 32)) & 0x001F00000000FFFFull;
+    x = (x | (x << 16)) & 0x001F0000FF0000FFull;
+    x = (x | (x << 8)) & 0x100F00F00F00F00Full;
+    x = (x | (x << 4)) & 0x10C30C30C30C30C3ull;
+    x = (x | (x << 2)) & 0x1249249249249249ull;
+    return x;
+}
+
 __global__ void __launch_bounds__(256) k_ps_codes(const float* __restrict__ pos, const uint32_t* __restrict__ idx, uint32_t N, const uint32_t* __restrict__ ord,
-                                                  unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+                                                  unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals, int bits63) {
     const uint32_t t = blockIdx.x * 256 + threadIdx.x;
     if (t >= N) return;
     const uint32_t i0 = __ldg(idx + 3 * (size_t)t), i1 = __ldg(idx + 3 * (size_t)t + 1), i2 = __ldg(idx + 3 * (size_t)t + 2);
@@ -55,7 +76,12 @@ __global__ void __launch_bounds__(256) k_ps_codes(const float* __restrict__ pos,
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
         const float c = ((__ldg(pos + 3 * (size_t)i0 + a) + __ldg(pos + 3 * (size_t)i1 + a)) + __ldg(pos + 3 * (size_t)i2 + a)) / 3.0f;
-        q[a] = quant20(c, ord2f_ps(ord[a]), ord2f_ps(ord[3 + a]));
+        q[a] = bits63 ? quant21(c, ord2f_ps(ord[a]), ord2f_ps(ord[3 + a])) : quant20(c, ord2f_ps(ord[a]), ord2f_ps(ord[3 + a]));
+    }
+    if (bits63) {
+        keys[t] = expand21(q[0]) | (expand21(q[1]) << 1) | (expand21(q[2]) << 2);
+        vals[t] = t;
+        return;
     }
     const unsigned long long lo30 = expand10(q[0] & 1023u) | (expand10(q[1] & 1023u) << 1) | (expand10(q[2] & 1023u) << 2);
     const unsigned long long hi30 = expand10(q[0] >> 10) | (expand10(q[1] >> 10) << 1) | (expand10(q[2] >> 10) << 2);
@@ -97,7 +123,7 @@ int launch_presort(Context& c) {
     if (!smCount) { cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c.device); if (smCount <= 0) smCount = 148; }
     k_ps_init<<<1, 32, 0, c.stream>>>(ord);
     k_ps_bounds<<<smCount * 8, 256, 0, c.stream>>>(c.dPos, c.numVerts, ord);
-    k_ps_codes<<<(N + 255) / 256, 256, 0, c.stream>>>(c.dPos, c.dIdx, N, ord, keys, c.dTriPerm);
+    k_ps_codes<<<(N + 255) / 256, 256, 0, c.stream>>>(c.dPos, c.dIdx, N, ord, keys, c.dTriPerm, c.mortonBits == 63 ? 1 : 0);
     c.launches += 3;
     const int where = radix_sort_pairs<unsigned long long>(c.stream, keys, c.dTriPerm, keysAlt, valsAlt, N, 0, 64, tmp, c.launches);
     if (where < 0) return c.fail(RTRT_ERR_CUDA, "global Morton sort launch failed");

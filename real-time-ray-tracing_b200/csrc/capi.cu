@@ -255,6 +255,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 32) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..32"); c.stackSize = (int)value; return RTRT_OK; }
     if (!strcmp(name, "assume_bvh_valid")) { c.bvhValid = value != 0; return RTRT_OK; }
+    if (!strcmp(name, "morton_bits")) { if (value != 60 && value != 63) return c.fail(RTRT_ERR_ARG, "morton_bits must be 60 or 63"); c.mortonBits = (int)value; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
     if (!strcmp(name, "count_visits")) { c.countVisits = value != 0; return RTRT_OK; }

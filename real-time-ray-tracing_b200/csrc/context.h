@@ -30,6 +30,7 @@ struct Context {
     uint32_t* dTicket = nullptr;
     void* dSortTmp = nullptr; size_t sortTmpBytes = 0;     // scratch of the global (multi-CTA) paths
     bool keepPresortMorton = false;
+    int mortonBits = 60;                                  // option "morton_bits": 60 = the reference tool's code (20 bits / axis), 63 = 21 bits / axis
     bool globalSort = false;                              // option "global_sort": device Morton pre-sort of the triangles before batching
     uint32_t* dIdxSorted = nullptr; uint32_t* dTriPerm = nullptr; void* dPresort = nullptr; size_t presortBytes = 0;
     bool bvhValid = false;

@@ -168,6 +168,9 @@ __global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict
 // range crosses the left / right image border need per-pixel clamping in x and take the per-thread path, as do gated tiles of
 // SpatialFilter7x7 (they only need their own 16x16 pixels) and images with an odd width.
 // -------------------------------------------------------------------------------------------------------------------
+#ifndef RTRT_DN_TMA
+#define RTRT_DN_TMA 1          // 0: every tile through the per-thread path (A/B and debugging)
+#endif
 VD uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 template <int T, int HALO>
 struct TileStage {
@@ -178,7 +181,7 @@ struct TileStage {
     static __device__ __forceinline__ void load(const DnParams& P, const ushort4* __restrict__ in, ushort4* sC, ushort4* sG, unsigned long long* mbar,
                                                 int tid, int bx, int by, int lo, int hi, bool wantTma) {
         const int x0 = bx * 16 - HALO, y0 = by * 16 - HALO, xa = x0 - OX;
-        const bool tma = wantTma && (P.W & 1) == 0 && xa >= 0 && xa + TP <= P.W &&
+        const bool tma = RTRT_DN_TMA && wantTma && (P.W & 1) == 0 && xa >= 0 && xa + TP <= P.W &&
                          ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(P.guide)) & 15) == 0;      // uniform per CTA
         if (tma) {
             if (tid == 0) {

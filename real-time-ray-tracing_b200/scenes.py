@@ -66,6 +66,21 @@ def morton60(cx, cy, cz, lo, hi):
     return (hi30 << np.uint64(30)) | lo30
 
 
+def morton63(cx, cy, cz, lo, hi):
+    """63-bit code of the product's "morton_bits" = 63 mode: 21 bits per axis (same float32 quantisation rule as morton60 with
+    2^21 - 1), bit i of x / y / z at position 3 i / 3 i + 1 / 3 i + 2."""
+    scale = np.float32((1 << 21) - 1)
+    def q(c, l, h):
+        ext = np.float32(h) - np.float32(l)
+        u = (c - np.float32(l)) / (ext if ext > 0 else np.float32(1))
+        return np.clip(u * scale, 0, scale).astype(np.uint64)
+    code = np.zeros(np.asarray(cx).shape, np.uint64)
+    for a, v in enumerate((q(cx, lo[0], hi[0]), q(cy, lo[1], hi[1]), q(cz, lo[2], hi[2]))):
+        for i in range(21):
+            code |= ((v >> np.uint64(i)) & np.uint64(1)) << np.uint64(3 * i + a)
+    return code
+
+
 def terrain(gx, gz, seed=1, order="morton", extent=50.0, amplitude=8.0, shuffle_seed=1234):
     """Returns (pos [V,3] f32, nrm [V,3] f32, idx [N,3] u32) with N = 2*gx*gz."""
     xs = np.linspace(-extent, extent, gx + 1, dtype=np.float32)

@@ -131,19 +131,20 @@ def test_build_beyond_1024_batches(pkg, orc, quads):
         assert_hits_equal(r.traverse(rays), orc.traverse(ob, rays))
 
 
-@pytest.mark.parametrize("quads", [(64, 80), (300, 512)])
-def test_global_morton_presort(pkg, orc, quads):
+@pytest.mark.parametrize("quads,bits", [((64, 80), 60), ((300, 512), 60), ((300, 512), 63)])
+def test_global_morton_presort(pkg, orc, quads, bits):
     """option global_sort: the offline CPU pre-sort of tool/meshProcessor.cpp:146-200 (60-bit Morton of the centroid in the mesh
     bounding box, stable) done on the device in front of the batch build.  Shuffled input + device sort must give exactly the
     arrays of host-sorted input + plain build, and the permutation must be the stable argsort of the codes."""
     pos, nrm, idx = pkg.scenes.terrain(*quads, seed=7, order="shuffle")
     c = (pos[idx[:, 0]] + pos[idx[:, 1]] + pos[idx[:, 2]]) / np.float32(3.0)
-    code = pkg.scenes.morton60(c[:, 0], c[:, 1], c[:, 2], pos.min(axis=0), pos.max(axis=0))
+    code = (pkg.scenes.morton63 if bits == 63 else pkg.scenes.morton60)(c[:, 0], c[:, 1], c[:, 2], pos.min(axis=0), pos.max(axis=0))
     perm = np.argsort(code, kind="stable").astype(np.uint32)
     ob = orc.build_bvh(pos, nrm, idx[perm])
     with pkg.RayTracer(64, 64) as r:
         r.set_option("keep_presort_morton", 1)
         r.set_option("global_sort", 1)
+        r.set_option("morton_bits", bits)                 # 63: 21 bits per axis (generalisation rule B7), 60: the reference tool's code
         r.set_mesh(pos, idx, nrm)
         r.build_bvh()
         np.testing.assert_array_equal(r.read_buffer(pkg.BUF_TRI_PERMUTATION), perm)

