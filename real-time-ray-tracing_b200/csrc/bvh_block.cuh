@@ -45,7 +45,12 @@ __device__ __forceinline__ uint32_t morton30(Float3 c, const AABB& box) {
            (expand10(__float2uint_rz(uz * 1023.0f)) << 2);
 }
 
-// Shared-memory working set of one segment.  `scratch` is time-multiplexed:
+// child links in shared memory: 16 bits (index < 1024, leaf flag in bit 15) <-> the 32-bit form used in registers (kLeafBit)
+__device__ __forceinline__ uint16_t pack_link(uint32_t l) { return (uint16_t)((l & 0x7FFFu) | ((l >> 16) & 0x8000u)); }
+__device__ __forceinline__ uint32_t unpack_link(uint16_t v) { return ((uint32_t)v & 0x7FFFu) | (((uint32_t)v & 0x8000u) << 16); }
+
+// Shared-memory working set of one segment (64 KB: three CTAs and their 1 KB system reservations fit the 196 KB carve-out, which leaves
+// 60 KB of the SM's 256 KB to L1 for the vertex gather instead of 28 KB).  `scratch` is time-multiplexed:
 //   gather phase : item centres (12 KB) ; sort phase : digit histograms (16 KB) ; refit : node boxes (24 KB)
 struct SegSmem {
     AABB leafBox[kSeg];                        // 24 KB  per-item boxes, indexed by original (pre-sort) id
@@ -56,12 +61,11 @@ struct SegSmem {
     } scratch;                                 // 24 KB
     uint32_t keys[2][kSeg];                    //  8 KB  ping-pong; after the sort keys[1] holds the rendezvous slots of the emit
     uint16_t ids[2][kSeg];                     //  4 KB  ping-pong
-    uint32_t childL[kSeg], childR[kSeg];       //  8 KB  link | kLeafBit
-    uint32_t digitBase[256];                   //  1 KB
-    uint32_t warpSum[8];
-    float    red[6][32];                       //  block AABB reduction
-    AABB     segBox;
-    uint32_t misc[4];
+    // 4 KB, time-multiplexed: block reduction / sort bookkeeping (dead before the emit) | child links of the emit (11 bits + leaf flag)
+    union {
+        struct { uint16_t childL[kSeg], childR[kSeg]; } link;
+        struct { uint16_t digitBase[256]; uint32_t warpSum[8]; float red[6][16]; AABB segBox; uint32_t misc[4]; } aux;
+    } u;
 };
 
 // ---- block-wide AABB reduction (exact; min/max are order independent) ----
@@ -78,16 +82,16 @@ __device__ __forceinline__ AABB block_reduce_aabb(SegSmem& s, AABB v) {
         v.max.z = sel_max(v.max.z, __shfl_xor_sync(0xffffffffu, v.max.z, o));
     }
     if (lane == 0) {
-        s.red[0][warp] = v.min.x; s.red[1][warp] = v.min.y; s.red[2][warp] = v.min.z;
-        s.red[3][warp] = v.max.x; s.red[4][warp] = v.max.y; s.red[5][warp] = v.max.z;
+        s.u.aux.red[0][warp] = v.min.x; s.u.aux.red[1][warp] = v.min.y; s.u.aux.red[2][warp] = v.min.z;
+        s.u.aux.red[3][warp] = v.max.x; s.u.aux.red[4][warp] = v.max.y; s.u.aux.red[5][warp] = v.max.z;
     }
     __syncthreads();
     if (warp == 0) {
         constexpr int NW = NT / 32;
         AABB w = aabb_empty();
         if (lane < NW) {
-            w.min = Float3{s.red[0][lane], s.red[1][lane], s.red[2][lane]};
-            w.max = Float3{s.red[3][lane], s.red[4][lane], s.red[5][lane]};
+            w.min = Float3{s.u.aux.red[0][lane], s.u.aux.red[1][lane], s.u.aux.red[2][lane]};
+            w.max = Float3{s.u.aux.red[3][lane], s.u.aux.red[4][lane], s.u.aux.red[5][lane]};
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -98,10 +102,10 @@ __device__ __forceinline__ AABB block_reduce_aabb(SegSmem& s, AABB v) {
             w.max.y = sel_max(w.max.y, __shfl_xor_sync(0xffffffffu, w.max.y, o));
             w.max.z = sel_max(w.max.z, __shfl_xor_sync(0xffffffffu, w.max.z, o));
         }
-        if (lane == 0) s.segBox = w;
+        if (lane == 0) s.u.aux.segBox = w;
     }
     __syncthreads();
-    return s.segBox;
+    return s.u.aux.segBox;
 }
 
 // ---- stable LSD radix sort of the 1024 (key,id) pairs in s.keys[0]/s.ids[0]; 4 passes x 8 bits ----
@@ -110,7 +114,7 @@ __device__ __forceinline__ AABB block_reduce_aabb(SegSmem& s, AABB v) {
 // column scan (one thread per digit) + one 256-wide block scan.  Result lands back in keys[0]/ids[0].
 template <int NT>
 __device__ __forceinline__ void block_sort_1024(SegSmem& s) {
-    static_assert(NT >= 256 && NT % 32 == 0 && kSeg % NT == 0, "block size");
+    static_assert(NT >= 256 && NT <= 512 && NT % 32 == 0 && kSeg % NT == 0, "block size");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
     constexpr int CHUNKS_PER_WARP = 32 / NW;            // 32 chunks of 32 keys
@@ -150,20 +154,20 @@ __device__ __forceinline__ void block_sort_1024(SegSmem& s) {
             const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += n;
         }
-        if (tid < 256 && lane == 31) s.warpSum[warp] = incl;
+        if (tid < 256 && lane == 31) s.u.aux.warpSum[warp] = incl;
         __syncthreads();
         if (tid < 256) {
             uint32_t base = 0;
 #pragma unroll
-            for (int w = 0; w < 8; ++w) if (w < warp) base += s.warpSum[w];
-            s.digitBase[tid] = base + incl - total;
+            for (int w = 0; w < 8; ++w) if (w < warp) base += s.u.aux.warpSum[w];
+            s.u.aux.digitBase[tid] = (uint16_t)(base + incl - total);
         }
         __syncthreads();
 #pragma unroll
         for (int r = 0; r < CHUNKS_PER_WARP; ++r) {
             const int c = warp * CHUNKS_PER_WARP + r;
             const uint32_t d = (key[r] >> shift) & 255u;
-            const uint32_t pos = s.digitBase[d] + s.scratch.hist[c][d] + rank[r];
+            const uint32_t pos = (uint32_t)s.u.aux.digitBase[d] + s.scratch.hist[c][d] + rank[r];
             kdst[pos] = key[r];
             idst[pos] = isrc[c * 32 + lane];
         }
@@ -264,7 +268,7 @@ __device__ __forceinline__ void block_emit_refit(SegSmem& s, int n) {
             // Karras numbering: a right child carries the START of its range, a left child the END, the root (dF = -1 > dL = -2) is 0
             const bool root = f == 0 && l == n - 1;
             const int idx = (dF > dL) ? f : l;
-            s.childL[idx] = L; s.childR[idx] = R;
+            s.u.link.childL[idx] = pack_link(L); s.u.link.childR[idx] = pack_link(R);
             mine = bl; aabb_grow(mine, br);
             if (root) break;
             sts_box(&s.scratch.nodeBox[idx], mine);
@@ -280,7 +284,7 @@ __device__ __forceinline__ void block_write_nodes(const SegSmem& s, int n, BVHNo
     float4* o4 = reinterpret_cast<float4*>(out);
     for (int e = threadIdx.x; e < (n - 1) * 4; e += NT) {
         const int i = e >> 2, q = e & 3;
-        const uint32_t L = s.childL[i], R = s.childR[i];
+        const uint32_t L = unpack_link(s.u.link.childL[i]), R = unpack_link(s.u.link.childR[i]);
         float4 v;
         if (q == 3) {
             v.x = __uint_as_float(L & ~kLeafBit); v.y = __uint_as_float(R & ~kLeafBit);

@@ -11,12 +11,13 @@
 // without 3+-fold duplicate keys inside a segment (see bvh_block.cuh: seg_delta).
 #include "bvh_block.cuh"
 #include "context.h"
+#include <cstdlib>
 
 namespace rtrt {
 
 constexpr int kBuildThreads = 512;
 #ifndef RTRT_BUILD_MINB
-#define RTRT_BUILD_MINB 3          // 3 CTAs/SM: <= 40 registers/thread and <= 75 KB shared memory per CTA
+#define RTRT_BUILD_MINB 3          // 3 CTAs/SM: <= 40 registers/thread, 64 KB shared memory per CTA
 #endif
 
 struct BuildParams {
@@ -186,9 +187,9 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     if (p.fuseTlas) {
         __threadfence();
         __syncthreads();
-        if (tid == 0) s.misc[0] = atomicAdd(p.ticket, 1u);
+        if (tid == 0) s.u.aux.misc[0] = atomicAdd(p.ticket, 1u);
         __syncthreads();
-        if (s.misc[0] == p.numBatches - 1) {
+        if (s.u.aux.misc[0] == p.numBatches - 1) {
             __threadfence();
             tlas_build_block<NT>(s, p);
         }
@@ -220,7 +221,9 @@ int launch_build_bvh(Context& c) {
     if (!attrSet) {
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_tlas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));   // 3 x 73 KB per SM
+        // 3 x (64 KB + 1 KB reserved) = 195 KB: ask for the 196 KB carve-out (85 % of 228 KB rounds up to it), the rest of the SM's 256 KB is L1
+        const char* cv = getenv("RTRT_BUILD_CARVEOUT");
+        RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributePreferredSharedMemoryCarveout, cv ? atoi(cv) : 85));
         attrSet = true;
     }
     RTRT_CUDA(c, cudaMemsetAsync(c.dTicket, 0, sizeof(uint32_t), c.stream));
