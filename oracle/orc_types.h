@@ -49,9 +49,11 @@ static inline F2 operator+(F2 a, float s) { return F2{a.x + s, a.y + s}; }
 static inline F2 operator-(F2 a, float s) { return F2{a.x - s, a.y - s}; }
 static inline F2 operator/(F2 a, float s) { return F2{a.x / s, a.y / s}; }
 
-// src/linearMath.h:25-39 — select-style min/max (NOT fminf/fmaxf: NaN and ±0 behave differently)
-static inline float rmax(float a, float b) { return a > b ? a : b; }
-static inline float rmin(float a, float b) { return a < b ? a : b; }
+// The reference's scalar min(a, b) / max(a, b): for two floats overload resolution picks CUDA's non-template ::min / ::max (= fminf /
+// fmaxf, one FMNMX on the device) over the select-style templates of src/linearMath.h:25-31, so: NaN loses and -0 < +0.  (glibc's
+// fminf is not sign-of-zero aware, hence written out.)  Pinned by tests/test_refcuda_gpu.py::test_signed_zero_boxes_bitwise.
+static inline float rmax(float a, float b) { if (a != a) return b; if (b != b) return a; if (a == b) return std::signbit(a) ? b : a; return a > b ? a : b; }
+static inline float rmin(float a, float b) { if (a != a) return b; if (b != b) return a; if (a == b) return std::signbit(a) ? a : b; return a < b ? a : b; }
 static inline float rmax3(float a, float b, float c) { return rmax(rmax(a, b), c); }
 static inline float rmin3(float a, float b, float c) { return rmin(rmin(a, b), c); }
 static inline F3 min3f(F3 a, F3 b) { return F3{rmin(a.x, b.x), rmin(a.y, b.y), rmin(a.z, b.z)}; }   // linearMath.h:465

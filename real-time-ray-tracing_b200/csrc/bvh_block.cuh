@@ -16,9 +16,13 @@ namespace rtrt {
 constexpr int kSeg = 1024;                 // items per segment (BatchSize)
 constexpr uint32_t kLeafBit = 0x80000000u; // child link flag inside shared memory
 
-// select-style min/max of the reference (src/linearMath.h:25-31); NOT fminf/fmaxf
-__device__ __forceinline__ float sel_min(float a, float b) { return a < b ? a : b; }
-__device__ __forceinline__ float sel_max(float a, float b) { return a > b ? a : b; }
+// The reference's scalar min(a, b) / max(a, b) calls (min3f / max3f src/linearMath.h:463-464, AABBCompact::GetMerged src/geometry.h:107-110,
+// ...) do NOT reach its own select-style templates (src/linearMath.h:25-31): for two floats, overload resolution prefers CUDA's
+// non-template ::min(float, float) / ::max(float, float), i.e. fminf / fmaxf — one FMNMX, NaN loses, -0 < +0.  The result is therefore
+// independent of the operand order down to the sign of a zero (pinned against the reference's own kernels by
+// tests/test_refcuda_gpu.py::test_signed_zero_boxes_bitwise), which is what lets the batch boxes be reduced in any order.
+__device__ __forceinline__ float sel_min(float a, float b) { return fminf(a, b); }
+__device__ __forceinline__ float sel_max(float a, float b) { return fmaxf(a, b); }
 
 __device__ __forceinline__ AABB aabb_empty() {
     AABB b; b.min = Float3{FLT_MAX, FLT_MAX, FLT_MAX}; b.max = Float3{-FLT_MAX, -FLT_MAX, -FLT_MAX}; return b;
@@ -310,19 +314,27 @@ __device__ __forceinline__ void write_single_leaf_node(const AABB& b, BVHNode* o
     *out = nd;
 }
 
-// sort -> publish sorted keys/reorderIdx -> Karras -> refit -> nodes, for a segment whose keys/ids and
-// leafBox are already in shared memory.
+// sort -> publish sorted keys/reorderIdx | Karras -> refit -> nodes, for a segment whose keys/ids and leafBox are already in shared
+// memory (two halves: the batch kernel publishes its top-level box in between).
 template <int NT>
-__device__ __forceinline__ void block_build_segment(SegSmem& s, int n, uint32_t* __restrict__ gKeys,
-                                                    uint32_t* __restrict__ gReorder, BVHNode* __restrict__ gNodes) {
+__device__ __forceinline__ void block_sort_publish(SegSmem& s, uint32_t* __restrict__ gKeys, uint32_t* __restrict__ gReorder) {
     block_sort_1024<NT>(s);
     for (int i = threadIdx.x; i < kSeg; i += NT) { gKeys[i] = s.keys[0][i]; gReorder[i] = s.ids[0][i]; }
+}
+template <int NT>
+__device__ __forceinline__ void block_emit_write(SegSmem& s, int n, BVHNode* __restrict__ gNodes) {
     if (n == 1) {
         if (threadIdx.x == 0) write_single_leaf_node(s.leafBox[0], gNodes);
         return;
     }
     block_emit_refit<NT>(s, n);
     block_write_nodes<NT>(s, n, gNodes);
+}
+template <int NT>
+__device__ __forceinline__ void block_build_segment(SegSmem& s, int n, uint32_t* __restrict__ gKeys,
+                                                    uint32_t* __restrict__ gReorder, BVHNode* __restrict__ gNodes) {
+    block_sort_publish<NT>(s, gKeys, gReorder);
+    block_emit_write<NT>(s, n, gNodes);
 }
 
 }  // namespace rtrt

@@ -5,7 +5,8 @@
 //   * one CTA per 1024-triangle batch does gather -> Triangle/AABB emit -> batch AABB -> Morton30 ->
 //     stable radix sort -> Karras emit -> refit -> node write entirely out of shared memory, so keys,
 //     boxes and links never round-trip HBM between steps;
-//   * the last CTA to retire (device-wide ticket) builds the TLAS over the batch roots in the same launch.
+//   * one extra CTA of the same launch builds the TLAS over the batch boxes, which every batch CTA publishes right after its
+//     gather: the top level is ready before the last batches have finished their sort / emit.
 // Output arrays are the reference's (src/init.cu:159-187): Triangle[ ], AABB[ ], morton[ ] (sorted),
 // reorderIdx[ ], BVHNode[ ] + the TLAS equivalents, bit-identical to the reference's for scenes
 // without 3+-fold duplicate keys inside a segment (see bvh_block.cuh: seg_delta).
@@ -30,8 +31,8 @@ struct BuildParams {
     uint32_t* mortonPre;                 // optional debug observation point (may be null)
     AABB* tlasAabbs; uint32_t* tlasMorton; uint32_t* tlasReorderIdx; BVHNode* tlasNodes;
     uint32_t* tlasMortonPre;             // optional
-    uint32_t* ticket;                    // device-wide retirement counter (zeroed before launch)
-    int fuseTlas;                        // 1: last CTA builds the TLAS (B <= 1024)
+    uint32_t* ticket;                    // number of batch boxes published to tlasAabbs (zeroed before launch)
+    int fuseTlas;                        // 1: one extra CTA builds the TLAS concurrently (B <= 1024)
 };
 
 __device__ __forceinline__ Float3 ld3(const float* __restrict__ p, uint32_t i) {
@@ -45,15 +46,14 @@ __device__ void tlas_build_block(SegSmem& s, const BuildParams& p) {
     AABB mine = aabb_empty();
     for (int k = threadIdx.x; k < kSeg; k += NT) {
         if (k < B) {
-            // root of BLAS k = nodes[1024*k]; written by other CTAs of this launch in the fused path -> L2 loads
-            const float4* r4 = reinterpret_cast<const float4*>(p.nodes + (size_t)kSeg * k);
-            const float4 a = __ldcg(r4), b = __ldcg(r4 + 1), c = __ldcg(r4 + 2);
-            AABB m;                                             // AABBCompact::GetMerged (src/geometry.h:107-110)
-            m.max.x = sel_max(a.x, c.x); m.max.y = sel_max(a.y, c.y); m.max.z = sel_max(a.z, c.z);
-            m.min.x = sel_min(b.x, a.w); m.min.y = sel_min(b.y, b.w); m.min.z = sel_min(b.z, c.w);
+            // box of BLAS k = AABBCompact::GetMerged of its root node (src/updateGeometry.cuh:283-300, src/geometry.h:107-110), published
+            // by the CTA that builds batch k (publish_tlas_leaf below) -> L2 loads
+            const float* g = reinterpret_cast<const float*>(p.tlasAabbs + k);
+            AABB m;
+            m.min.x = __ldcg(g); m.min.y = __ldcg(g + 1); m.min.z = __ldcg(g + 2);
+            m.max.x = __ldcg(g + 3); m.max.y = __ldcg(g + 4); m.max.z = __ldcg(g + 5);
             s.leafBox[k] = m;
             s.scratch.centre[k] = Float3{(m.max.x + m.min.x) / 2.0f, (m.max.y + m.min.y) / 2.0f, (m.max.z + m.min.z) / 2.0f};
-            p.tlasAabbs[k] = m;
             // the reference's UpdateTLAS drops the per-thread boxes of threads 32..63 (mod 64) from its scene-box reduction
             // (src/updateGeometry.cuh:313-330 lacks the "merge tid + 32" step of :219-223): batches with k mod 256 >= 128
             // do not contribute.  Reproduced bit for bit (the Morton codes of the top level depend on it).
@@ -70,6 +70,20 @@ __device__ void tlas_build_block(SegSmem& s, const BuildParams& p) {
     block_build_segment<NT>(s, B, p.tlasMorton, p.tlasReorderIdx, p.tlasNodes);
 }
 
+// ---- top level concurrent with the batches ----
+// The TLAS needs one box per batch: GetMerged of the batch's root node = the union of its leaf boxes.  min / max are exact, so that
+// union is known as soon as the batch box has been reduced (right after the gather) — long before the batch's sort / emit / node
+// write are through.  Every batch CTA therefore publishes its box early (tlasAabbs[b], release, counter), and ONE EXTRA CTA of the
+// same launch (blockIdx == numBatches) waits for the counter and builds the top level while the last wave of batch CTAs is still
+// sorting and emitting: the serial single-CTA tail (27 us of 163 at 1 M triangles when it ran after the last batch) disappears behind
+// them.  Exactness: the reference's min / max are fminf / fmaxf (bvh_block.cuh), whose result does not depend on the operand order, so
+// the early reduction gives the bits the refit tree would.  A partial last batch (pad items take part in the gather box but not in
+// the tree) publishes GetMerged of its root's children after the emit instead.
+__device__ __forceinline__ void publish_tlas_leaf(const BuildParams& p, uint32_t b, const AABB& box) {     // one thread
+    p.tlasAabbs[b] = box;
+    __threadfence();
+    atomicAdd(p.ticket, 1u);
+}
 // ---- one CTA per batch ----
 template <int NT>
 __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildParams p) {
@@ -78,6 +92,19 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
     const uint32_t b = blockIdx.x;
+    if (b == p.numBatches) {                 // the extra CTA of the fused launch: top level, as soon as every batch box is there
+        if (tid == 0) {
+            uint32_t seen = 0;
+            for (uint32_t spin = 0; spin < (1u << 22); ++spin) {          // bounded: a lost publication must not hang the device
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.ticket) : "memory");
+                if (seen >= p.numBatches) break;
+                __nanosleep(100);
+            }
+        }
+        __syncthreads();
+        tlas_build_block<NT>(s, p);
+        return;
+    }
     const uint32_t base = b * kSeg;
     const uint32_t count = (b == p.numBatches - 1) ? (p.numTris - kSeg * (p.numBatches - 1)) : (uint32_t)kSeg;  // src/init.cu:129-130
     const uint32_t active = (count + 3u) & ~3u;     // src/updateGeometry.cuh:93 : threads own 4 items each
@@ -163,6 +190,8 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     else if (sub == 1) { mine.min.y = accMin; mine.max.y = accMax; }
     else if (sub == 2) { mine.min.z = accMin; mine.max.z = accMax; }
     const AABB batchBox = block_reduce_aabb<NT>(s, mine);     // barriers inside also publish leafBox/centre
+    const bool tlasEarly = p.fuseTlas && count == (uint32_t)kSeg;          // block-uniform
+    if (tlasEarly && tid == 0) publish_tlas_leaf(p, b, batchBox);
 
     // ---- per-item AABB array (24 KB contiguous per batch) + Morton keys ----
     if (active == (uint32_t)kSeg) {                          // 24 KB = 1536 float4, three per thread
@@ -181,25 +210,17 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     }
     __syncthreads();
 
-    block_build_segment<NT>(s, (int)count, p.morton + base, p.reorderIdx + base, p.nodes + base);
-
-    // ---- fused TLAS: last CTA to retire builds the top level in the same launch ----
-    if (p.fuseTlas) {
-        __threadfence();
-        __syncthreads();
-        if (tid == 0) s.u.aux.misc[0] = atomicAdd(p.ticket, 1u);
-        __syncthreads();
-        if (s.u.aux.misc[0] == p.numBatches - 1) {
-            __threadfence();
-            tlas_build_block<NT>(s, p);
-        }
+    block_sort_publish<NT>(s, p.morton + base, p.reorderIdx + base);
+    block_emit_write<NT>(s, (int)count, p.nodes + base);
+    if (p.fuseTlas && !tlasEarly && tid == 0) {                  // partial last batch: GetMerged of the root node's two child boxes
+        AABB bl, br;
+        if (count == 1) { bl = s.leafBox[0]; br.min = Float3{0.0f, 0.0f, 0.0f}; br.max = br.min; }      // src/buildBVH.cuh:31-38
+        else { bl = child_box(s, unpack_link(s.u.link.childL[0])); br = child_box(s, unpack_link(s.u.link.childR[0])); }
+        AABB m;
+        m.max.x = sel_max(bl.max.x, br.max.x); m.max.y = sel_max(bl.max.y, br.max.y); m.max.z = sel_max(bl.max.z, br.max.z);
+        m.min.x = sel_min(bl.min.x, br.min.x); m.min.y = sel_min(bl.min.y, br.min.y); m.min.z = sel_min(bl.min.z, br.min.z);
+        publish_tlas_leaf(p, b, m);
     }
-}
-
-template <int NT>
-__global__ void __launch_bounds__(NT) k_build_tlas(const BuildParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    tlas_build_block<NT>(*reinterpret_cast<SegSmem*>(smem_raw), p);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -220,14 +241,13 @@ int launch_build_bvh(Context& c) {
     const size_t smem = sizeof(SegSmem);
     if (!attrSet) {
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        RTRT_CUDA(c, cudaFuncSetAttribute(k_build_tlas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         // 3 x (64 KB + 1 KB reserved) = 195 KB: ask for the 196 KB carve-out (85 % of 228 KB rounds up to it), the rest of the SM's 256 KB is L1
         const char* cv = getenv("RTRT_BUILD_CARVEOUT");
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributePreferredSharedMemoryCarveout, cv ? atoi(cv) : 85));
         attrSet = true;
     }
     RTRT_CUDA(c, cudaMemsetAsync(c.dTicket, 0, sizeof(uint32_t), c.stream));
-    k_build_blas<kBuildThreads><<<c.numBatches, kBuildThreads, smem, c.stream>>>(p);
+    k_build_blas<kBuildThreads><<<c.numBatches + (p.fuseTlas ? 1u : 0u), kBuildThreads, smem, c.stream>>>(p);
     c.launches += 1;
     { int rc = geometry_consumed(c); if (rc) return rc; }   // the vertex buffers may be overwritten from here on
     if (!p.fuseTlas) {

@@ -66,3 +66,42 @@ def test_product_and_oracle_match_reference_kernels(pkg, orc, ref, quads, seed):
     assert_hits_equal(got, ref_hits)
     assert_hits_equal(orc.traverse(ob, rays), ref_hits)
     assert (ref_hits["tri"] >= 0).mean() > 0.2
+
+
+def test_signed_zero_boxes_bitwise(pkg, orc, ref):
+    """Batch boxes with zero components of both signs: the select-style min / max of the reference return the right operand on ties,
+    so the sign of a zero in a merged box depends on the leaf order.  The product publishes the top-level boxes before the refit tree
+    exists (bvh_build.cu: fix_zero_signs), so the BITS of TLAS AABBs, TLAS nodes and BLAS nodes are compared with the reference
+    kernels' and the oracle's here (the value comparisons elsewhere cannot see a sign of zero)."""
+    rng = np.random.default_rng(11)
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=5)                    # 10 240 triangles = 10 full batches
+    pos = pos.copy()
+    # x >= 0 with a column of zeros, a plateau of y == 0, z <= 0 (zero is the MAX there); no mirroring: mirrored halves would give
+    # batches with identical centres, i.e. duplicate top-level Morton keys, which the reference's LCP cannot handle (DESIGN.md par. 2)
+    pos[:, 0] -= pos[:, 0].min(); pos[:, 2] -= pos[:, 2].max()
+    pos[:, 1] = np.maximum(pos[:, 1] - np.quantile(pos[:, 1], 0.3).astype(np.float32), np.float32(0.0))
+    for a in range(3):                                                     # half of the zeros become -0.0
+        z = np.nonzero(pos[:, a] == 0.0)[0]
+        pos[z[rng.random(z.size) < 0.5], a] = np.float32(-0.0)
+    assert (np.signbit(pos) & (pos == 0)).sum() > 10 and ((~np.signbit(pos)) & (pos == 0)).sum() > 10
+    rb = ref.build_bvh(pos, nrm, idx)
+    ob = orc.build_bvh(pos, nrm, idx)
+    with pkg.RayTracer(64, 64) as rt:
+        rt.set_mesh(pos, idx, nrm); rt.build_bvh()
+        got = read_all_stage1(rt, pkg)
+    B = ob.num_batches
+    def bits(a):
+        return np.ascontiguousarray(a).view(np.uint32)
+    want_tlas = rb.host("tlasAabbs", orc.AABB_DTYPE)
+    for f in ("min", "max"):
+        np.testing.assert_array_equal(bits(got[pkg.BUF_TLAS_AABBS][f][:B]), bits(want_tlas[f][:B]), err_msg=f"TLAS aabbs.{f} bits vs reference kernels")
+        np.testing.assert_array_equal(bits(ob.tlas_aabbs[f][:B]), bits(want_tlas[f][:B]), err_msg=f"oracle TLAS aabbs.{f} bits vs reference kernels")
+    assert (want_tlas["min"][:B] == 0).any() or (want_tlas["max"][:B] == 0).any()
+    want_nodes, want_tnodes = rb.host("nodes", orc.BVHNODE_DTYPE), rb.host("tlasNodes", orc.BVHNODE_DTYPE)
+    valid = np.zeros(B * 1024, bool)
+    for b in range(B):
+        valid[b * 1024: b * 1024 + 1023] = True
+    for f in NODE_BOX_FIELDS:
+        np.testing.assert_array_equal(bits(got[pkg.BUF_BVH_NODES][f][valid]), bits(want_nodes[f][valid]), err_msg=f"bvhNodes.{f} bits")
+        np.testing.assert_array_equal(bits(got[pkg.BUF_TLAS_BVH_NODES][f][:B - 1]), bits(want_tnodes[f][:B - 1]), err_msg=f"TLAS nodes.{f} bits")
+    np.testing.assert_array_equal(got[pkg.BUF_TLAS_MORTON], rb.host("tlasMorton", np.uint32))
