@@ -113,9 +113,7 @@ __device__ __forceinline__ bool ray_box(const RayPrep& r, float mnx, float mny, 
     const float tfx = ((r.negX ? mnx : mxx) - r.orgFar.x) * r.rdirFar.x;
     const float tfy = ((r.negY ? mny : mxy) - r.orgFar.y) * r.rdirFar.y;
     const float tfz = ((r.negZ ? mnz : mxz) - r.orgFar.z) * r.rdirFar.z;
-    // fmaxf/fminf (one FMNMX each) instead of the reference's select-style max/min: the operands are never NaN here
-    // (safe_divide keeps the reciprocals finite) and the two forms differ only in the sign of a zero result, which
-    // no later comparison can see (tNear is re-clamped with max(.,0), everything else is </<=/>).
+    // fmaxf / fminf like the reference: its scalar max() / min() calls resolve to CUDA's overloads (bvh_block.cuh), one FMNMX each
     const float tn = fmaxf(fmaxf(tnx, tny), tnz);
     const float tf = fminf(fminf(tfx, tfy), tfz);
     const bool hit = tn <= tf && (tf > 0.0f);

@@ -69,10 +69,11 @@ def test_product_and_oracle_match_reference_kernels(pkg, orc, ref, quads, seed):
 
 
 def test_signed_zero_boxes_bitwise(pkg, orc, ref):
-    """Batch boxes with zero components of both signs: the select-style min / max of the reference return the right operand on ties,
-    so the sign of a zero in a merged box depends on the leaf order.  The product publishes the top-level boxes before the refit tree
-    exists (bvh_build.cu: fix_zero_signs), so the BITS of TLAS AABBs, TLAS nodes and BLAS nodes are compared with the reference
-    kernels' and the oracle's here (the value comparisons elsewhere cannot see a sign of zero)."""
+    """Batch boxes with zero components of both signs.  The reference's scalar min() / max() calls resolve to CUDA's fminf / fmaxf
+    (-0 < +0, independent of the operand order) and not to its select-style templates (ties -> right operand, order dependent); the
+    product relies on that to publish the top-level boxes before the refit tree exists (bvh_build.cu).  The BITS of TLAS AABBs, TLAS
+    nodes and BLAS nodes are therefore compared with the reference kernels' and the oracle's here (the value comparisons elsewhere
+    cannot see a sign of zero)."""
     rng = np.random.default_rng(11)
     pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=5)                    # 10 240 triangles = 10 full batches
     pos = pos.copy()
