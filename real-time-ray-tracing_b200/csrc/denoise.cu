@@ -168,6 +168,9 @@ __global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict
 // range crosses the left / right image border need per-pixel clamping in x and take the per-thread path, as do gated tiles of
 // SpatialFilter7x7 (they only need their own 16x16 pixels) and images with an odd width.
 // -------------------------------------------------------------------------------------------------------------------
+#ifndef RTRT_DN_MINB
+#define RTRT_DN_MINB 1
+#endif
 #ifndef RTRT_DN_TMA
 #define RTRT_DN_TMA 1          // 0: every tile through the per-thread path (A/B and debugging)
 #endif
@@ -221,7 +224,7 @@ struct TileStage {
 // Pass A: TemporalFilter (+ tile noise of its output).  16x16 pixels per CTA, 18x18 staged tile.
 // -------------------------------------------------------------------------------------------------------------------
 template <bool FILTER>
-__global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ushort4* __restrict__ in, const ushort4* __restrict__ accum, ushort4* __restrict__ out) {
+__global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_temporal(const DnParams P, const ushort4* __restrict__ in, const ushort4* __restrict__ accum, ushort4* __restrict__ out) {
     constexpr int T = 18;
     using Stage = TileStage<T, 1>;
     constexpr int TP = Stage::TP, OX = Stage::OX;
@@ -293,7 +296,7 @@ __global__ void __launch_bounds__(256) k_dn_temporal(const DnParams P, const ush
 // 16x16 pixels per CTA, 22x22 staged tile.  gate16 = noise level of the INPUT (written by the previous pass).
 // -------------------------------------------------------------------------------------------------------------------
 template <bool FILTER>
-__global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, ushort4* __restrict__ accumOut,
+__global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial7(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, ushort4* __restrict__ accumOut,
                                                      const __half* __restrict__ gate16, int wantNoise) {
     constexpr int T = 22;
     using Stage = TileStage<T, 3>;
@@ -352,7 +355,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial7(const DnParams P, const ush
 // Pass C: SpatialFilterGlobal5x5<S>, S = 3, 6, 12 — dilated taps straight from global memory (L1/L2 resident).
 // -------------------------------------------------------------------------------------------------------------------
 template <int S>
-__global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, const __half* __restrict__ gate16) {
+__global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial5(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, const __half* __restrict__ gate16) {
     const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
     if (x >= P.W || y >= P.H) return;
     const size_t c = (size_t)y * P.W + x;
@@ -399,7 +402,7 @@ __global__ void __launch_bounds__(256) k_dn_spatial5(const DnParams P, const ush
 // 18x18 tile as YCoCg; the history of the previous frame is read from histPrev, this frame's goes to histNext.
 // -------------------------------------------------------------------------------------------------------------------
 template <bool TF2>
-__global__ void __launch_bounds__(256) k_dn_final(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out,
+__global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_final(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out,
                                                   const ushort4* __restrict__ histPrev, ushort4* __restrict__ histNext, __half* __restrict__ histDepth) {
     constexpr int T = 18;
     __shared__ Float3 sY[T * T];
