@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(256) k_dn_pack_guide(const ushort4* __restrict
 // SpatialFilter7x7 (they only need their own 16x16 pixels) and images with an odd width.
 // -------------------------------------------------------------------------------------------------------------------
 #ifndef RTRT_DN_MINB
-#define RTRT_DN_MINB 1
+#define RTRT_DN_MINB 6          // <= 40 registers, 6 CTAs/SM: 0.360 ms at 1080p (5: 0.362, 8: 0.360; a bound of 1 makes ptxas pick a slower schedule: 0.389)
 #endif
 #ifndef RTRT_DN_TMA
 #define RTRT_DN_TMA 1          // 0: every tile through the per-thread path (A/B and debugging)
