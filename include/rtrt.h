@@ -116,8 +116,12 @@ typedef enum rtrt_buffer {
     RTRT_BUF_COLOR64,            /* half4[w64*h64]: ColorBuffer64, the 1/64-resolution colour the histogram reads                    */
     RTRT_BUF_EXPOSURE,           /* float[4]: d_exposure = EV, adapted luminance, adapted bright luminance, bright luminance          */
     RTRT_BUF_HISTOGRAM,          /* uint32[64]: d_histogram                                                                           */
-    RTRT_BUF_WF_COUNTERS = 100   /* diagnostics: uint32[64] of the wavefront path tracer: [r] rays of bounce round r, [16+r] hits, [24+r] misses,
+    RTRT_BUF_WF_COUNTERS = 100,  /* diagnostics: uint32[64] of the wavefront path tracer: [r] rays of bounce round r, [16+r] hits, [24+r] misses,
                                     with option count_visits: [40+r] max and [48+r] sum of traversal iterations of round r */
+    /* option wide_bvh = 1 (layout documented in csrc/wide_bvh.cuh): */
+    RTRT_BUF_WIDE_NODES = 101,   /* 128 B per node slot: batch b owns slots [512 b, 512 b + 512), the top level follows at 512 B */
+    RTRT_BUF_WIDE_TRIS = 102,    /* 48 B per triangle {v1.xyz, original index; v2.xyz, 0; v3.xyz, 0}, 1024 per batch, leaf-allocation order */
+    RTRT_BUF_WIDE_STAT = 103     /* uint32[4]: error flags, nodes written, top-level nodes, 0 */
 } rtrt_buffer;
 
 /* SkyParams (src/settingParams.h:26-46), same defaults. */
@@ -190,7 +194,19 @@ int rtrt_update_vertices(rtrt_ctx* ctx, const float* pos, const float* nrm_or_nu
 /* ---- options ---- */
 int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
- *   "stack_size"          16   : traversal stack entries (src/traverse.h:28), 1..32
+ *   "wide_bvh"            0/1  : traversal layout.  0 = the reference's arrays (64-byte two-child nodes, one 128-byte triangle per leaf),
+ *                                traversed with the reference's loop, caps and quirks: per-ray (tri, t, u, v) bit-identical to it.
+ *                                1 = rtrt_build_bvh additionally derives an 8-wide BVH with 8-bit quantised child boxes (one 128-byte line
+ *                                per visit) and 48-byte triangles from those arrays (they stay available and bit-exact), and rtrt_traverse /
+ *                                rtrt_pathtrace use it: same watertight triangle test on the same vertex bits, conservative box test, spill
+ *                                stack and no iteration cap -> (tri, t) bit-identical to the reference's search on every ray where the
+ *                                reference neither drops a push on its full stack nor hits its iteration cap nor ties two triangles in t
+ *   "stack_size"          16   : traversal stack entries (src/traverse.h:28): 1..16 for rtrt_pathtrace, 1..64 for rtrt_traverse
+ *                                (> 32: stack in local memory; with a large max_loop this is the uncapped search used as a checker)
+ *   "tlas_spin_limit"     4M   : polls before the top-level CTA of the fused build gives up waiting for the batch boxes; a time-out is
+ *                                reported as RTRT_ERR_CUDA by the next rtrt_sync / rtrt_get_timings (0 forces it: test knob)
+ *   "keep_all_triangles"  0/1  : 1 = the up-to-3 pad items of a partial last batch sort behind every real triangle, so no real triangle is
+ *                                pushed out of the hierarchy (0 = the reference's behaviour, src/init.cu:103-115)
  *   "max_loop"            1024 : traversal iteration cap  (src/traverse.h:132)
  *   "pt_chunks"           1    : rtrt_pathtrace splits the frame into this many independent sets of 8-row strips and runs their
  *                                wavefront pipelines on side streams, so that the latency tail of one set's bounce rounds overlaps

@@ -7,7 +7,9 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("RTRT_LIB") or os.path.join(HERE, "librtrt.so")     # RTRT_LIB: A/B builds of the same library (experiments)
+LIB_PATH = os.path.join(HERE, "librtrt.so")
+if os.environ.get("RTRT_EXPERIMENT") == "1" and os.environ.get("RTRT_LIB"):   # A/B builds of the same library, experiments only
+    LIB_PATH = os.environ["RTRT_LIB"]
 
 RTRT_OK = 0
 STATUS_NAMES = {0: "RTRT_OK", -1: "RTRT_ERR_ARG", -2: "RTRT_ERR_CUDA", -3: "RTRT_ERR_CAPACITY",
@@ -20,6 +22,7 @@ BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCU
     BUF_HISTORY_DEPTH, BUF_NOISE_LEVEL, BUF_NOISE_LEVEL_16, BUF_SKY, BUF_SKY_CDF, BUF_SUN, BUF_SUN_CDF, BUF_ACCUM_RADIANCE = range(32, 47)
 BUF_OUTPUT_RGBA8, BUF_COLOR64, BUF_EXPOSURE, BUF_HISTOGRAM = range(47, 51)
 BUF_WF_COUNTERS = 100
+BUF_WIDE_NODES, BUF_WIDE_TRIS, BUF_WIDE_STAT = 101, 102, 103
 
 
 class Config(C.Structure):

@@ -41,7 +41,8 @@ for _b, _dt in ((L.BUF_RENDER_COLOR, COLOR_DTYPE), (L.BUF_NORMAL, np.dtype(("<f2
                 (L.BUF_SKY, np.dtype(("<f4", 4))), (L.BUF_SKY_CDF, np.dtype("<f4")), (L.BUF_SUN, np.dtype(("<f4", 4))),
                 (L.BUF_SUN_CDF, np.dtype("<f4")), (L.BUF_ACCUM_RADIANCE, np.dtype(("<f4", 4))), (L.BUF_WF_COUNTERS, np.dtype("<u4")),
                 (L.BUF_OUTPUT_RGBA8, np.dtype(("u1", 4))), (L.BUF_COLOR64, np.dtype(("<f2", 4))), (L.BUF_EXPOSURE, np.dtype("<f4")),
-                (L.BUF_HISTOGRAM, np.dtype("<u4"))):
+                (L.BUF_HISTOGRAM, np.dtype("<u4")), (L.BUF_WIDE_NODES, np.dtype(("u1", 128))), (L.BUF_WIDE_TRIS, np.dtype(("<f4", 12))),
+                (L.BUF_WIDE_STAT, np.dtype("<u4"))):
     BUFFER_DTYPES[_b] = _dt
 MAT_LAMBERTIAN_DIFFUSE, MAT_PERFECT_REFLECTION, MAT_GLASS, MAT_MICROFACET_REFLECTION, MAT_EMISSIVE, MAT_SKY = range(6)
 

@@ -31,8 +31,11 @@ struct BuildParams {
     uint32_t* mortonPre;                 // optional debug observation point (may be null)
     AABB* tlasAabbs; uint32_t* tlasMorton; uint32_t* tlasReorderIdx; BVHNode* tlasNodes;
     uint32_t* tlasMortonPre;             // optional
-    uint32_t* ticket;                    // number of batch boxes published to tlasAabbs (zeroed before launch)
+    uint32_t* ticket;                    // [0] number of batch boxes published to tlasAabbs (zeroed before launch)
+                                         // [1] sticky error word: the top-level CTA gave up waiting (reported by rtrt_sync / rtrt_get_timings)
     int fuseTlas;                        // 1: one extra CTA builds the TLAS concurrently (B <= 1024)
+    uint32_t spinLimit;                  // polls of the ticket before the top-level CTA gives up (option tlas_spin_limit)
+    int keepAllTris;                     // option keep_all_triangles: pad items of the last batch sort behind every real triangle
 };
 
 __device__ __forceinline__ Float3 ld3(const float* __restrict__ p, uint32_t i) {
@@ -93,15 +96,22 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
     constexpr int NW = NT / 32;
     const uint32_t b = blockIdx.x;
     if (b == p.numBatches) {                 // the extra CTA of the fused launch: top level, as soon as every batch box is there
+        // Bounded wait: a lost publication must not hang the device.  CUDA does not promise that the batch CTAs are all resident
+        // before this one, so a time-out is an ERROR, not a reason to build from stale boxes: the sticky word ticket[1] is set, the top
+        // level is left untouched and the host reports RTRT_ERR_CUDA at its next synchronisation point (capi.cu: check_build_error).
+        __shared__ uint32_t sSeen;
         if (tid == 0) {
             uint32_t seen = 0;
-            for (uint32_t spin = 0; spin < (1u << 22); ++spin) {          // bounded: a lost publication must not hang the device
+            for (uint32_t spin = 0; spin < p.spinLimit; ++spin) {
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.ticket) : "memory");
                 if (seen >= p.numBatches) break;
                 __nanosleep(100);
             }
+            if (seen < p.numBatches) atomicExch(p.ticket + 1, 1u);
+            sSeen = seen;
         }
         __syncthreads();
+        if (sSeen < p.numBatches) return;
         tlas_build_block<NT>(s, p);
         return;
     }
@@ -204,7 +214,11 @@ __global__ void __launch_bounds__(NT, RTRT_BUILD_MINB) k_build_blas(const BuildP
         for (uint32_t e = tid; e < active * 6u; e += NT) ga[e] = lb[e];
     }
     for (int i = tid; i < kSeg; i += NT) {
-        const uint32_t key = ((uint32_t)i < active) ? morton30(s.scratch.centre[i], batchBox) : 0xFFFFFFFFu;  // src/kernel.cu:279
+        // The reference gives the (up to 3) pad items of a partial last batch real keys while the hierarchy only takes the first `count`
+        // sorted entries: pad items (degenerate, at vertex 0) can push real triangles out of the tree (src/init.cu:103-115,
+        // src/updateGeometry.cuh:93).  Reproduced by default; keep_all_triangles sorts the pad items last instead.
+        const uint32_t keyed = p.keepAllTris ? count : active;
+        const uint32_t key = ((uint32_t)i < keyed) ? morton30(s.scratch.centre[i], batchBox) : 0xFFFFFFFFu;  // src/kernel.cu:279
         s.keys[0][i] = key; s.ids[0][i] = (uint16_t)i;
         if (p.mortonPre) p.mortonPre[base + i] = key;
     }
@@ -236,17 +250,18 @@ int launch_build_bvh(Context& c) {
     p.tlasMortonPre = c.keepPresortMorton ? c.dTlasMortonPre : nullptr;
     p.ticket = c.dTicket;
     p.fuseTlas = (c.numBatches <= (uint32_t)kSeg) ? 1 : 0;
+    p.spinLimit = c.tlasSpinLimit; p.keepAllTris = c.keepAllTris ? 1 : 0;
 
-    static bool attrSet = false;
     const size_t smem = sizeof(SegSmem);
-    if (!attrSet) {
+    if (!c.buildAttrSet) {                           // function attributes are per device: the flag lives in the (per-device) context
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         // 3 x (64 KB + 1 KB reserved) = 195 KB: ask for the 196 KB carve-out (85 % of 228 KB rounds up to it), the rest of the SM's 256 KB is L1
         const char* cv = getenv("RTRT_BUILD_CARVEOUT");
         RTRT_CUDA(c, cudaFuncSetAttribute(k_build_blas<kBuildThreads>, cudaFuncAttributePreferredSharedMemoryCarveout, cv ? atoi(cv) : 85));
-        attrSet = true;
+        c.buildAttrSet = true;
     }
     RTRT_CUDA(c, cudaMemsetAsync(c.dTicket, 0, sizeof(uint32_t), c.stream));
+    if (p.fuseTlas) c.buildErrPending = true;
     k_build_blas<kBuildThreads><<<c.numBatches + (p.fuseTlas ? 1u : 0u), kBuildThreads, smem, c.stream>>>(p);
     c.launches += 1;
     { int rc = geometry_consumed(c); if (rc) return rc; }   // the vertex buffers may be overwritten from here on

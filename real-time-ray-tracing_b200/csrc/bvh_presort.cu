@@ -119,8 +119,7 @@ int launch_presort(Context& c) {
     unsigned long long* keysAlt = reinterpret_cast<unsigned long long*>(p); p += al256(8 * (size_t)N);
     uint32_t* valsAlt = reinterpret_cast<uint32_t*>(p); p += al256(4 * (size_t)N);
     void* tmp = p;
-    static int smCount = 0;
-    if (!smCount) { cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c.device); if (smCount <= 0) smCount = 148; }
+    const int smCount = c.smCount;
     k_ps_init<<<1, 32, 0, c.stream>>>(ord);
     k_ps_bounds<<<smCount * 8, 256, 0, c.stream>>>(c.dPos, c.numVerts, ord);
     k_ps_codes<<<(N + 255) / 256, 256, 0, c.stream>>>(c.dPos, c.dIdx, N, ord, keys, c.dTriPerm, c.mortonBits == 63 ? 1 : 0);

@@ -29,6 +29,8 @@ static void free_mesh(Context& c) {
     if (c.dSortTmp) { cudaFree(c.dSortTmp); c.dSortTmp = nullptr; c.sortTmpBytes = 0; }
     if (c.dPresort) { cudaFree(c.dPresort); c.dPresort = nullptr; c.presortBytes = 0; }
     dfree(c.dIdxSorted); dfree(c.dTriPerm);
+    if (c.dWideNodes) cudaFree(c.dWideNodes); if (c.dWideTris) cudaFree(c.dWideTris); if (c.dWideQueue) cudaFree(c.dWideQueue);
+    c.dWideNodes = nullptr; c.dWideTris = nullptr; c.dWideQueue = nullptr; c.wideNodeCap = 0; c.wideValid = false; c.wideStatPending = false;
     c.numVerts = c.numTris = c.numBatches = c.numBatchesPadded = 0;
     c.bvhValid = false;
 }
@@ -137,12 +139,13 @@ int rtrt_create(const rtrt_config* cfg, int device, rtrt_ctx** out) {
     rtrt_set_denoise_defaults(&c.denoiseParams, &c.passSettings);
     rtrt_postprocess_defaults(&c.postParams);
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
+    if (cudaDeviceGetAttribute(&c.smCount, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || c.smCount <= 0) c.smCount = 148;
     if (cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     if (cudaStreamCreateWithFlags(&c.copyStream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     if (cudaStreamCreateWithFlags(&c.uploadStream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     for (cudaEvent_t* e : {&c.evGeomReady, &c.evGeomFree, &c.evStaged, &c.evReadDone}) cudaEventCreateWithFlags(e, cudaEventDisableTiming);
     for (auto& e : c.ev) { cudaEventCreate(&e[0]); cudaEventCreate(&e[1]); }
-    if (cudaMalloc((void**)&c.dTicket, 64) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
+    if (cudaMalloc((void**)&c.dTicket, 64) != cudaSuccess || cudaMemset(c.dTicket, 0, 64) != cudaSuccess) { delete h; return RTRT_ERR_CUDA; }
     *out = h;
     return RTRT_OK;
 }
@@ -240,6 +243,18 @@ int wait_geometry(Context& c) {
     if (c.geomPending) { RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.evGeomReady, 0)); c.geomPending = false; }
     return RTRT_OK;
 }
+// After a stream synchronisation: did the top-level CTA of a fused build give up waiting for the batch boxes (bvh_build.cu)?
+// The BVH is then incomplete: mark it invalid and report instead of tracing against a stale top level.
+int check_build_error(Context& c) {
+    if (!c.buildErrPending) return RTRT_OK;
+    c.buildErrPending = false;
+    uint32_t w[2] = {0, 0};
+    RTRT_CUDA(c, cudaMemcpy(w, c.dTicket, sizeof(w), cudaMemcpyDeviceToHost));
+    if (w[1] == 0u) return RTRT_OK;
+    RTRT_CUDA(c, cudaMemset(c.dTicket + 1, 0, sizeof(uint32_t)));
+    c.bvhValid = false;
+    return c.fail(RTRT_ERR_CUDA, "rtrt_build_bvh: the top-level CTA timed out waiting for the batch boxes; the BVH is incomplete (rebuild)");
+}
 int geometry_consumed(Context& c) {
     RTRT_CUDA(c, cudaEventRecord(c.evGeomFree, c.stream));
     c.geomFreeValid = true;
@@ -253,8 +268,9 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     Context& c = ctx->c;
     if (!name) return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: null name");
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
-    if (!strcmp(name, "stack_size")) { if (value < 1 || value > 32) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..32"); c.stackSize = (int)value; return RTRT_OK; }
-    if (!strcmp(name, "assume_bvh_valid")) { c.bvhValid = value != 0; return RTRT_OK; }
+    if (!strcmp(name, "stack_size")) { if (value < 1 || value > 64) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..64"); c.stackSize = (int)value; return RTRT_OK; }
+    if (!strcmp(name, "assume_bvh_valid")) { c.bvhValid = value != 0; c.wideValid = false; return RTRT_OK; }
+    if (!strcmp(name, "wide_bvh")) { c.wideBvh = value != 0; return RTRT_OK; }
     if (!strcmp(name, "morton_bits")) { if (value != 60 && value != 63) return c.fail(RTRT_ERR_ARG, "morton_bits must be 60 or 63"); c.mortonBits = (int)value; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
@@ -262,6 +278,8 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "any_hit_rays")) { c.anyHitRays = value != 0; return RTRT_OK; }
     if (!strcmp(name, "kernel_timing")) { c.kernelTiming = value != 0; return RTRT_OK; }
     if (!strcmp(name, "pt_chunks")) { if (value < 1 || value > Context::kMaxChunks) return c.fail(RTRT_ERR_ARG, "pt_chunks must be 1..8"); c.ptChunks = (int)value; return RTRT_OK; }
+    if (!strcmp(name, "tlas_spin_limit")) { if (value < 0 || value > (1ll << 31)) return c.fail(RTRT_ERR_ARG, "tlas_spin_limit out of range"); c.tlasSpinLimit = (uint32_t)value; return RTRT_OK; }
+    if (!strcmp(name, "keep_all_triangles")) { c.keepAllTris = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "max_loop")) { if (value < 1) return c.fail(RTRT_ERR_ARG, "max_loop must be >= 1"); c.maxLoop = (int)value; return RTRT_OK; }
     return c.fail(RTRT_ERR_ARG, "rtrt_set_option_i: unknown option");
 }
@@ -273,6 +291,8 @@ int rtrt_build_bvh(rtrt_ctx* ctx) {
     RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_BUILD][0], c.stream));
     int rc = launch_build_bvh(c);
     if (rc) return rc;
+    c.wideValid = false;
+    if (c.wideBvh) { rc = launch_wide_build(c); if (rc) return rc; }     // part of the build (and of its time) when the option is on
     RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_BUILD][1], c.stream));
     c.bvhValid = true;
     c.evPending[STAGE_BUILD] = true;    // resolved lazily in rtrt_get_timings
@@ -349,6 +369,9 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         case RTRT_BUF_EXPOSURE: p = c.dExposure; b = c.dExposure ? 16 : 0; break;
         case RTRT_BUF_HISTOGRAM: p = c.dExposure ? (void*)((float*)c.dExposure + 4) : nullptr; b = c.dExposure ? 256 : 0; break;
         case RTRT_BUF_WF_COUNTERS: p = c.dWf; b = c.dWf ? 256 : 0; break;
+        case RTRT_BUF_WIDE_NODES: p = c.wideValid ? c.dWideNodes : nullptr; b = ((size_t)c.numBatches * 512 + 2 * (size_t)c.numBatches + 8) * 128; break;
+        case RTRT_BUF_WIDE_TRIS: p = c.wideValid ? c.dWideTris : nullptr; b = n * 48; break;
+        case RTRT_BUF_WIDE_STAT: p = c.wideValid ? (void*)((char*)c.dWideQueue + (2 * (size_t)c.numBatches + 8) * 40) : nullptr; b = 16; break;
         case RTRT_BUF_SKY: p = c.dSky; b = sizeof(float) * 4 * kSkySize; break;
         case RTRT_BUF_SKY_CDF: p = c.dSkyCdf; b = sizeof(float) * kSkySize; break;
         case RTRT_BUF_SUN: p = c.dSun; b = sizeof(float) * 4 * kSunSize; break;
@@ -425,7 +448,8 @@ int rtrt_sync(rtrt_ctx* ctx) {
     RTRT_CUDA(c, cudaStreamSynchronize(c.copyStream));
     RTRT_CUDA(c, cudaStreamSynchronize(c.uploadStream));
     c.readPending = false;
-    return RTRT_OK;
+    { int rc = check_wide_error(c); if (rc) return rc; }
+    return check_build_error(c);
 }
 
 int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
@@ -434,6 +458,8 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
     if (!out) return c.fail(RTRT_ERR_ARG, "rtrt_get_timings: null out");
     RTRT_CUDA(c, cudaSetDevice(c.device));
     RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
+    { int rc = check_build_error(c); if (rc) return rc; }
+    { int rc = check_wide_error(c); if (rc) return rc; }
     float* slots[4] = {&c.timings.build_bvh_ms, &c.timings.traverse_ms, &c.timings.pathtrace_ms, &c.timings.denoise_ms};
     for (int s = 0; s < 4; ++s)
         if (c.evPending[s]) {

@@ -13,6 +13,9 @@ namespace rtrt {
 
 struct Context {
     int device = 0;
+    int smCount = 148;                       // SMs of `device` (rtrt_create)
+    bool buildAttrSet = false;               // k_build_blas shared-memory opt-in done on this device
+    int traceResident = 0, traceResidentWide = 0;   // resident k_pt_trace CTAs on this device (reference layout / wide layout)
     cudaStream_t stream = nullptr;
     std::string lastError;
     rtrt_config cfg{};
@@ -34,6 +37,13 @@ struct Context {
     bool globalSort = false;                              // option "global_sort": device Morton pre-sort of the triangles before batching
     uint32_t* dIdxSorted = nullptr; uint32_t* dTriPerm = nullptr; void* dPresort = nullptr; size_t presortBytes = 0;
     bool bvhValid = false;
+    // ---- wide traversal layout (option wide_bvh; wide_build.cu) ----
+    bool wideBvh = false, wideValid = false, wideStatPending = false;
+    void* dWideNodes = nullptr; void* dWideTris = nullptr; void* dWideQueue = nullptr; size_t wideNodeCap = 0;
+    uint32_t wideRoot = 0, wideNodes = 0;
+    uint32_t tlasSpinLimit = 1u << 22;                    // option "tlas_spin_limit" (test knob: 0 forces the time-out path)
+    bool keepAllTris = false;                             // option "keep_all_triangles"
+    bool buildErrPending = false;                         // a fused build was launched since the error word was last read
 
     // ---- traversal scratch for the host-buffer entry point ----
     Ray* dRayStage = nullptr; Hit* dHitStage = nullptr; uint32_t rayStageCap = 0;
@@ -115,7 +125,11 @@ enum { STAGE_BUILD = 0, STAGE_TRAVERSE = 1, STAGE_PATHTRACE = 2, STAGE_DENOISE =
 int launch_build_bvh(Context& c);
 int launch_build_tlas_global(Context& c);
 int launch_presort(Context& c);             // bvh_presort.cu
+int ensure_wide(Context& c);                // traverse.cu: builds the wide layout if option wide_bvh is on and it is stale
+int launch_wide_build(Context& c);          // wide_build.cu: 8-wide compressed nodes + 48-byte triangles from the arrays of the build
+int check_wide_error(Context& c);           // wide_build.cu: after a stream sync
 int wait_geometry(Context& c);              // capi.cu: main stream waits for a pending rtrt_update_vertices upload
+int check_build_error(Context& c);           // capi.cu: after a stream sync, turns the fused build's time-out word into RTRT_ERR_CUDA
 int geometry_consumed(Context& c);          // capi.cu: records that the main stream has read the vertex buffers
 int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int anyHit, unsigned long long* dCounters);
 int launch_pathtrace(Context& c);

@@ -134,9 +134,16 @@ int local_rows(const Context& c) {
 int launch_pathtrace(Context& c) {
     if (!c.bvhValid) return c.fail(RTRT_ERR_STATE, "rtrt_pathtrace: BVH not built");
     if (!c.cameraSet) return c.fail(RTRT_ERR_STATE, "rtrt_pathtrace: camera not set");
+    // the path-trace kernels keep the reference's 16-entry stack (src/traverse.h:28) in shared memory; a deeper one exists only in
+    // rtrt_traverse (<= 64) and in the wide layout (option wide_bvh: spill stack, no cap) — say so instead of clamping silently
+    if (!c.wideBvh && c.stackSize > 16)
+        return c.fail(RTRT_ERR_ARG, "rtrt_pathtrace: stack_size > 16 is honoured by rtrt_traverse only (use option wide_bvh for deep scenes)");
     int rc = ensure_frame_resources(c);       // G-buffers, blue noise, default materials / textures, sky
     if (rc) return rc;
+    rc = ensure_wide(c);
+    if (rc) return rc;
     if (c.wavefront) return launch_pathtrace_wavefront(c);
+    if (c.wideBvh) return c.fail(RTRT_ERR_ARG, "rtrt_pathtrace: the megakernel (wavefront = 0) traverses the reference layout only; switch wide_bvh off");
     PathTraceParams P{};
     fill_pathtrace_params(c, P);
     RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));

@@ -17,6 +17,7 @@
 // Path state in HBM (per pixel, SoA float4): orig|coneWidth, dir|coneSpread, beta0|albedo.x, beta1|albedo.y,
 // albedo.z|lightIdx|flags|mask+seg  and the hit record t|ua|va|tri = 96 B/px, touched only for live paths.
 #include "pathtrace_common.cuh"
+#include "wide_bvh.cuh"
 
 namespace rtrt {
 
@@ -179,23 +180,23 @@ VD void init_path(const PathTraceParams& P, RayState& r, Float2& sampleUv, int i
     generate_ray(r.orig, r.dir, r.centerRaydir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
 }
 
-template <bool COUNT>
+template <bool COUNT, class Trav>
 __global__ void __launch_bounds__(kPtThreads, RTRT_PRIMARY_MINB) k_pt_primary(const PathTraceParams P, const WfBuffers B) {
-    __shared__ uint32_t sLink[16 * kPtThreads];
-    __shared__ float sT[16 * kPtThreads];
+    __shared__ uint2 sRaw[16 * kPtThreads];
     const int tid = threadIdx.y * kPtBlockX + threadIdx.x, lane = tid & 31;
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
     const int jc = blockIdx.y * kPtBlockY + threadIdx.y, jy = chunk_row(P, jc), iy = frame_row(P, jy);
     uint32_t nodeVisits = 0, leafTests = 0;
     if (ix < P.width && jc < P.chunkRows && jy < P.localRows) {
-        const AABB sceneBox = scene_box(P.sc);
+        Trav tr;
+        tr.setup(P.sc, sRaw, tid, kPtThreads);
         const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
         Float3 orig, dir, centerDir; Float2 sampleUv;
         generate_ray(orig, dir, centerDir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
-        const RayPrep rp = prepare_ray(orig, dir, sceneBox);
-        const TraverseResult h = traverse_bvh<16, COUNT>(P.sc, rp, 0, sLink + tid, sT + tid, kPtThreads);
-        if (COUNT) { nodeVisits = h.nodeVisits; leafTests = h.leafTests; }
-        B.hit[(size_t)iy * P.width + ix] = make_float4(h.t, h.ua, h.va, __int_as_float(h.tri));
+        tr.begin(P.sc, orig, dir);
+        while (!tr.template step<COUNT>(P.sc, 0)) {}
+        if (COUNT) { nodeVisits = tr.nodeVisits(); leafTests = tr.leafTests(); }
+        B.hit[(size_t)iy * P.width + ix] = make_float4(tr.t(), tr.ua(), tr.va(), __int_as_float(tr.tri()));
     }
     if (COUNT && P.rayCounter) {
         for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
@@ -205,21 +206,16 @@ __global__ void __launch_bounds__(kPtThreads, RTRT_PRIMARY_MINB) k_pt_primary(co
 
 // ---------------------------------------------------------------------------------------------------------------------
 // k_pt_trace: persistent wavefront traversal with lane refill.  Queue entries are pixel ids; rays come from st0/st1.
+// Trav = ParityTrav (the reference's node / triangle arrays, its loop step by step) or WideTrav (8-wide compressed layout).
 // ---------------------------------------------------------------------------------------------------------------------
-template <bool COUNT>
+template <bool COUNT, class Trav>
 __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(const SceneView sc, const WfBuffers B, const uint32_t* __restrict__ countPtr,
                                                             uint32_t* fetchPtr, uint32_t* hitCount, uint32_t* missCount, unsigned long long* visitCounters) {
     const uint32_t* __restrict__ queue = B.rayQueue;
-    __shared__ uint32_t sLink[16 * kTraceThreads];
-    __shared__ float sT[16 * kTraceThreads];
+    __shared__ uint2 sRaw[16 * kTraceThreads];
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t n = *countPtr;
     if (n == 0u) return;
-    const AABB sceneBox = scene_box(sc);
-    const int cap = sc.stackSize < 16 ? sc.stackSize : 16;
-    const uint32_t numTri = sc.numBatches * kBatchSize;
-    const int maxLoop = sc.maxLoop;
-    uint32_t* stL = sLink + tid; float* stT = sT + tid;
     // Small queues (the later bounce rounds: a few 10^4 rays) are spread thin: with fewer rays than lanes on the device every warp
     // takes only `perWarp` rays at a time, so a warp's time is the longest of a few traversals (and each of its steps waits on a
     // few node loads) instead of the longest of 32.
@@ -230,10 +226,9 @@ __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(con
     bool active = false, exhausted = false;
     uint32_t pix = 0;
     int anyHit = 0;
-    RayPrep rp; TravState s;
+    Trav tr;
     uint32_t nodeVisits = 0, leafTests = 0;
-    trav_init(s);
-    rp = prepare_ray(Float3{0, 0, 0}, Float3{0, 1, 0}, sceneBox);
+    tr.setup(sc, sRaw, tid, kTraceThreads);
     while (true) {
         // ---- refill idle lanes from the queue ----
         const unsigned idle = __ballot_sync(0xffffffffu, !active) & laneMask;
@@ -248,8 +243,7 @@ __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(con
                     const uint32_t entry = __ldg(queue + q);
                     pix = entry & ~kAnyHitBit; anyHit = (int)(entry >> 31);
                     const float4 o = B.st0[pix], d = B.st1[pix];
-                    rp = prepare_ray(Float3{o.x, o.y, o.z}, Float3{d.x, d.y, d.z}, sceneBox);
-                    trav_init(s);
+                    tr.begin(sc, Float3{o.x, o.y, o.z}, Float3{d.x, d.y, d.z});
                     active = true;
                 }
             }
@@ -260,12 +254,12 @@ __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(con
         while (true) {
             bool finishedNow = false;
             if (active) {
-                if (trav_step<COUNT>(sc, rp, s, anyHit, cap, numTri, maxLoop, stL, stT, kTraceThreads)) {
-                    B.hit[pix] = make_float4(s.t, s.ua, s.va, __int_as_float(s.tri));
+                if (tr.template step<COUNT>(sc, anyHit)) {
+                    B.hit[pix] = make_float4(tr.t(), tr.ua(), tr.va(), __int_as_float(tr.tri()));
                     if (COUNT) {
-                        nodeVisits += s.nodeVisits; leafTests += s.leafTests;
-                        atomicMax(fetchPtr + 32, (uint32_t)s.it); atomicAdd(fetchPtr + 40, (uint32_t)s.it);      // diagnostics: [40+r] max, [48+r] sum of iterations
-                        atomicAdd(fetchPtr + 48, s.nodeVisits); atomicAdd(fetchPtr + 52, s.leafTests);          // [56+r] node visits, [60+r] leaf tests of the round
+                        nodeVisits += tr.nodeVisits(); leafTests += tr.leafTests();
+                        atomicMax(fetchPtr + 32, tr.iterations()); atomicAdd(fetchPtr + 40, tr.iterations());      // diagnostics: [40+r] max, [48+r] sum of iterations
+                        atomicAdd(fetchPtr + 48, tr.nodeVisits()); atomicAdd(fetchPtr + 52, tr.leafTests());      // [56+r] node visits, [60+r] leaf tests of the round
                     }
                     active = false; finishedNow = true;
                 }
@@ -273,13 +267,13 @@ __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(con
             // shade queue: hits from the front, misses from the back, so that k_pt_logic warps are all-surface or all-sky
             const unsigned fin = __ballot_sync(0xffffffffu, finishedNow);
             if (fin) {
-                const unsigned mh = __ballot_sync(0xffffffffu, finishedNow && s.tri >= 0), mm = fin & ~mh;
+                const unsigned mh = __ballot_sync(0xffffffffu, finishedNow && tr.tri() >= 0), mm = fin & ~mh;
                 uint32_t bh = 0, bm = 0;
                 if (mh) { const int l = __ffs(mh) - 1; if (lane == l) bh = atomicAdd(hitCount, (uint32_t)__popc(mh)); bh = __shfl_sync(0xffffffffu, bh, l); }
                 if (mm) { const int l = __ffs(mm) - 1; if (lane == l) bm = atomicAdd(missCount, (uint32_t)__popc(mm)); bm = __shfl_sync(0xffffffffu, bm, l); }
                 if (finishedNow) {
                     const unsigned below = (1u << lane) - 1u;
-                    if (s.tri >= 0) B.shadeQueue[bh + __popc(mh & below)] = pix;
+                    if (tr.tri() >= 0) B.shadeQueue[bh + __popc(mh & below)] = pix;
                     else B.shadeQueue[B.capacity - 1u - (bm + __popc(mm & below))] = pix;
                 }
             }
@@ -410,27 +404,34 @@ static void launch_chunk(Context& c, const PathTraceParams& P, const WfBuffers& 
         for (auto& e : c.kev) if (!e) cudaEventCreate(&e);
         cudaEventRecord(c.kev[0], st);
     }
-    if (c.countVisits) k_pt_primary<true><<<grid, block, 0, st>>>(P, B);
-    else k_pt_primary<false><<<grid, block, 0, st>>>(P, B);
+    const bool wide = c.wideBvh;
+    if (wide) { if (c.countVisits) k_pt_primary<true, WideTrav><<<grid, block, 0, st>>>(P, B); else k_pt_primary<false, WideTrav><<<grid, block, 0, st>>>(P, B); }
+    else      { if (c.countVisits) k_pt_primary<true, ParityTrav><<<grid, block, 0, st>>>(P, B); else k_pt_primary<false, ParityTrav><<<grid, block, 0, st>>>(P, B); }
     if (kt) cudaEventRecord(c.kev[1], st);
     const int tiles = ((c.width + 7) / 8) * ((rows + 3) / 4);
     k_pt_logic_first<<<(tiles + kLogicThreads / 32 - 1) / (kLogicThreads / 32), kLogicThreads, 0, st>>>(P, B, B.counters + 0);
     c.launches += 2;
     if (kt) cudaEventRecord(c.kev[2], st);
     // persistent grids sized for the chunk: at most one CTA per 128 pixels, never more than are resident at once
-    static int traceResident = 0;
-    if (!traceResident) {
+    if (!c.traceResident) {                          // per context = per device (a process may hold contexts on several GPUs)
         int perSm = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_pt_trace<false>, kTraceThreads, 0);
-        traceResident = smCount * (perSm > 0 ? perSm : 4);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_pt_trace<false, ParityTrav>, kTraceThreads, 0);
+        c.traceResident = smCount * (perSm > 0 ? perSm : 4);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_pt_trace<false, WideTrav>, kTraceThreads, 0);
+        c.traceResidentWide = smCount * (perSm > 0 ? perSm : 4);
     }
-    const int maxGrid = traceResident;
+    const int maxGrid = wide ? c.traceResidentWide : c.traceResident;
     const int want = (int)(((size_t)c.width * rows + 127) / 128);
     const int traceGrid = want < maxGrid ? (want > 0 ? want : 1) : maxGrid, logicGrid = traceGrid;
     for (int round = 0; round < 4; ++round) {
         uint32_t* cnt = B.counters;
-        if (c.countVisits) k_pt_trace<true><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
-        else k_pt_trace<false><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
+        if (wide) {
+            if (c.countVisits) k_pt_trace<true, WideTrav><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
+            else k_pt_trace<false, WideTrav><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
+        } else {
+            if (c.countVisits) k_pt_trace<true, ParityTrav><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, c.dRayCounter);
+            else k_pt_trace<false, ParityTrav><<<traceGrid, kTraceThreads, 0, st>>>(P.sc, B, cnt + round, cnt + 8 + round, cnt + 16 + round, cnt + 24 + round, nullptr);
+        }
         if (kt && round < 2) cudaEventRecord(c.kev[3 + 2 * round], st);
         k_pt_logic<<<logicGrid, kLogicThreads, 0, st>>>(P, B, cnt + 16 + round, cnt + 24 + round, cnt + round + 1);
         if (kt && round == 0) cudaEventRecord(c.kev[4], st);
@@ -447,8 +448,7 @@ int launch_pathtrace_wavefront(Context& c) {
     WfBuffers B{};
     int rc = ensure_wf_buffers(c, B);
     if (rc) return rc;
-    static int smCount = 0;
-    if (!smCount) { cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c.device); if (smCount <= 0) smCount = 148; }
+    const int smCount = c.smCount;
     RTRT_CUDA(c, cudaMemsetAsync(B.counters, 0, 256 * Context::kMaxChunks, c.stream));
     RTRT_CUDA(c, cudaMemsetAsync(c.dRayCounter, 0, 3 * sizeof(unsigned long long), c.stream));
     const int rows = local_rows(c);

@@ -183,11 +183,8 @@ inline int radix_sort_pairs(cudaStream_t stream, K* keys, uint32_t* vals, K* key
     uint32_t* tileHist = reinterpret_cast<uint32_t*>(tmp);
     uint32_t* digitTotal = tileHist + (size_t)256 * numTiles;
     constexpr size_t exchangeBytes = (sizeof(K) + sizeof(uint32_t)) * kRsTile;       // 24 KB (64-bit keys) / 16 KB + ~6 KB static
-    static bool attrSet = false;
-    if (!attrSet) {
-        if (cudaFuncSetAttribute(k_rs_scatter<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)exchangeBytes) != cudaSuccess) return -1;
-        attrSet = true;
-    }
+    // function attributes are per device and contexts may live on several GPUs of one process: set it on every call (host-side, cheap)
+    if (cudaFuncSetAttribute(k_rs_scatter<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)exchangeBytes) != cudaSuccess) return -1;
     int cur = 0;
     for (int shift = beginBit; shift < endBit; shift += 8) {
         K* kin = cur ? keysAlt : keys; uint32_t* vin = cur ? valsAlt : vals;

@@ -21,12 +21,20 @@
 
 namespace rtrt {
 
+// the 8-wide compressed layout (wide_bvh.cuh), null when option wide_bvh is off
+struct WideView {
+    const float4* __restrict__ nodes;            // 8 float4 rows (128 B) per node, 80 B used
+    const float4* __restrict__ tris;             // 3 float4 rows per triangle, row0.w = original triangle index
+    uint32_t root;                               // index of the top-level root node
+};
+
 struct SceneView {
     const float4* __restrict__ triRows;     // Triangle[] viewed as 8 float4 rows per triangle
     const float4* __restrict__ nodeRows;    // BVHNode[]  viewed as 4 float4 rows per node (BLAS, 1024 per batch)
     const float4* __restrict__ tlasRows;    // TLAS nodes
     uint32_t numBatches;
     int stackSize, maxLoop;
+    WideView wide;
 };
 
 __device__ __forceinline__ float comp(const Float3& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }

@@ -151,3 +151,70 @@ def test_global_morton_presort(pkg, orc, quads, bits):
         assert_bvh_equal(read_all_stage1(r, pkg, presort=True), ob, pkg)
         r.build_bvh()                                     # per-frame re-sort + rebuild is repeatable
         assert_bvh_equal(read_all_stage1(r, pkg, presort=True), ob, pkg)
+
+
+def test_fused_tlas_timeout_is_an_error(pkg):
+    """if the top-level CTA of the fused build gives up waiting for the batch boxes, the build must not report success with a
+    stale top level.  tlas_spin_limit = 0 forces the time-out: the next synchronisation point returns RTRT_ERR_CUDA, the BVH is
+    invalid, and a normal rebuild recovers."""
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=1)
+    with pkg.RayTracer(64, 64) as r:
+        r.set_mesh(pos, idx, nrm)
+        r.set_option("tlas_spin_limit", 0)
+        r.build_bvh()
+        with pytest.raises(pkg.RtrtError) as e:
+            r.sync()
+        assert e.value.code == -2
+        with pytest.raises(pkg.RtrtError) as e:
+            r.traverse(np.zeros(4, pkg.RAY_DTYPE))
+        assert e.value.code == -4                      # RTRT_ERR_STATE: BVH not built
+        r.set_option("tlas_spin_limit", 1 << 22)
+        r.build_bvh(); r.sync()
+        assert r.traverse(np.zeros(4, pkg.RAY_DTYPE)).shape == (4,)
+
+
+@pytest.mark.parametrize("n", [5, 1025, 2050])
+def test_keep_all_triangles_option(pkg, n):
+    """Reference quirk (src/init.cu:103-115, src/updateGeometry.cuh:93): when N % 4 != 0 the up-to-3 pad items of the last batch get real
+    Morton keys and can push real triangles out of the hierarchy.  Default = reproduced; keep_all_triangles = 1 keeps every real one."""
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=1)
+    idx = np.ascontiguousarray(idx[:n])
+    with pkg.RayTracer(64, 64) as r:
+        r.set_option("keep_all_triangles", 1)
+        r.set_mesh(pos, idx, nrm); r.build_bvh()
+        nodes = r.read_buffer(pkg.BUF_BVH_NODES)
+        last = n - 1024 * ((n - 1) // 1024)
+        leaves = tree_leaves(nodes[1024 * ((n - 1) // 1024):], last)
+        assert sorted(leaves) == list(range(last)), "a real triangle of the last batch is missing from the hierarchy"
+
+
+def test_pathtrace_rejects_deep_parity_stack(pkg):
+    pos, nrm, idx = pkg.scenes.terrain(16, 16, seed=1)
+    with pkg.RayTracer(64, 64) as r:
+        r.set_mesh(pos, idx, nrm); r.build_bvh()
+        r.set_camera(pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 64, 64), reset_history=True)
+        r.set_option("stack_size", 32)
+        with pytest.raises(pkg.RtrtError) as e:
+            r.pathtrace()
+        assert e.value.code == -1
+        r.set_option("wide_bvh", 1)                     # the wide layout has a spill stack: any stack_size is fine
+        r.build_bvh(); r.pathtrace(); r.sync()
+
+
+def test_contexts_on_two_devices_in_one_process(pkg, orc):
+    """kernel attributes (dynamic shared memory opt-in) are per device; contexts on GPUs 0 and 1 of ONE process must both build."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=1)
+    ob = orc.build_bvh(pos, nrm, idx)
+    cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 64, 64)
+    rays = pkg.scenes.primary_rays(cam, 64, 64)
+    for dev in (0, 1):
+        with pkg.RayTracer(64, 64, device=dev) as r:
+            r.set_option("global_sort", 0)
+            r.set_mesh(pos, idx, nrm); r.build_bvh()
+            assert_bvh_equal(read_all_stage1(r, pkg), ob, pkg)
+            from helpers import assert_hits_equal
+            assert_hits_equal(r.traverse(rays), orc.traverse(ob, rays))
+            r.set_camera(cam, reset_history=True); r.pathtrace(); r.denoise(); r.sync()

@@ -1,0 +1,220 @@
+"""GPU tests of the wide traversal layout (option wide_bvh, csrc/wide_bvh.cuh + wide_build.cu).
+
+Parity contract of the mode (include/rtrt.h): the closest hit (tri, t, u, v) is bit-identical to the reference's search
+(src/traverse.h:107-253) on every ray where the reference neither drops a push on its full 16-entry stack nor stops at its
+1024-iteration cap, up to exact ties in t between two triangles.  Checked here as
+
+    wide  ==  reference-layout traversal with a 64-entry stack and max_loop 2^20  ==  CPU oracle with the same settings
+
+on primary and incoherent rays; the rays on which the CAPPED reference search differs from the uncapped one are counted and
+printed (they are the only rays on which wide_bvh = 1 can differ from wide_bvh = 0).  The structure itself (every triangle exactly
+once, decoded child boxes enclose their subtrees, slot ordering) is verified on the host from the raw node / triangle arrays."""
+import numpy as np
+import pytest
+
+from helpers import assert_hits_equal, read_all_stage1, assert_bvh_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def _random_rays(pkg, n, seed, lo, hi):
+    rng = np.random.default_rng(seed)
+    rays = np.zeros(n, pkg.RAY_DTYPE)
+    rays["orig"] = rng.uniform(lo, hi, size=(n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    rays["dir"] = d / np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    return rays
+
+
+def _bounce_rays(pkg, pos, idx, n, seed):
+    """Incoherent rays that start ON the surface (like bounce / shadow rays): origin = a point of a random triangle pushed a
+    little along +y, direction uniform on the sphere."""
+    rng = np.random.default_rng(seed)
+    t = rng.integers(0, idx.shape[0], n)
+    w = rng.dirichlet((1, 1, 1), n).astype(np.float32)
+    p = (pos[idx[t, 0]] * w[:, :1] + pos[idx[t, 1]] * w[:, 1:2] + pos[idx[t, 2]] * w[:, 2:3]).astype(np.float32)
+    rays = np.zeros(n, pkg.RAY_DTYPE)
+    rays["orig"] = p + np.float32([0, 1e-3, 0])
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    rays["dir"] = d / np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    return rays
+
+
+def decode_nodes(raw):
+    """raw: (n, 128) uint8 -> dict of per-node fields"""
+    f = raw[:, :12].copy().view(np.float32)                      # px, py, pz
+    e = raw[:, 12:15].astype(np.int32)
+    imask = raw[:, 15]
+    base = raw[:, 16:24].copy().view(np.uint32)                   # childBase, triBase
+    meta = raw[:, 24:32]
+    q = raw[:, 32:80].reshape(-1, 6, 8)                           # lox, loy, loz, hix, hiy, hiz
+    scale = np.ldexp(np.float64(1.0), e - 127)                    # (n, 3)
+    lo = f[:, None, :].astype(np.float64) + q[:, 0:3, :].transpose(0, 2, 1) * scale[:, None, :]     # (n, 8, 3)
+    hi = f[:, None, :].astype(np.float64) + q[:, 3:6, :].transpose(0, 2, 1) * scale[:, None, :]
+    return {"origin": f, "imask": imask, "childBase": base[:, 0], "triBase": base[:, 1], "meta": meta, "lo": lo, "hi": hi}
+
+
+def check_structure(pkg, rt, n_tris, n_batches):
+    stat = rt.read_buffer(pkg.BUF_WIDE_STAT)
+    assert stat[0] == 0, f"wide build error flags {stat[0]}"
+    raw = rt.read_buffer(pkg.BUF_WIDE_NODES)
+    tris = rt.read_buffer(pkg.BUF_WIDE_TRIS).reshape(-1, 3, 4)
+    ref = rt.read_buffer(pkg.BUF_TRIANGLES)
+    nd = decode_nodes(raw)
+    root = 512 * n_batches
+    seen = np.zeros(n_batches * 1024, np.int32)
+    n_nodes = 0
+    max_depth = 0
+    fill = []
+
+    def visit(i, depth):
+        """returns (lo, hi) of the subtree's triangles; asserts every decoded child box encloses its subtree"""
+        nonlocal n_nodes, max_depth
+        n_nodes += 1; max_depth = max(max_depth, depth)
+        lo_all, hi_all = np.full(3, np.inf), np.full(3, -np.inf)
+        inner_rank = 0
+        used = 0
+        for s in range(8):
+            m = int(nd["meta"][i, s])
+            if m == 0:
+                assert not (nd["imask"][i] >> s) & 1
+                continue
+            used += 1
+            if (m & 0x18) == 0x18 and (m >> 5) == 1:              # inner: 0x20 | (24 + s)
+                assert (m & 0x1F) == 24 + s and (nd["imask"][i] >> s) & 1
+                clo, chi = visit(int(nd["childBase"][i]) + inner_rank, depth + 1)
+                inner_rank += 1
+            else:
+                assert not (nd["imask"][i] >> s) & 1
+                k = {1: 1, 3: 2, 7: 3}[m >> 5]
+                first = int(nd["triBase"][i]) + (m & 0x1F)
+                v = tris[first:first + k, :, :3].astype(np.float64)
+                ids = tris[first:first + k, 0, 3].copy().view(np.int32)
+                for j, t in enumerate(ids):
+                    seen[t] += 1
+                    r = ref[t]
+                    assert np.array_equal(tris[first + j, 0, :3], r["v1"]) and np.array_equal(tris[first + j, 1, :3], r["v2"]) and \
+                        np.array_equal(tris[first + j, 2, :3], r["v3"])
+                clo, chi = v.reshape(-1, 3).min(axis=0), v.reshape(-1, 3).max(axis=0)
+            assert np.all(nd["lo"][i, s] <= clo) and np.all(nd["hi"][i, s] >= chi), f"node {i} slot {s}: decoded box does not enclose the subtree"
+            lo_all = np.minimum(lo_all, clo); hi_all = np.maximum(hi_all, chi)
+        assert used >= 1
+        fill.append(used)
+        return lo_all, hi_all
+
+    import sys
+    sys.setrecursionlimit(10000)
+    visit(root, 0)
+    return seen, n_nodes, max_depth, float(np.mean(fill))
+
+
+@pytest.mark.parametrize("quads", [(64, 80), (3, 1), (16, 31), (128, 131)])
+def test_wide_structure(pkg, quads):
+    """10 240 triangles (10 batches), 6 triangles (one tiny batch), 992 triangles (one partial batch), 33 536 (partial last batch)."""
+    pos, nrm, idx = pkg.scenes.terrain(*quads, seed=3)
+    n = idx.shape[0]
+    with pkg.RayTracer(64, 64) as rt:
+        rt.set_option("wide_bvh", 1)
+        rt.set_mesh(pos, idx, nrm); rt.build_bvh(); rt.sync()
+        nb = rt.counts()[1]
+        seen, n_nodes, depth, fill = check_structure(pkg, rt, n, nb)
+    assert (seen[:n] == 1).all() if n % 4 == 0 else (seen.sum() == n)       # (pad items may replace real triangles when N % 4 != 0, a reference quirk)
+    assert seen[n:].sum() == 0 or n % 4 != 0
+    print(f"{n} tris: {n_nodes} wide nodes, depth {depth}, {fill:.2f} children per node")
+
+
+def _compare(pkg, orc, pos, nrm, idx, rays, label, capsys):
+    ob = orc.build_bvh(pos, nrm, idx)
+    with pkg.RayTracer(64, 64) as rt:
+        rt.set_mesh(pos, idx, nrm); rt.build_bvh()
+        capped = rt.traverse(rays)                                  # the reference's search, caps and all
+        rt.set_option("stack_size", 64); rt.set_option("max_loop", 1 << 20)
+        deep = rt.traverse(rays)                                    # the same search without the caps
+        rt.set_option("wide_bvh", 1)
+        rt.build_bvh()
+        wide = rt.traverse(rays)
+        wide_any = rt.traverse(rays, any_hit=True)
+        # the reference-layout arrays are untouched by the option
+        assert_bvh_equal(read_all_stage1(rt, pkg), ob, pkg)
+    assert_hits_equal(deep, orc.traverse(ob, rays, stack_size=64, max_loop=1 << 20))
+    quirk = (capped["tri"] != deep["tri"]) | (capped["t"].view(np.uint32) != deep["t"].view(np.uint32))
+    diff = (wide["tri"] != deep["tri"]) | (wide["t"].view(np.uint32) != deep["t"].view(np.uint32))
+    tie = diff & (wide["t"].view(np.uint32) == deep["t"].view(np.uint32))          # same t, other triangle: first found wins, order differs
+    unexplained = diff & ~tie
+    uv = (~diff) & ((wide["u"].view(np.uint32) != deep["u"].view(np.uint32)) | (wide["v"].view(np.uint32) != deep["v"].view(np.uint32)))
+    with capsys.disabled():
+        print(f"\n[{label}] {rays.shape[0]} rays, hit rate {(deep['tri'] >= 0).mean():.3f}: wide vs uncapped reference search: {int(diff.sum())} differ "
+              f"({int(tie.sum())} exact ties in t, {int(unexplained.sum())} unexplained), u/v differ on {int(uv.sum())} equal hits; "
+              f"capped reference (16 entries / 1024 iterations) differs from its uncapped self on {int(quirk.sum())} rays")
+    assert unexplained.sum() == 0
+    assert tie.sum() <= max(2, rays.shape[0] // 100000)
+    assert uv.sum() <= tie.sum() + max(2, rays.shape[0] // 100000)      # u, v of the reference are overwritten by tied acceptances
+    assert np.array_equal(wide_any["tri"] >= 0, deep["tri"] >= 0), "any-hit classification differs from the closest-hit search"
+    return int(quirk.sum())
+
+
+def test_wide_hits_c1(pkg, orc, capsys):
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C1"], seed=1)
+    cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 256, 256)
+    rays = np.concatenate([pkg.scenes.primary_rays(cam, 256, 256), _random_rays(pkg, 100000, 7, (-60, -10, -60), (60, 20, 60)),
+                           _bounce_rays(pkg, pos, idx, 200000, 9)])
+    # axis-aligned directions (zero components -> safe_divide path), rays from inside boxes
+    rays["dir"][65536:65836] = np.tile(np.eye(3, dtype=np.float32), (100, 1))
+    rays["dir"][65836:66136] = -np.tile(np.eye(3, dtype=np.float32), (100, 1))
+    _compare(pkg, orc, pos, nrm, idx, rays, "C1", capsys)
+
+
+def test_wide_hits_grazing(pkg, orc, capsys):
+    """Grazing rays over the terrain: deep stacks and long walks, where the reference's caps bite."""
+    pos, nrm, idx = pkg.scenes.terrain(64, 80, seed=2)
+    rays = _random_rays(pkg, 100000, 11, (-60, 0, -60), (60, 6, 60))
+    rays["dir"][:, 1] *= 0.05
+    rays["dir"] /= np.linalg.norm(rays["dir"], axis=1, keepdims=True)
+    _compare(pkg, orc, pos, nrm, idx, rays, "grazing", capsys)
+
+
+def test_wide_hits_c2(pkg, orc, capsys):
+    """Bench geometry: 1 047 552 triangles, 1080p primary rays + 1 M surface-born incoherent rays."""
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C2ref"], seed=1)
+    cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 1920, 1080)
+    rays = np.concatenate([pkg.scenes.primary_rays(cam, 1920, 1080), _bounce_rays(pkg, pos, idx, 1000000, 5)])
+    _compare(pkg, orc, pos, nrm, idx, rays, "C2", capsys)
+
+
+def test_wide_hits_beyond_1024_batches(pkg, orc, capsys):
+    """C3 geometry (4096 batches, global top level): the reference's caps drop subtrees here, the wide layout must not.
+    Also bounds the capped search's miss rate (reported in DESIGN.md)."""
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C3"], seed=5)
+    cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 640, 360)
+    rays = np.concatenate([pkg.scenes.primary_rays(cam, 640, 360), _bounce_rays(pkg, pos, idx, 300000, 6)])
+    quirk = _compare(pkg, orc, pos, nrm, idx, rays, "C3", capsys)
+    assert quirk <= rays.shape[0] // 20
+
+
+def test_wide_frame_outputs_match_reference_layout(pkg, capsys):
+    """rtrt_pathtrace with wide_bvh = 1 vs wide_bvh = 0 on the same frames: G-buffers identical on all but a handful of pixels."""
+    W, H = 640, 360
+    pos, nrm, idx = pkg.scenes.terrain(300, 512, seed=1)
+    out = {}
+    for wide in (0, 1):
+        with pkg.RayTracer(W, H) as rt:
+            rt.set_option("wide_bvh", wide)
+            rt.set_mesh(pos, idx, nrm); rt.build_bvh()
+            frames = []
+            for frame in (1, 2, 3):
+                cam = pkg.scenes.make_camera((0.3 * frame, 30, -60 + 0.2 * frame), 0.01 * frame, -0.4, W, H)
+                rt.set_camera(cam, reset_history=(frame == 1)); rt.set_frame_number(frame)
+                rt.pathtrace()
+                frames.append({k: rt.read_buffer(b) for k, b in [("color", pkg.BUF_RENDER_COLOR), ("normal", pkg.BUF_NORMAL), ("albedo", pkg.BUF_ALBEDO),
+                                                                 ("depth", pkg.BUF_DEPTH), ("motion", pkg.BUF_MOTION_VECTOR)]})
+                rt.denoise()
+            frames.append({"denoised": rt.read_buffer(pkg.BUF_RENDER_COLOR)})
+            out[wide] = frames, rt.timings()["rays_traced"]
+    for fr, (a, b) in enumerate(zip(out[0][0][:3], out[1][0][:3]), start=1):
+        same = np.ones(W * H, bool)
+        for k in a:
+            same &= (a[k].view(np.uint8).reshape(W * H, -1) == b[k].view(np.uint8).reshape(W * H, -1)).all(axis=1)
+        with capsys.disabled():
+            print(f"\n[wide vs reference layout, frame {fr}] {int((~same).sum())} of {W * H} pixels differ in any G-buffer bit")
+        assert (~same).sum() <= 20
+    assert abs(out[0][1] - out[1][1]) <= 40
