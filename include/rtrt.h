@@ -133,7 +133,9 @@ typedef struct rtrt_denoise_params {
     float temporal_denoise_sigma_normal, temporal_denoise_sigma_depth, temporal_denoise_sigma_material;
     float noise_threshold_local, noise_threshold_large;
 } rtrt_denoise_params;
-/* the denoiser toggles of RenderPassSettings (src/settingParams.h:66-99) */
+/* the denoiser toggles of RenderPassSettings (src/settingParams.h:66-99).  enableWideSpatialFilter = 2 selects the 5-iteration a-trous
+ * schedule of BASELINE config 4: five SpatialFilterGlobal5x5 passes with strides 1, 2, 4, 8, 16 (the kernel template of
+ * src/temporalDenoising.cuh:495-608 with the classic power-of-two strides) instead of the shipped three with strides 3, 6, 12. */
 typedef struct rtrt_pass_settings {
     int32_t enableTemporalDenoising, enableLocalSpatialFilter, enableWideSpatialFilter, enableTemporalDenoising2;
 } rtrt_pass_settings;
@@ -312,6 +314,57 @@ int rtrt_read_buffer_async(rtrt_ctx* ctx, int which, void* dst, size_t dst_bytes
 int rtrt_join(rtrt_ctx* ctx);
 int rtrt_sync(rtrt_ctx* ctx);
 int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out);   /* synchronises the stream */
+/* ---- multi-GPU: SURVEY 8(b) `rtrt_create_multi`, 8(e) (csrc/multi.cu).  No counterpart in the reference (single-GPU); the stages are those of
+ * RayTracer::draw (src/kernel.cu:259-362).  One context per GPU and rank (one process per GPU, or one host thread per context).  NCCL over
+ * NVLink carries the vertex broadcast, the strip -> band redistribution of the G-buffers, the a-trous HALO EXCHANGE between the denoiser's
+ * passes and the frame-buffer gather; NCCL is loaded with dlopen at the first use (RTRT_NCCL_LIB overrides the library path) and its errors
+ * are reported as RTRT_ERR_NCCL.
+ *   rtrt_multi_unique_id    ncclGetUniqueId: 128 bytes the host hands to every rank (MPI, torch.distributed, a file)
+ *   rtrt_create_multi       rtrt_create + rtrt_multi_init
+ *   rtrt_multi_init         ncclCommInitRank on the context's device; the context becomes rank `rank` of `world`
+ *   rtrt_multi_attach_comm  the same with a caller-owned ncclComm_t (must come from the NCCL library this process uses)
+ *   rtrt_multi_link_local   N contexts of ONE process become ranks 0..N-1 of an in-process group (copies between the contexts, host barriers;
+ *                           each context must then be driven by its own host thread): single-process multi-GPU, and the single-GPU tests
+ *   rtrt_multi_set_mode     RTRT_MULTI_ROWS (default): ONE frame, path-traced in interleaved strips of `strip_height` rows (strip k -> rank k % N)
+ *                           and denoised in contiguous bands of whole 16-row tiles with a halo exchange per filter pass (strong scaling);
+ *                           RTRT_MULTI_SAMPLES: every rank renders the whole frame with sample index frame + rank, the denoised frames are
+ *                           averaged by one all-reduce (weak scaling: N samples per pixel and frame)
+ *   rtrt_update_vertices_multi   rank 0 passes the host arrays (others NULL): one PCIe upload, NCCL broadcast of the vertex / normal buffers
+ *   rtrt_render_frame_multi      one frame; on return RTRT_BUF_RENDER_COLOR holds the whole denoised frame on EVERY rank and the temporal history
+ *                                is complete; frame number += 1 (rows) or += N (samples).  Collective: every rank must call it
+ *   rtrt_render_progressive_multi  BASELINE config 5: spp samples accumulated in fp32, rank r renders samples r, r + N, ... of the whole frame, one
+ *                                all-reduce (sum) of RTRT_BUF_ACCUM_RADIANCE at the end
+ *   rtrt_multi_get_band     the rank's denoiser band, and the exchanges / bytes sent so far
+ *   rtrt_multi_plan_rows    pure host function (no GPU): the rows `rank` sends to `peer` in exchange kind 0 (G-buffer redistribution: rows of
+ *                           rank's strips inside peer's band +- 32), 1 (halo of `halo` rows around peer's band), 2 (frame gather); returns the
+ *                           count and writes up to `cap` row numbers */
+#define RTRT_NCCL_UNIQUE_ID_BYTES 128
+#define RTRT_MULTI_ROWS 0
+#define RTRT_MULTI_SAMPLES 1
+int rtrt_multi_unique_id(void* id_out_128_bytes);
+int rtrt_create_multi(const rtrt_config* cfg_or_null, int device, const void* unique_id, int rank, int world, rtrt_ctx** out);
+int rtrt_multi_init(rtrt_ctx* ctx, const void* unique_id, int rank, int world);
+int rtrt_multi_attach_comm(rtrt_ctx* ctx, void* nccl_comm, int rank, int world);
+int rtrt_multi_link_local(rtrt_ctx** ctxs, int n);
+int rtrt_multi_set_mode(rtrt_ctx* ctx, int mode, int strip_height);
+int rtrt_update_vertices_multi(rtrt_ctx* ctx, const float* pos_rank0, const float* nrm_rank0_or_null, uint32_t num_vertices);
+int rtrt_render_frame_multi(rtrt_ctx* ctx);
+int rtrt_render_progressive_multi(rtrt_ctx* ctx, int32_t spp, int32_t first_frame);
+int rtrt_multi_get_band(rtrt_ctx* ctx, int32_t* row_begin, int32_t* row_end, uint64_t* exchanges, uint64_t* bytes_sent);
+int rtrt_multi_plan_rows(int32_t height, int32_t world, int32_t strip_height, int32_t rank, int32_t peer, int32_t kind, int32_t halo,
+                         int32_t* rows_out, int32_t cap);
+
+/* Measured ceilings of a traversal without RT cores on this GPU (csrc/microbench.cu; replaces nothing in the reference — it is the
+ * denominator SURVEY 8(d) asks for: "node-fetch bytes/s vs measured L2 bandwidth"): L2 read bandwidth of all SMs streaming an
+ * L2-resident 32 MiB buffer, and the latency of one dependent 128-byte-line load served by L1 (64 KiB set), L2 (16 MiB) and DRAM
+ * (512 MiB).  Allocates and frees its own buffers, synchronises; not for timed regions. */
+typedef struct rtrt_microbench_result {
+    float l2_read_gbs;
+    float l1_latency_ns, l2_latency_ns, dram_latency_ns;
+    float l1_latency_cycles, l2_latency_cycles, dram_latency_cycles;
+    float reserved_;
+} rtrt_microbench_result;
+int rtrt_microbench(rtrt_ctx* ctx, rtrt_microbench_result* out);
 /* the cudaStream_t all work is enqueued on, as an opaque pointer (for event timing by the caller) */
 void* rtrt_get_stream(rtrt_ctx* ctx);
 

@@ -318,7 +318,10 @@ int orc_denoise_hist(int W, int H, int accumW, int accumH, int histW, int histH,
     if (passes4[0]) std::memcpy(accumOut, cur, n * sizeof(Px4));                       // CopyToHistoryColorBuffer
     if (passes4[2]) {
         noise_levels(f, Img{W, H, cur}, (h16*)noise8, (h16*)noise16);
-        for (int S : {3, 6, 12}) { spatial5x5(f, Img{W, H, cur}, nxt, (const h16*)noise16, S, p, threads); swap(); }
+        // passes4[2] == 2: the 5-iteration a-trous schedule of BASELINE config 4 (strides 1, 2, 4, 8, 16: the same kernel template,
+        // src/temporalDenoising.cuh:495-608, instantiated with the classic power-of-two strides instead of the shipped 3, 6, 12)
+        if (passes4[2] == 2) { for (int S : {1, 2, 4, 8, 16}) { spatial5x5(f, Img{W, H, cur}, nxt, (const h16*)noise16, S, p, threads); swap(); } }
+        else { for (int S : {3, 6, 12}) { spatial5x5(f, Img{W, H, cur}, nxt, (const h16*)noise16, S, p, threads); swap(); } }
     }
     apply_albedo(f, Img{W, H, cur}, nxt, threads); swap();
     if (passes4[3]) {

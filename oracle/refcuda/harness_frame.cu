@@ -247,9 +247,17 @@ int refcuda_frame_denoise(void* h, int frameNum, const int* passes, const float*
     if (passes[2]) {
         CalculateTileNoiseLevel<<<gridDim8, dim3(8, 4, 1)>>>(S(RB_COLOR), S(RB_DEPTH), S(RB_NOISE), bufferDim);
         TileNoiseLevel8x8to16x16<<<dim3(divRoundUp(n16.x, 8), divRoundUp(n16.y, 8), 1), blockDim8>>>(S(RB_NOISE), S(RB_NOISE16));
+        if (passes[2] == 2) {      // BASELINE config 4's 5-iteration a-trous schedule: the reference's kernel template with strides 1, 2, 4, 8, 16
+            SpatialFilterGlobal5x5<1><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
+            SpatialFilterGlobal5x5<2><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
+            SpatialFilterGlobal5x5<4><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
+            SpatialFilterGlobal5x5<8><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
+            SpatialFilterGlobal5x5<16><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
+        } else {
         SpatialFilterGlobal5x5<3><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
         SpatialFilterGlobal5x5<6><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
         SpatialFilterGlobal5x5<12><<<grid16, block16>>>(cbo, S(RB_COLOR), S(RB_NORMAL), S(RB_DEPTH), S(RB_NOISE16), dp, bufferDim);
+        }
     }
     ApplyAlbedo<<<gridDim8, blockDim8>>>(S(RB_COLOR), S(RB_ALBEDO), bufferDim);
     if (passes[3]) {

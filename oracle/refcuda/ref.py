@@ -50,14 +50,19 @@ def build_bvh(pos, nrm, idx, iterations=1, fmad=False):
              "triangles": z(B * 1024 * 128), "aabbs": z(B * 1024 * 24), "morton": z(B * 1024 * 4), "reorderIdx": z(B * 1024 * 4),
              "nodes": z(B * 1024 * 64), "tlasAabbs": z(1024 * 24), "tlasMorton": z(1024 * 4), "tlasReorderIdx": z(1024 * 4), "tlasNodes": z(1024 * 64)}
     p = lambda k: C.c_void_p(r.dev[k].data_ptr())
-    ms = C.c_float()
-    torch.cuda.synchronize()
-    rc = lib.refcuda_build_bvh(p("pos"), p("idx"), p("nrm"), C.c_uint(N), p("triangles"), p("aabbs"), p("morton"), p("reorderIdx"), p("nodes"),
-                               p("tlasAabbs"), p("tlasMorton"), p("tlasReorderIdx"), p("tlasNodes"), p("triCount"), p("batchCount"),
-                               C.c_int(iterations), C.byref(ms))
-    if rc:
-        raise RuntimeError(f"refcuda_build_bvh failed: {rc}")
-    r.ms = ms.value
+
+    def run(iters):
+        """one timed pass of the kernel sequence over the same device arrays: mean ms of `iters` builds (the first of several is warm-up)"""
+        ms = C.c_float()
+        torch.cuda.synchronize()
+        rc = lib.refcuda_build_bvh(p("pos"), p("idx"), p("nrm"), C.c_uint(N), p("triangles"), p("aabbs"), p("morton"), p("reorderIdx"), p("nodes"),
+                                   p("tlasAabbs"), p("tlasMorton"), p("tlasReorderIdx"), p("tlasNodes"), p("triCount"), p("batchCount"),
+                                   C.c_int(iters), C.byref(ms))
+        if rc:
+            raise RuntimeError(f"refcuda_build_bvh failed: {rc}")
+        return ms.value
+    r.rebuild = run
+    r.ms = run(iterations)
     return r
 
 

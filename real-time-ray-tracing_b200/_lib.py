@@ -23,6 +23,7 @@ BUF_RENDER_COLOR, BUF_NORMAL, BUF_ALBEDO, BUF_DEPTH, BUF_MOTION_VECTOR, BUF_ACCU
 BUF_OUTPUT_RGBA8, BUF_COLOR64, BUF_EXPOSURE, BUF_HISTOGRAM = range(47, 51)
 BUF_WF_COUNTERS = 100
 BUF_WIDE_NODES, BUF_WIDE_TRIS, BUF_WIDE_STAT = 101, 102, 103
+MULTI_ROWS, MULTI_SAMPLES = 0, 1
 
 
 class Config(C.Structure):
@@ -73,6 +74,11 @@ class PostprocessParams(C.Structure):   # src/settingParams.h:92-99, 112-116
                 ("enableToneMapping", C.c_int32)]
 
 
+class MicrobenchResult(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("l2_read_gbs", "l1_latency_ns", "l2_latency_ns", "dram_latency_ns",
+                                         "l1_latency_cycles", "l2_latency_cycles", "dram_latency_cycles", "reserved_")]
+
+
 # every symbol include/rtrt.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "rtrt_abi_version": (C.c_int, []),
@@ -101,6 +107,18 @@ SYMBOLS = {
     "rtrt_read_buffer_async": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "rtrt_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "rtrt_get_stream": (C.c_void_p, [C.c_void_p]),
+    "rtrt_microbench": (C.c_int, [C.c_void_p, C.POINTER(MicrobenchResult)]),
+    "rtrt_multi_unique_id": (C.c_int, [C.c_void_p]),
+    "rtrt_create_multi": (C.c_int, [C.POINTER(Config), C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "rtrt_multi_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "rtrt_multi_attach_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "rtrt_multi_link_local": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
+    "rtrt_multi_set_mode": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "rtrt_update_vertices_multi": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
+    "rtrt_render_frame_multi": (C.c_int, [C.c_void_p]),
+    "rtrt_render_progressive_multi": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "rtrt_multi_get_band": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "rtrt_multi_plan_rows": (C.c_int, [C.c_int32] * 7 + [C.c_void_p, C.c_int32]),
     "rtrt_set_camera": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
     "rtrt_load_camera_file": (C.c_int, [C.c_void_p, C.c_char_p]),
     "rtrt_save_camera_file": (C.c_int, [C.c_void_p, C.c_char_p]),

@@ -321,6 +321,12 @@ class RayTracer:
         self._check(self._lib.rtrt_get_timings(self._h, C.byref(t)))
         return {k: (list(getattr(t, k)) if hasattr(getattr(t, k), "__len__") else getattr(t, k)) for k, _ in L.Timings._fields_ if k != "reserved_"}
 
+    def microbench(self):
+        """rtrt_microbench: measured L2 read bandwidth and L1 / L2 / DRAM dependent-load latencies of this GPU."""
+        r = L.MicrobenchResult()
+        self._check(self._lib.rtrt_microbench(self._h, C.byref(r)))
+        return {k: getattr(r, k) for k, _ in L.MicrobenchResult._fields_ if k != "reserved_"}
+
     @property
     def stream(self):
         return self._lib.rtrt_get_stream(self._h)

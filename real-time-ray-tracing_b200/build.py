@@ -12,7 +12,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "librtrt.so")
+OUT = os.environ.get("RTRT_BUILD_OUT") or os.path.join(HERE, "librtrt.so")      # RTRT_BUILD_OUT: A/B variants (experiments), with their own object directory
+OBJDIR = os.path.join(HERE, "build" + ("_" + os.path.basename(OUT) if os.environ.get("RTRT_BUILD_OUT") else ""))
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -59,9 +60,9 @@ def build(force=False, verbose=True):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     objs = []
     procs = []
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    os.makedirs(OBJDIR, exist_ok=True)
     for src in sources():
-        obj = os.path.join(HERE, "build", os.path.basename(src) + ".o")
+        obj = os.path.join(OBJDIR, os.path.basename(src) + ".o")
         objs.append(obj)
         cmd = [nvcc] + flags_for(src) + ["-x", "cu" if src.endswith(".cu") else "c++", "-c", src, "-o", obj]
         if verbose:

@@ -157,6 +157,7 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     cudaStreamSynchronize(c.stream);
     if (c.copyStream) cudaStreamSynchronize(c.copyStream);
     if (c.uploadStream) cudaStreamSynchronize(c.uploadStream);
+    multi_release(c);
     free_mesh(c);
     free_frame_resources(c);
     dfree(c.dStage);
@@ -270,7 +271,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 64) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..64"); c.stackSize = (int)value; return RTRT_OK; }
     if (!strcmp(name, "assume_bvh_valid")) { c.bvhValid = value != 0; c.wideValid = false; return RTRT_OK; }
-    if (!strcmp(name, "wide_bvh")) { c.wideBvh = value != 0; return RTRT_OK; }
+    if (!strcmp(name, "wide_bvh")) { if (value < 0 || value > 2) return c.fail(RTRT_ERR_ARG, "wide_bvh must be 0, 1 or 2"); c.wideBvh = value != 0; c.widePrimary = value != 2; return RTRT_OK; }
     if (!strcmp(name, "morton_bits")) { if (value != 60 && value != 63) return c.fail(RTRT_ERR_ARG, "morton_bits must be 60 or 63"); c.mortonBits = (int)value; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }

@@ -39,6 +39,7 @@ struct Context {
     bool bvhValid = false;
     // ---- wide traversal layout (option wide_bvh; wide_build.cu) ----
     bool wideBvh = false, wideValid = false, wideStatPending = false;
+    bool widePrimary = true;                              // option wide_bvh = 2: primary rays keep the reference layout (coherent rays: its two-child nodes hit L1), bounce rays the wide one
     void* dWideNodes = nullptr; void* dWideTris = nullptr; void* dWideQueue = nullptr; size_t wideNodeCap = 0;
     uint32_t wideRoot = 0, wideNodes = 0;
     uint32_t tlasSpinLimit = 1u << 22;                    // option "tlas_spin_limit" (test knob: 0 forces the time-out path)
@@ -96,6 +97,12 @@ struct Context {
     bool geomPending = false, geomFreeValid = false, readPending = false;
     void* dStage = nullptr; size_t stageBytes = 0;       // device staging copy of the buffer being read back
 
+    // ---- multi-GPU (multi.cu): the group this context is a rank of, and the denoiser's halo hook ----
+    void* multi = nullptr;                               // rtrt::Multi
+    int bandHaloRows = -1;                               // rows around the band that rtrt_denoise recomputes: -1 = the full dependency halo (80 / 112 rows,
+                                                         // nothing is exchanged between passes), 0 = none (the halo rows are exchanged: haloFn)
+    int (*haloFn)(Context&, void* colour, int rows) = nullptr;   // called before every pass that reads `rows` neighbouring rows of `colour`
+
     // ---- bookkeeping ----
     unsigned long long launches = 0;                     // kernels launched by this library
     cudaEvent_t ev[4][2] = {};                           // [build, traverse, pathtrace, denoise][begin, end]
@@ -136,6 +143,7 @@ int launch_pathtrace(Context& c);
 int launch_denoise(Context& c);
 int launch_accumulate(Context& c, int reset);
 int launch_postprocess(Context& c, float deltaTimeMs);   // postprocess.cu
+void multi_release(Context& c);             // multi.cu: leaves the multi-GPU group (rtrt_destroy)
 int local_rows(const Context& c);            // rows of the frame this context path-traces (band or strips)
 int ensure_frame_resources(Context& c);      // frame.cu: G-buffers, tables, default materials/textures, sky regeneration
 void free_frame_resources(Context& c);

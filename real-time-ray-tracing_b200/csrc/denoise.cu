@@ -527,9 +527,14 @@ int launch_denoise(Context& c) {
     // its own gate 15, TemporalFilter 1  => 77 rows; kBandHalo = 80 = five block rows.  Every pass covers the same block rows:
     // what the outer halo rows compute from rows outside is garbage by construction and never reaches the band.
     // The caller must have made ALL rows of the G-buffers and history valid first (all-gather of the bands).
-    constexpr int kBandHalo = 80;
-    const int blocksY = (c.height + 15) / 16;
+    // With the 5-iteration schedule (enableWideSpatialFilter == 2: strides 1, 2, 4, 8, 16) the dilated passes reach 62 rows instead of 42
+    // => 97 rows; the halo is then seven block rows.
+    const bool sched5 = ps.enableWideSpatialFilter == 2;
     const bool band = c.rowBegin > 0 || c.rowEnd < c.height;
+    const int kBandHalo = c.bandHaloRows >= 0 ? c.bandHaloRows : (sched5 ? 112 : 80);     // 0 with the multi-GPU halo exchange (multi.cu)
+    // halo exchange: before a pass that reads `rows` rows beyond the band, the multi-GPU driver fetches them from the neighbouring bands
+    auto halo = [&](ushort4* img, int rows) -> int { return (c.haloFn && band) ? c.haloFn(c, img, rows) : RTRT_OK; };
+    const int blocksY = (c.height + 15) / 16;
     const int by0 = band ? (c.rowBegin - kBandHalo < 0 ? 0 : (c.rowBegin - kBandHalo) / 16) : 0;
     const int by1 = band ? (c.rowEnd + kBandHalo + 15) / 16 < blocksY ? (c.rowEnd + kBandHalo + 15) / 16 : blocksY : blocksY;
     P.by0 = by0;
@@ -542,7 +547,8 @@ int launch_denoise(Context& c) {
 
     {
         // guide rows: the filtered block rows + the 24-row reach of the widest dilated pass
-        const int g0 = by0 * 16 - 24 < 0 ? 0 : by0 * 16 - 24, g1 = by1 * 16 + 24 > c.height ? c.height : by1 * 16 + 24;
+        const int gr = sched5 ? 32 : 24;
+        const int g0 = by0 * 16 - gr < 0 ? 0 : by0 * 16 - gr, g1 = by1 * 16 + gr > c.height ? c.height : by1 * 16 + gr;
         const size_t first = (size_t)g0 * c.width, n = (size_t)(g1 - g0) * c.width;
         k_dn_pack_guide<<<(unsigned)((n + 255) / 256), 256, 0, c.stream>>>(P.normal, P.depth, reinterpret_cast<ushort4*>(c.dGuide), first, n);
         c.launches++;
@@ -551,21 +557,44 @@ int launch_denoise(Context& c) {
     if (temporal && notFirst) { k_dn_temporal<true><<<grid, block, 0, c.stream>>>(P, cur, accum, oth); swap(); c.launches++; }
     else if (local) { k_dn_temporal<false><<<grid, block, 0, c.stream>>>(P, cur, accum, oth); c.launches++; }
     // SpatialFilter7x7 (:90-98) + CopyToHistoryColorBuffer (:100-106) [+ noise level for the wide passes, :110-118]
-    if (local) { k_dn_spatial7<true><<<grid, block, 0, c.stream>>>(P, cur, oth, temporal ? accum : nullptr, n16, wide ? 1 : 0); swap(); c.launches++; }
+    if (local) {
+        { int rc = halo(cur, 3); if (rc) return rc; }
+        k_dn_spatial7<true><<<grid, block, 0, c.stream>>>(P, cur, oth, temporal ? accum : nullptr, n16, wide ? 1 : 0); swap(); c.launches++;
+    }
     else if (temporal || wide) { k_dn_spatial7<false><<<grid, block, 0, c.stream>>>(P, cur, oth, temporal ? accum : nullptr, n16, wide ? 1 : 0); c.launches++; }
     // SpatialFilterGlobal5x5<3|6|12> (:132-157)
-    if (wide) {
+    if (wide && sched5) {                                     // BASELINE config 4: five a-trous iterations, strides 1, 2, 4, 8, 16
+        { int rc = halo(cur, 2); if (rc) return rc; }
+        k_dn_spatial5<1><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        { int rc = halo(cur, 4); if (rc) return rc; }
+        k_dn_spatial5<2><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        { int rc = halo(cur, 8); if (rc) return rc; }
+        k_dn_spatial5<4><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        { int rc = halo(cur, 16); if (rc) return rc; }
+        k_dn_spatial5<8><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        { int rc = halo(cur, 32); if (rc) return rc; }
+        k_dn_spatial5<16><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        c.launches += 5;
+    } else if (wide) {
+        { int rc = halo(cur, 6); if (rc) return rc; }
         k_dn_spatial5<3><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        { int rc = halo(cur, 12); if (rc) return rc; }
         k_dn_spatial5<6><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
+        { int rc = halo(cur, 24); if (rc) return rc; }
         k_dn_spatial5<12><<<grid, block, 0, c.stream>>>(P, cur, oth, n16); swap();
         c.launches += 3;
     }
     // ApplyAlbedo (:160-163) + TemporalFilter2 (:165-179) + CopyToHistoryColorDepthBuffer (:180-186)
     ushort4* histPrev = reinterpret_cast<ushort4*>(c.dHistoryColor); ushort4* histNext = reinterpret_cast<ushort4*>(c.dHistoryAlbedo);
-    if (tf2 && notFirst) k_dn_final<true><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, histNext, reinterpret_cast<__half*>(c.dHistoryDepth));
+    if (tf2 && notFirst) {
+        { int rc = halo(cur, 1); if (rc) return rc; }
+        k_dn_final<true><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, histNext, reinterpret_cast<__half*>(c.dHistoryDepth));
+    }
     else k_dn_final<false><<<grid, block, 0, c.stream>>>(P, cur, oth, histPrev, tf2 ? histNext : nullptr, reinterpret_cast<__half*>(c.dHistoryDepth));
     swap(); c.launches++;
-    if (band && tf2) RTRT_CUDA(c, cudaMemcpyAsync(c.dHistoryDepth, c.dDepth, (size_t)c.width * c.height * sizeof(__half), cudaMemcpyDeviceToDevice, c.stream));
+    // band mode with all-gathered G-buffers: the history depth of the rows outside the band (k_dn_final stores the band's).  With the halo exchange the
+    // depth is only valid around the band and RTRT_BUF_HISTORY_DEPTH (an observation point: no kernel reads it) stays band-local.
+    if (band && tf2 && !c.haloFn) RTRT_CUDA(c, cudaMemcpyAsync(c.dHistoryDepth, c.dDepth, (size_t)c.width * c.height * sizeof(__half), cudaMemcpyDeviceToDevice, c.stream));
     if (temporal) { c.accumW = c.width; c.accumH = c.height; }
     if (tf2) { c.histW = c.width; c.histH = c.height; }
     if (tf2) { void* t = c.dHistoryColor; c.dHistoryColor = c.dHistoryAlbedo; c.dHistoryAlbedo = t; }       // history ping-pong

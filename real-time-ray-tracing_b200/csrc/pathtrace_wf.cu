@@ -187,16 +187,25 @@ __global__ void __launch_bounds__(kPtThreads, RTRT_PRIMARY_MINB) k_pt_primary(co
     const int ix = blockIdx.x * kPtBlockX + threadIdx.x;
     const int jc = blockIdx.y * kPtBlockY + threadIdx.y, jy = chunk_row(P, jc), iy = frame_row(P, jy);
     uint32_t nodeVisits = 0, leafTests = 0;
-    if (ix < P.width && jc < P.chunkRows && jy < P.localRows) {
+    {
+        const bool inside = ix < P.width && jc < P.chunkRows && jy < P.localRows;
         Trav tr;
-        tr.setup(P.sc, sRaw, tid, kPtThreads);
-        const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
-        Float3 orig, dir, centerDir; Float2 sampleUv;
-        generate_ray(orig, dir, centerDir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
-        tr.begin(P.sc, orig, dir);
-        while (!tr.template step<COUNT>(P.sc, 0)) {}
-        if (COUNT) { nodeVisits = tr.nodeVisits(); leafTests = tr.leafTests(); }
-        B.hit[(size_t)iy * P.width + ix] = make_float4(tr.t(), tr.ua(), tr.va(), __int_as_float(tr.tri()));
+        uint2 spill[Trav::kSpill];
+        tr.setup(P.sc, sRaw, tid, kPtThreads, spill);
+        if (inside) {
+            const Float4 rnd0 = blue_rand4(P, ix, iy, 0);
+            Float3 orig, dir, centerDir; Float2 sampleUv;
+            generate_ray(orig, dir, centerDir, sampleUv, P.camera, ix, iy, Float2{rnd0.x, rnd0.y}, Float2{rnd0.z, rnd0.w});
+            tr.begin(P.sc, orig, dir);
+        }
+        bool active = inside;                                     // every lane of the warp steps together (the wide layout votes inside)
+        while (__any_sync(0xffffffffu, active)) {
+            if (tr.template step_warp<COUNT>(P.sc, 0, active)) active = false;
+        }
+        if (inside) {
+            if (COUNT) { nodeVisits = tr.nodeVisits(); leafTests = tr.leafTests(); }
+            B.hit[(size_t)iy * P.width + ix] = make_float4(tr.t(), tr.ua(), tr.va(), __int_as_float(tr.tri()));
+        }
     }
     if (COUNT && P.rayCounter) {
         for (int o = 16; o > 0; o >>= 1) { nodeVisits += __shfl_xor_sync(0xffffffffu, nodeVisits, o); leafTests += __shfl_xor_sync(0xffffffffu, leafTests, o); }
@@ -227,8 +236,9 @@ __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(con
     uint32_t pix = 0;
     int anyHit = 0;
     Trav tr;
+    uint2 spill[Trav::kSpill];
     uint32_t nodeVisits = 0, leafTests = 0;
-    tr.setup(sc, sRaw, tid, kTraceThreads);
+    tr.setup(sc, sRaw, tid, kTraceThreads, spill);
     while (true) {
         // ---- refill idle lanes from the queue ----
         const unsigned idle = __ballot_sync(0xffffffffu, !active) & laneMask;
@@ -253,8 +263,8 @@ __global__ void __launch_bounds__(kTraceThreads, RTRT_TRACE_MINB) k_pt_trace(con
         // ---- traverse until enough lanes have finished to make a refill worthwhile ----
         while (true) {
             bool finishedNow = false;
-            if (active) {
-                if (tr.template step<COUNT>(sc, anyHit)) {
+            {
+                if (tr.template step_warp<COUNT>(sc, anyHit, active)) {
                     B.hit[pix] = make_float4(tr.t(), tr.ua(), tr.va(), __int_as_float(tr.tri()));
                     if (COUNT) {
                         nodeVisits += tr.nodeVisits(); leafTests += tr.leafTests();
@@ -405,7 +415,7 @@ static void launch_chunk(Context& c, const PathTraceParams& P, const WfBuffers& 
         cudaEventRecord(c.kev[0], st);
     }
     const bool wide = c.wideBvh;
-    if (wide) { if (c.countVisits) k_pt_primary<true, WideTrav><<<grid, block, 0, st>>>(P, B); else k_pt_primary<false, WideTrav><<<grid, block, 0, st>>>(P, B); }
+    if (wide && c.widePrimary) { if (c.countVisits) k_pt_primary<true, WideTrav><<<grid, block, 0, st>>>(P, B); else k_pt_primary<false, WideTrav><<<grid, block, 0, st>>>(P, B); }
     else      { if (c.countVisits) k_pt_primary<true, ParityTrav><<<grid, block, 0, st>>>(P, B); else k_pt_primary<false, ParityTrav><<<grid, block, 0, st>>>(P, B); }
     if (kt) cudaEventRecord(c.kev[1], st);
     const int tiles = ((c.width + 7) / 8) * ((rows + 3) / 4);

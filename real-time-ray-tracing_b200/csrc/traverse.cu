@@ -57,13 +57,19 @@ __global__ void __launch_bounds__(kTravThreads) k_traverse_wide(SceneView sc, co
                                                                 Hit* __restrict__ hits, int anyHit, unsigned long long* counters) {
     __shared__ uint2 sRaw[16 * kTravThreads];
     const uint32_t i = blockIdx.x * kTravThreads + threadIdx.x;
-    if (i >= n) return;
     WideTrav tr;
-    tr.setup(sc, sRaw, threadIdx.x, kTravThreads);
-    const float4* r4 = reinterpret_cast<const float4*>(rays + i);
-    const float4 o = __ldg(r4), d = __ldg(r4 + 1);
-    tr.begin(sc, Float3{o.x, o.y, o.z}, Float3{d.x, d.y, d.z});
-    while (!tr.template step<COUNT>(sc, anyHit)) {}
+    uint2 spill[WideTrav::kSpill];
+    tr.setup(sc, sRaw, threadIdx.x, kTravThreads, spill);
+    bool active = i < n;                                           // whole warps step together (wide_step votes)
+    if (active) {
+        const float4* r4 = reinterpret_cast<const float4*>(rays + i);
+        const float4 o = __ldg(r4), d = __ldg(r4 + 1);
+        tr.begin(sc, Float3{o.x, o.y, o.z}, Float3{d.x, d.y, d.z});
+    }
+    while (__any_sync(0xffffffffu, active)) {
+        if (tr.template step_warp<COUNT>(sc, anyHit, active)) active = false;
+    }
+    if (i >= n) return;
     reinterpret_cast<float4*>(hits)[i] = make_float4(tr.t(), tr.u(), tr.v(), __int_as_float(tr.tri()));
     if (COUNT) {
         atomicAdd(counters, (unsigned long long)tr.nodeVisits()); atomicAdd(counters + 1, (unsigned long long)tr.leafTests());

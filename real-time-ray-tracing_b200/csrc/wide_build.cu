@@ -10,6 +10,7 @@
 // Nodes are allocated breadth-first from a per-batch region (inner children of a node are consecutive), triangles are copied
 // (positions only, original index in row0.w) in the order the leaves were allocated, so a node's leaf triangles are consecutive too.
 #include "wide_bvh.cuh"
+#include <cuda_fp16.h>
 #include "context.h"
 
 namespace rtrt {
@@ -67,11 +68,10 @@ __device__ __forceinline__ void load_rec(const float4* __restrict__ binNodes, ui
     rec[0] = __ldcg(r); rec[1] = __ldcg(r + 1); rec[2] = __ldcg(r + 2); rec[3] = __ldcg(r + 3);     // written by the build just before: L2
 }
 
-__device__ __forceinline__ uint32_t exp_byte(float extent) {          // smallest e with 255 * 2^(e-127) >= extent
-    const float s = extent * (1.0f / 255.0f) * 1.0000005f;             // rounded up a little: the bound below must hold in exact arithmetic
-    uint32_t e = ((__float_as_uint(s) + 0x007FFFFFu) >> 23) & 0xFFu;
-    if (255.0f * __uint_as_float(e << 23) < extent) ++e;
-    return e < 1u ? 1u : (e > 254u ? 254u : e);
+__device__ __forceinline__ uint32_t exp_byte(float extent) {          // smallest e with 2^(e-127) >= extent
+    const uint32_t b = __float_as_uint(extent);
+    uint32_t e = ((b >> 23) & 0xFFu) + ((b & 0x007FFFFFu) ? 1u : 0u);
+    return e < 1u ? 1u : (e > 253u ? 253u : e);
 }
 
 // One wide node per 8-lane group.  Every lane of the warp runs this (valid = the group has an entry), shuffles use the full mask.
@@ -89,7 +89,7 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
     float4* outNode = p.nodes + (size_t)(regionBase + w) * kWideStride;
     if (TLAS && valid && (e.link & kCopyFlag)) {           // top-level leaf: the node is the batch's wide root, children / triangles stay where they are
         const float4* src = p.nodes + (size_t)((e.link & ~kCopyFlag) * (uint32_t)kWideRegion) * kWideStride;
-        if (g < 5) outNode[g] = __ldcg(src + g);
+        outNode[g] = __ldcg(src + g);
         valid = false;
     }
     Slot s; s.kind = K_EMPTY; s.idx = 0; s.f = 0; s.l = 0;
@@ -183,24 +183,26 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
         queue[childBase + __popc(imask & ((1u << g) - 1u))] = q;
     }
     if (!TLAS && cnt) for (uint32_t k = 0; k < cnt; ++k) triSrc[triBase + triOff + k] = (uint16_t)(c.f + k);
-    // ---- quantise the child box to the node's grid (conservative in exact arithmetic: evaluated in double) and write the node ----
+    // ---- child planes relative to the node origin in units of the per-axis scale, as fp16: lo rounded down, hi rounded up (the difference
+    // and the power-of-two scaling are evaluated in double; both roundings go the conservative way) ----
     const uint32_t ex = exp_byte(e.hi[0] - e.lo[0]), ey = exp_byte(e.hi[1] - e.lo[1]), ez = exp_byte(e.hi[2] - e.lo[2]);
     const uint32_t eb[3] = {ex, ey, ez};
     uint8_t* ob = reinterpret_cast<uint8_t*>(outNode);
+    __half* oh = reinterpret_cast<__half*>(outNode);
     uint32_t meta = 0u;
     if (inner) meta = 0x20u | (24u + (uint32_t)g);
     else if (cnt) meta = (((1u << cnt) - 1u) << 5) | triOff;
     ob[24 + g] = (uint8_t)meta;
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
-        uint32_t qlo = 0u, qhi = 0u;
+        __half hlo = __float2half_rd(0.0f), hhi = hlo;
         if (c.kind != K_EMPTY) {
             const double inv = (double)__uint_as_float((254u - eb[a]) << 23);           // 2^(127 - e), exact
-            const double dlo = floor(((double)c.lo[a] - (double)e.lo[a]) * inv), dhi = ceil(((double)c.hi[a] - (double)e.lo[a]) * inv);
-            qlo = (uint32_t)fmin(fmax(dlo, 0.0), 255.0); qhi = (uint32_t)fmin(fmax(dhi, 0.0), 255.0);
+            const double dlo = fmin(fmax(((double)c.lo[a] - (double)e.lo[a]) * inv, 0.0), 1.0), dhi = fmin(fmax(((double)c.hi[a] - (double)e.lo[a]) * inv, 0.0), 1.0);
+            hlo = __float2half_rd(__double2float_rd(dlo)); hhi = __float2half_ru(__double2float_ru(dhi));
         }
-        ob[32 + 8 * a + g] = (uint8_t)qlo;
-        ob[56 + 8 * a + g] = (uint8_t)qhi;
+        oh[16 + 8 * a + g] = hlo;                                                        // rows 2..4
+        oh[40 + 8 * a + g] = hhi;                                                        // rows 5..7
     }
     if (g == 0) {
         outNode[0] = make_float4(e.lo[0], e.lo[1], e.lo[2], __uint_as_float(ex | (ey << 8) | (ez << 16) | (imask << 24)));

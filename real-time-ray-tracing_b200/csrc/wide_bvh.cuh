@@ -1,4 +1,4 @@
-// "Fast" traversal layout (option wide_bvh): an 8-wide BVH with child boxes quantised to 8 bits inside the parent box and
+// "Fast" traversal layout (option wide_bvh): an 8-wide BVH with fp16 child boxes relative to the parent box and
 // 48-byte position-only triangles, derived on the device from the reference-layout (parity) arrays after every build.
 //
 // Why: B200 has no RT cores.  The reference's layout (src/bvhNode.cuh:5-13: 64-byte two-child nodes, src/geometry.h:52-97: 128-byte
@@ -7,15 +7,18 @@
 // An 8-wide node answers three binary levels with ONE cache line, leaves hold up to 3 triangles, and the whole node array of the bench
 // scene is ~9 MB (vs 64 MB), i.e. it lives in L2.
 //
-// Layout (node = 128-byte stride, first 80 bytes used — one L1/L2 line per visit; after Ylitie, Karras, Laine 2017,
-// "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs"):
+// Layout (node = 128 bytes = one L1/L2 line per visit; the slot / octant scheme follows Ylitie, Karras, Laine 2017, "Efficient
+// Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs"):
 //   row 0   float px, py, pz      origin = min corner of the node box
-//           u8 ex, ey, ez         IEEE exponent bytes of the per-axis grid step (step = 2^(e-127), 255 steps >= extent)
+//           u8 ex, ey, ez         IEEE exponent bytes of the per-axis scale 2^(e-127) >= extent (child planes are stored in units of it)
 //           u8 imask              bit s = child slot s is an inner node
 //   row 1   u32 childBase         index of the first inner child; inner children are consecutive in slot order
 //           u32 triBase           index (in triangles) of the node's first leaf triangle in the wide triangle array
 //           u8 meta[8]            per slot: 0 empty | inner: 0x20 | (24 + s) | leaf of k <= 3 triangles: (2^k - 1) << 5 | first triangle (0..23)
-//   row 2-4 u8 qlo[3][8], qhi[3][8]   child boxes in grid steps: rows are {lox, loy}, {loz, hix}, {hiy, hiz}, 8 bytes each
+//   row 2-7 half lox[8], loy[8], loz[8], hix[8], hiy[8], hiz[8]   child boxes relative to the origin in units of the scale, in [0, 1]:
+//           fp16, lo planes rounded down, hi planes rounded up.  Round 2 first used 8-bit grid coordinates (Ylitie et al.): decoding 48 bytes
+//           per visit (PRMT / I2F) kept the ALU pipe 57 % busy and bound the kernel (profiles/r2d); a half converts to float on the FMA pipe
+//           (HADD2.F32 with a half selector, no extraction), the grid is 8x finer, and the node still is one cache line.
 // Slots are assigned so that (slot ^ octant) approximates front-to-back order for every ray octant (no per-visit sort, no
 // distances on the stack).  Triangle = 3 x float4 {v.xyz, w}: row0.w carries the ORIGINAL triangle index (batch * 1024 + local id),
 // so hit records, normals and materials keep using the reference-layout arrays.
@@ -27,6 +30,7 @@
 // wins in both, the visiting order differs).  tests/test_wide_bvh_gpu.py counts all three classes.
 #pragma once
 #include "traverse.cuh"
+#include <cuda_fp16.h>
 
 namespace rtrt {
 
@@ -41,6 +45,7 @@ struct WideRay {
     float idx, idy, idz;                         // 1 / dir (safe_divide, src/traverse.cuh:88)
     float aox, aoy, aoz;                         // |org| * |1/dir| * 2^-20: absolute-coordinate part of the box-test margin
     uint32_t octinv4;                            // (7 - octant) replicated into 4 bytes
+    int rnx, rny, rnz;                           // node row of the NEAR plane per axis: lo row (2, 3, 4) for a non-negative reciprocal, else hi row (5, 6, 7)
     int kz; float Sx, Sy, Sz;                    // watertight test constants (RayPrep subset)
 };
 
@@ -60,6 +65,7 @@ __device__ __forceinline__ WideRay wide_prepare_ray(const Float3& org, const Flo
     w.aox = fabsf(org.x) * fabsf(w.idx) * m; w.aoy = fabsf(org.y) * fabsf(w.idy) * m; w.aoz = fabsf(org.z) * fabsf(w.idz) * m;
     const uint32_t oct = (dir.x < 0.0f ? 4u : 0u) | (dir.y < 0.0f ? 2u : 0u) | (dir.z < 0.0f ? 1u : 0u);
     w.octinv4 = (7u - oct) * 0x01010101u;
+    w.rnx = w.idx >= 0.0f ? 2 : 5; w.rny = w.idy >= 0.0f ? 3 : 6; w.rnz = w.idz >= 0.0f ? 4 : 7;
     int kz = max_dim3(fabsf(dir.x), fabsf(dir.y), fabsf(dir.z));
     int kx = kz + 1; if (kx == 3) kx = 0;
     int ky = kx + 1; if (ky == 3) ky = 0;
@@ -90,27 +96,34 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {   // 0x80 in 
     asm("prmt.b32 %0, %1, 0, 0xba98;" : "=r"(r) : "r"(x));            // replicate-sign mode
     return r;
 }
-__device__ __forceinline__ float byte_to_float(uint32_t v, int i) {   // byte i of v as float (exact)
-    return (float)((v >> (8 * i)) & 0xFFu);
+// child planes: 8 halves per 16-byte row; half I of the row as float (one HADD2.F32 on the FMA pipe, the half is selected in the instruction)
+template <int I>
+__device__ __forceinline__ float row_half(const uint4& r) {
+    const uint32_t wd = (I >> 1) == 0 ? r.x : ((I >> 1) == 1 ? r.y : ((I >> 1) == 2 ? r.z : r.w));
+    const __half2 h = *reinterpret_cast<const __half2*>(&wd);
+    return (I & 1) ? __high2float(h) : __low2float(h);
 }
 
-// Box tests of the four children whose quantised planes are in (lox, loy, loz, hix, hiy, hiz): each word holds one plane byte per child.
-// t = q * a + b per plane (one FMA; a = step / dir, b = (origin - ray origin) / dir), near planes biased by -delta, far planes by +delta.
-__device__ __forceinline__ uint32_t wide_test4(uint32_t meta4, uint32_t octinv4, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz,
-                                               float ax, float ay, float az, float bnx, float bny, float bnz, float bfx, float bfy, float bfz, float tmax) {
+// Box tests of the four children LO..LO+3 (meta4 = their meta bytes): t = l A + b per plane, l = the stored plane in [0, 1], A = scale / dir,
+// b = (origin - ray origin) / dir; near planes carry -delta, far planes +delta (wide_step).
+template <int LO>
+__device__ __forceinline__ uint32_t wide_test4(uint32_t meta4, uint32_t octinv4, const uint4& nx, const uint4& ny, const uint4& nz, const uint4& fx, const uint4& fy,
+                                               const uint4& fz, float Ax, float Ay, float Az, float cnx, float cny, float cnz, float cfx, float cfy, float cfz, float tmax) {
     const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
     const uint32_t innerMask4 = sign_extend_s8x4(isInner4 << 3);
     const uint32_t bitIndex4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1F1F1F1Fu;
     const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
     uint32_t hit = 0u;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float tnx = fmaf(byte_to_float(nx, i), ax, bnx), tny = fmaf(byte_to_float(ny, i), ay, bny), tnz = fmaf(byte_to_float(nz, i), az, bnz);
-        const float tfx = fmaf(byte_to_float(fx, i), ax, bfx), tfy = fmaf(byte_to_float(fy, i), ay, bfy), tfz = fmaf(byte_to_float(fz, i), az, bfz);
-        const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-        const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-        if (cmin <= cmax) hit |= ((childBits4 >> (8 * i)) & 0xFFu) << ((bitIndex4 >> (8 * i)) & 0xFFu);
+#define RTRT_WIDE_CHILD(I)                                                                                                                              \
+    {                                                                                                                                                   \
+        const float tnx = fmaf(row_half<LO + I>(nx), Ax, cnx), tny = fmaf(row_half<LO + I>(ny), Ay, cny), tnz = fmaf(row_half<LO + I>(nz), Az, cnz);   \
+        const float tfx = fmaf(row_half<LO + I>(fx), Ax, cfx), tfy = fmaf(row_half<LO + I>(fy), Ay, cfy), tfz = fmaf(row_half<LO + I>(fz), Az, cfz);   \
+        const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));                                                                                    \
+        const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                                                                    \
+        if (cmin <= cmax) hit |= ((childBits4 >> (8 * I)) & 0xFFu) << ((bitIndex4 >> (8 * I)) & 0xFFu);                                                 \
     }
+    RTRT_WIDE_CHILD(0) RTRT_WIDE_CHILD(1) RTRT_WIDE_CHILD(2) RTRT_WIDE_CHILD(3)
+#undef RTRT_WIDE_CHILD
     return hit;
 }
 
@@ -130,12 +143,39 @@ __device__ __forceinline__ uint2 wide_pop(const WideStack& st, WideState& s) {
     return s.sp < kWideStackSmem ? st.smem[s.sp * st.stride] : st.spill[s.sp - kWideStackSmem];
 }
 
-// One traversal step: visit ONE inner node (if the current group has any), test ALL triangles it reported, pop when the group is
-// used up.  Returns true when the ray is finished.
+// One traversal step of a whole warp (every lane calls it, `active` = the lane has a ray in flight):
+//   fetch      a lane whose node group is used up takes the next group off its stack;
+//   node       every lane with a pending inner child visits ONE node: 8 quantised box tests -> hit inner children + hit triangles;
+//   triangles  POSTPONED (Ylitie et al. 2017, section 5.2): the hit triangles of a node wait in the lane's pending group (an older
+//              pending group goes onto the stack) and are tested, one per lane and step, only when the warp votes that enough lanes
+//              have one pending (>= RTRT_WIDE_TRI_NUM / RTRT_WIDE_TRI_DEN of the lanes in flight), or when some lane has nothing else
+//              left to do.  The first cut tested all triangles of a node right after it: ~45 % of the kernel's issue slots ran the
+//              ~80-instruction triangle test with ~3 of 32 lanes (profiles/r2b: 15.6 lanes per instruction).
+// The closest hit does not depend on the test order (up to exact ties in t), so (tri, t, u, v) are unchanged.
+// Returns true when this lane's ray is finished.
+#ifndef RTRT_WIDE_TRI_NUM
+#define RTRT_WIDE_TRI_NUM 3
+#endif
+#ifndef RTRT_WIDE_TRI_DEN
+#define RTRT_WIDE_TRI_DEN 8
+#endif
+__device__ __forceinline__ uint2 wide_peek(const WideStack& st, const WideState& s) {
+    const int i = s.sp - 1;
+    return i < kWideStackSmem ? st.smem[i * st.stride] : st.spill[i - kWideStackSmem];
+}
+// stack entries: node group (hit mask of inner children in y[31:24]) or triangle group (y[31:24] == 0, hit triangles in y[23:0])
+__device__ __forceinline__ void wide_fetch(const WideStack& st, WideState& s) {
+    if (s.ngroup.y <= 0x00FFFFFFu && s.sp > 0) {
+        const uint2 e = wide_peek(st, s);
+        if (e.y > 0x00FFFFFFu) { s.ngroup = e; --s.sp; }                     // more nodes first; a pending triangle group keeps waiting
+        else if (s.tgroup.y == 0u) { s.tgroup = e; --s.sp; }
+    }
+}
+
 template <bool COUNT>
-__device__ __forceinline__ bool wide_step(const WideView& wv, const WideRay& w, WideState& s, int anyHit, const WideStack& st) {
-    {   // the current group always has a pending inner child here: it is the root group, or it was popped (groups are only pushed
-        // with children left), or the node visited in the previous step reported inner hits
+__device__ __forceinline__ bool wide_step(const WideView& wv, const WideRay& w, WideState& s, int anyHit, const WideStack& st, bool active) {
+    const unsigned full = 0xffffffffu;
+    if (active && s.ngroup.y > 0x00FFFFFFu) {
         const uint32_t hits = s.ngroup.y;
         const uint32_t bit = 31u - (uint32_t)__clz(hits);
         s.ngroup.y &= ~(1u << bit);
@@ -143,35 +183,44 @@ __device__ __forceinline__ bool wide_step(const WideView& wv, const WideRay& w, 
         const uint32_t slot = (bit - 24u) ^ (w.octinv4 & 0xFFu);
         const uint32_t rel = __popc(hits & ~(0xFFFFFFFFu << slot) & 0xFFu);
         const float4* nd = wv.nodes + (size_t)(s.ngroup.x + rel) * kWideStride;
-        const float4 n0 = __ldg(nd), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3), n4 = __ldg(nd + 4);
+        const uint4* nu = reinterpret_cast<const uint4*>(nd);
+        const float4 n0 = __ldg(nd), n1 = __ldg(nd + 1);
+        // near / far plane rows are picked by ADDRESS (per-ray constants), not by selects on the loaded data.  (Fetching the node as four
+        // 32-byte loads — LDG.E.256, sm_100 — halves the L1 tag look-ups, 113 M -> 64 M sectors per launch, but then the rows must be selected
+        // in registers: measured 0.926 -> 0.950 ms for the bounce round and 0.67 -> 0.75 ms for the primary rays, profiles/r2f; not kept.)
+        const uint4 nx = __ldg(nu + w.rnx), ny = __ldg(nu + w.rny), nz = __ldg(nu + w.rnz);
+        const uint4 fx = __ldg(nu + (7 - w.rnx)), fy = __ldg(nu + (9 - w.rny)), fz = __ldg(nu + (11 - w.rnz));
         if (COUNT) s.nodeVisits++;
         const uint32_t eim = __float_as_uint(n0.w);
-        const float ax = __uint_as_float((eim & 0xFFu) << 23) * w.idx;
-        const float ay = __uint_as_float(((eim >> 8) & 0xFFu) << 23) * w.idy;
-        const float az = __uint_as_float(((eim >> 16) & 0xFFu) << 23) * w.idz;
+        const float Ax = __uint_as_float((eim & 0xFFu) << 23) * w.idx;
+        const float Ay = __uint_as_float(((eim >> 8) & 0xFFu) << 23) * w.idy;
+        const float Az = __uint_as_float(((eim >> 16) & 0xFFu) << 23) * w.idz;
         const float bx = (n0.x - w.org.x) * w.idx, by = (n0.y - w.org.y) * w.idy, bz = (n0.z - w.org.z) * w.idz;
-        // error margin of t = q a + b against exact arithmetic on the stored planes (3 eps |b| + 2 eps |q a|, eps = 2^-24) and of the
-        // watertight test's own translation v - org (eps |coordinate| / |dir|): 2^-20 (|b| + 256 |a| + (|org| + |origin|) / |dir|)
+        // Error margin delta of t = l A + b against exact arithmetic on the stored planes (l exact, eps = 2^-24): A one rounding (eps |A|),
+        // b two roundings plus the cancellation in origin - org (2 eps |b| + eps (|org| + |origin|) / |dir|), the fma eps |t| <= eps (|A| + |b|),
+        // and the watertight test's own translation v - org (eps |coordinate| / |dir|): all below 2^-20 (|A| + |b| + (|org| + |origin|) / |dir|).
         const float m = 9.5367431640625e-07f;
-        const float dx = m * (fabsf(bx) + 256.0f * fabsf(ax) + fabsf(n0.x) * fabsf(w.idx)) + w.aox;
-        const float dy = m * (fabsf(by) + 256.0f * fabsf(ay) + fabsf(n0.y) * fabsf(w.idy)) + w.aoy;
-        const float dz = m * (fabsf(bz) + 256.0f * fabsf(az) + fabsf(n0.z) * fabsf(w.idz)) + w.aoz;
+        const float dx = m * (fabsf(bx) + fabsf(Ax) + fabsf(n0.x) * fabsf(w.idx)) + w.aox;
+        const float dy = m * (fabsf(by) + fabsf(Ay) + fabsf(n0.y) * fabsf(w.idy)) + w.aoy;
+        const float dz = m * (fabsf(bz) + fabsf(Az) + fabsf(n0.z) * fabsf(w.idz)) + w.aoz;
         const float bnx = bx - dx, bny = by - dy, bnz = bz - dz, bfx = bx + dx, bfy = by + dy, bfz = bz + dz;
-        // near plane of an axis = lo plane when the direction is positive, hi plane otherwise
-        const bool px = w.idx >= 0.0f, py = w.idy >= 0.0f, pz = w.idz >= 0.0f;
-        const uint32_t lox0 = __float_as_uint(n2.x), lox1 = __float_as_uint(n2.y), loy0 = __float_as_uint(n2.z), loy1 = __float_as_uint(n2.w);
-        const uint32_t loz0 = __float_as_uint(n3.x), loz1 = __float_as_uint(n3.y), hix0 = __float_as_uint(n3.z), hix1 = __float_as_uint(n3.w);
-        const uint32_t hiy0 = __float_as_uint(n4.x), hiy1 = __float_as_uint(n4.y), hiz0 = __float_as_uint(n4.z), hiz1 = __float_as_uint(n4.w);
-        uint32_t hitmask = wide_test4(__float_as_uint(n1.z), w.octinv4, px ? lox0 : hix0, py ? loy0 : hiy0, pz ? loz0 : hiz0,
-                                      px ? hix0 : lox0, py ? hiy0 : loy0, pz ? hiz0 : loz0, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, s.tSlack);
-        hitmask |= wide_test4(__float_as_uint(n1.w), w.octinv4, px ? lox1 : hix1, py ? loy1 : hiy1, pz ? loz1 : hiz1,
-                              px ? hix1 : lox1, py ? hiy1 : loy1, pz ? hiz1 : loz1, ax, ay, az, bnx, bny, bnz, bfx, bfy, bfz, s.tSlack);
+        uint32_t hitmask = wide_test4<0>(__float_as_uint(n1.z), w.octinv4, nx, ny, nz, fx, fy, fz, Ax, Ay, Az, bnx, bny, bnz, bfx, bfy, bfz, s.tSlack);
+        hitmask |= wide_test4<4>(__float_as_uint(n1.w), w.octinv4, nx, ny, nz, fx, fy, fz, Ax, Ay, Az, bnx, bny, bnz, bfx, bfy, bfz, s.tSlack);
         s.ngroup = make_uint2(__float_as_uint(n1.x), (hitmask & 0xFF000000u) | (eim >> 24));
-        s.tgroup = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
+        if (hitmask & 0x00FFFFFFu) {
+            if (s.tgroup.y != 0u) wide_push(st, s, s.tgroup);                 // the older pending group waits on the stack
+            s.tgroup = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
+        }
     }
-    if (s.tgroup.y != 0u) {
-        const RayPrep rp = wide_tri_prep(w);
-        do {
+    if (active) wide_fetch(st, s);
+    // ---- triangle phase, warp-voted ----
+    const bool want = active && s.tgroup.y != 0u;
+    const bool must = want && s.ngroup.y <= 0x00FFFFFFu;                      // (after the fetch) nothing but triangles left to do
+    const unsigned wm = __ballot_sync(full, want), mm = __ballot_sync(full, must), am = __ballot_sync(full, active);
+    bool finished = false;
+    if (wm != 0u && (mm != 0u || __popc(wm) * RTRT_WIDE_TRI_DEN >= __popc(am) * RTRT_WIDE_TRI_NUM)) {
+        if (want) {
+            const RayPrep rp = wide_tri_prep(w);
             const uint32_t bit = 31u - (uint32_t)__clz(s.tgroup.y);
             s.tgroup.y &= ~(1u << bit);
             const float4* row = wv.tris + (size_t)(s.tgroup.x + bit) * 3;
@@ -181,16 +230,14 @@ __device__ __forceinline__ bool wide_step(const WideView& wv, const WideRay& w, 
             if (ray_triangle(rp, q1, q2, q3, s.t, tt, uu, vv)) {
                 if (tt < s.t) {
                     s.t = tt; s.tSlack = tt * 1.000001f; s.tri = __float_as_int(q1.w); s.ua = uu; s.va = vv;
-                    if (anyHit) return true;
+                    if (anyHit) finished = true;
                 }
             }
-        } while (s.tgroup.y != 0u);
+            if (!finished) wide_fetch(st, s);
+        }
     }
-    if (s.ngroup.y <= 0x00FFFFFFu) {
-        if (s.sp == 0) return true;
-        s.ngroup = wide_pop(st, s);
-    }
-    return false;
+    if (active && s.ngroup.y <= 0x00FFFFFFu && s.tgroup.y == 0u && s.sp == 0) finished = true;
+    return finished;
 }
 
 // ---- one interface over both layouts, so the traversal kernels (k_traverse, k_pt_primary, k_pt_trace) exist once ----
@@ -200,7 +247,8 @@ struct ParityTrav {
     static constexpr bool kWide = false;
     RayPrep rp; TravState s;
     uint32_t* stL; float* stT; int stride, cap, maxLoop; uint32_t numTri; AABB sceneBox;
-    __device__ __forceinline__ void setup(const SceneView& sc, uint2* raw, int tid, int threads) {
+    static constexpr int kSpill = 1;                     // no spill storage: the reference drops pushes on a full stack
+    __device__ __forceinline__ void setup(const SceneView& sc, uint2* raw, int tid, int threads, uint2*) {
         uint32_t* base = reinterpret_cast<uint32_t*>(raw);
         stL = base + tid; stT = reinterpret_cast<float*>(base + 16 * threads) + tid; stride = threads;
         cap = sc.stackSize < 16 ? sc.stackSize : 16; maxLoop = sc.maxLoop; numTri = sc.numBatches * kBatchSize;
@@ -212,6 +260,9 @@ struct ParityTrav {
     __device__ __forceinline__ void begin(const SceneView&, const Float3& o, const Float3& d) { rp = prepare_ray(o, d, sceneBox); trav_init(s); }
     template <bool COUNT>
     __device__ __forceinline__ bool step(const SceneView& sc, int anyHit) { return trav_step<COUNT>(sc, rp, s, anyHit, cap, numTri, maxLoop, stL, stT, stride); }
+    // called by every lane of the warp (the wide layout votes inside); true = this lane's ray is finished
+    template <bool COUNT>
+    __device__ __forceinline__ bool step_warp(const SceneView& sc, int anyHit, bool active) { return active ? step<COUNT>(sc, anyHit) : false; }
     __device__ __forceinline__ float t() const { return s.t; }
     __device__ __forceinline__ int tri() const { return s.tri; }
     __device__ __forceinline__ float u() const { return s.u; }
@@ -225,15 +276,17 @@ struct ParityTrav {
 
 struct WideTrav {
     static constexpr bool kWide = true;
+    // The spill array is NOT a member: an array member that is indexed dynamically puts the whole object (ray constants and traversal
+    // state included) into local memory.  The kernel declares `uint2 spill[kWideStackSpill]` next to its Trav and passes it to setup().
+    static constexpr int kSpill = kWideStackSpill;
     WideRay w; WideState s; WideStack st;
-    uint2 spill[kWideStackSpill];
-    __device__ __forceinline__ void setup(const SceneView& sc, uint2* raw, int tid, int threads) {
+    __device__ __forceinline__ void setup(const SceneView& sc, uint2* raw, int tid, int threads, uint2* spill) {
         st.smem = raw + tid; st.stride = threads; st.spill = spill;
         begin(sc, Float3{0, 0, 0}, Float3{0, 1, 0});
     }
     __device__ __forceinline__ void begin(const SceneView& sc, const Float3& o, const Float3& d) { w = wide_prepare_ray(o, d); wide_init(s, sc.wide.root); }
     template <bool COUNT>
-    __device__ __forceinline__ bool step(const SceneView& sc, int anyHit) { return wide_step<COUNT>(sc.wide, w, s, anyHit, st); }
+    __device__ __forceinline__ bool step_warp(const SceneView& sc, int anyHit, bool active) { return wide_step<COUNT>(sc.wide, w, s, anyHit, st, active); }
     __device__ __forceinline__ float t() const { return s.t; }
     __device__ __forceinline__ int tri() const { return s.tri; }
     __device__ __forceinline__ float u() const { return s.ua; }      // the closest hit's barycentrics (the reference's u, v differ from them only on exact ties)

@@ -235,3 +235,85 @@ def assemble_rows(parts, bands, row_items):
     for p, (b, e) in zip(parts, bands):
         out[b * row_items: e * row_items] = p[b * row_items: e * row_items]
     return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# C-level multi-GPU (csrc/multi.cu): strips for the path tracer, bands + per-pass halo exchange for the denoiser, NCCL inside the library
+# ------------------------------------------------------------------------------------------------------------------
+def plan_rows(height, world, strip_height, rank, peer, kind, halo=0):
+    """rtrt_multi_plan_rows (pure host function): the rows `rank` sends to `peer` in exchange kind 0 (G-buffer redistribution),
+    1 (halo of `halo` rows), 2 (frame gather)."""
+    import ctypes as C
+    lib = L.load()
+    out = np.zeros(height, np.int32)
+    n = lib.rtrt_multi_plan_rows(height, world, strip_height, rank, peer, kind, halo, out.ctypes.data_as(C.c_void_p), height)
+    if n < 0:
+        raise ValueError(f"rtrt_multi_plan_rows: {L.STATUS_NAMES.get(n, n)}")
+    return out[:n].copy()
+
+
+def band_bounds(height, world):
+    """The denoiser bands of csrc/multi.cu: whole 16-row tiles, [(begin, end), ...]."""
+    tiles = (height + 15) // 16
+    b = [min(height, (tiles * r // world) * 16) for r in range(world)] + [height]
+    return list(zip(b[:-1], b[1:]))
+
+
+class MultiGpuRayTracer:
+    """Rank `rank` of `world` through the library's own multi-GPU entry points (rtrt_multi_init / rtrt_render_frame_multi).
+    `unique_id`: the 128 bytes of rtrt_multi_unique_id made on rank 0 (use `MultiGpuRayTracer.bootstrap` under torch.distributed)."""
+
+    def __init__(self, rt, rank, world, unique_id, mode="rows", strip_height=8):
+        import ctypes as C
+        self.rt, self.rank, self.world = rt, rank, world
+        buf = (C.c_ubyte * 128).from_buffer_copy(bytes(unique_id))
+        rt._check(rt._lib.rtrt_multi_init(rt._h, buf, rank, world))
+        self.set_mode(mode, strip_height)
+
+    @staticmethod
+    def unique_id():
+        import ctypes as C
+        buf = (C.c_ubyte * 128)()
+        rc = L.load().rtrt_multi_unique_id(buf)
+        if rc:
+            raise RuntimeError(f"rtrt_multi_unique_id: {L.STATUS_NAMES.get(rc, rc)} (NCCL not loadable?)")
+        return bytes(buf)
+
+    @classmethod
+    def bootstrap(cls, rt, mode="rows", strip_height=8):
+        """Under an initialised torch.distributed process group: rank 0 makes the NCCL id, broadcast_object_list hands it out."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        box = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        return cls(rt, rank, world, box[0], mode, strip_height)
+
+    def set_mode(self, mode, strip_height=8):
+        self.rt._check(self.rt._lib.rtrt_multi_set_mode(self.rt._h, {"rows": L.MULTI_ROWS, "samples": L.MULTI_SAMPLES}[mode], strip_height))
+        self.mode = mode
+
+    def update_vertices(self, pos_ptr=None, nrm_ptr=None):
+        self.rt._check(self.rt._lib.rtrt_update_vertices_multi(self.rt._h, pos_ptr, nrm_ptr, self.rt._nverts))
+
+    def draw(self, frame_number=None):
+        if frame_number is not None:
+            self.rt.set_frame_number(frame_number)
+        self.rt._check(self.rt._lib.rtrt_render_frame_multi(self.rt._h))
+
+    def render_progressive(self, spp, first_frame=1):
+        self.rt._check(self.rt._lib.rtrt_render_progressive_multi(self.rt._h, spp, first_frame))
+
+    def band(self):
+        import ctypes as C
+        b, e, x, n = C.c_int32(), C.c_int32(), C.c_uint64(), C.c_uint64()
+        self.rt._check(self.rt._lib.rtrt_multi_get_band(self.rt._h, C.byref(b), C.byref(e), C.byref(x), C.byref(n)))
+        return b.value, e.value, x.value, n.value
+
+
+def link_local(rts):
+    """rtrt_multi_link_local: the contexts of `rts` become ranks 0..N-1 of an in-process group (drive each from its own thread)."""
+    import ctypes as C
+    arr = (C.c_void_p * len(rts))(*[rt._h for rt in rts])
+    rc = L.load().rtrt_multi_link_local(arr, len(rts))
+    if rc:
+        raise RuntimeError(f"rtrt_multi_link_local: {L.STATUS_NAMES.get(rc, rc)}")

@@ -72,7 +72,7 @@ def test_denoise_pass_toggles(pkg, orc):
     W = H = 128
     pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C1"], seed=1)
     cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, W, H)
-    for passes in [(0, 0, 0, 0), (1, 0, 0, 1), (0, 1, 0, 0), (0, 0, 1, 0), (1, 1, 0, 0), (0, 1, 1, 1)]:
+    for passes in [(0, 0, 0, 0), (1, 0, 0, 1), (0, 1, 0, 0), (0, 0, 1, 0), (1, 1, 0, 0), (0, 1, 1, 1), (1, 1, 2, 1)]:
         st = orc.DenoiseState(W, H)
         with pkg.RayTracer(W, H) as rt:
             rt.set_mesh(pos, idx, nrm); rt.build_bvh()

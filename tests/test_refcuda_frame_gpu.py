@@ -176,7 +176,8 @@ def test_denoise_pass_toggles_match_reference_kernels(pkg, orc, ref, scene):
     Wd = Hd = 128
     pos, nrm, idx, ob, rb = scene
     cam = pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, Wd, Hd)
-    for passes in [(0, 0, 0, 0), (1, 0, 0, 1), (0, 1, 0, 0), (0, 0, 1, 0), (0, 1, 1, 1)]:
+    # wide = 2: the 5-iteration a-trous schedule (strides 1, 2, 4, 8, 16) of BASELINE config 4, vs the same reference kernel template
+    for passes in [(0, 0, 0, 0), (1, 0, 0, 1), (0, 1, 0, 0), (0, 0, 1, 0), (0, 1, 1, 1), (1, 1, 2, 1), (1, 0, 2, 1)]:
         with pkg.RayTracer(Wd, Hd) as rt, ref.RefFrame(Wd, Hd) as rf:
             rt.set_mesh(pos, idx, nrm); rt.build_bvh()
             rt.set_denoise_params(None, pkg.PassSettings(*passes))
