@@ -237,6 +237,19 @@ int rtrt_build_bvh(rtrt_ctx* ctx);
 int rtrt_traverse(rtrt_ctx* ctx, const rtrt_ray* d_rays, uint32_t n, rtrt_hit* d_hits, int any_hit);
 /* Same through HOST buffers (H2D of rays, traversal, D2H of hits, synchronous). */
 int rtrt_traverse_host(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_hit* h_hits, int any_hit);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc (CUDA graph
+ * capture around their own work, tight serving loops, harnesses that forbid it).  rtrt_traverse_host without any allocation: the device
+ * staging of rays / hits and the visit counters live in one file-scope `static __device__` array of csrc/traverse_noalloc.cu
+ * (RTRT_NOALLOC_MAX_RAYS x 48 B + 256 B = 3 MiB, held by every GPU that loads the library until the process exits); its address is
+ * taken with cudaGetSymbolAddress once per device.  n > RTRT_NOALLOC_MAX_RAYS -> RTRT_ERR_CAPACITY (split the batch).  Calls no
+ * cudaMalloc / cudaFree: it always traverses the reference-layout arrays of the last rtrt_build_bvh (option wide_bvh is ignored, stack_size
+ * <= 32), so the hits are bit-identical to rtrt_traverse_host with wide_bvh = 0.  *node_visits / *leaf_tests (may be NULL) receive the
+ * inner-node visits / triangle tests of this call.  The array is shared by all calls and contexts on a GPU and keeps the last call's
+ * contents (the counters are cleared per call); the call synchronises before returning, calls that overlap on one GPU (several host
+ * threads) race. */
+#define RTRT_NOALLOC_MAX_RAYS 65536u
+int rtrt_traverse_host_noalloc(rtrt_ctx* ctx, const rtrt_ray* h_rays, uint32_t n, rtrt_hit* h_hits, int any_hit,
+                               uint64_t* node_visits, uint64_t* leaf_tests);
 
 /* ---- frame inputs -------------------------------------------------------------------------------
  * Camera: the raw `Camera` struct of src/kernel.cuh:78-101 (176 bytes), which is also the camera.bin file format

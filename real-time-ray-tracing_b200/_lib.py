@@ -24,6 +24,7 @@ BUF_OUTPUT_RGBA8, BUF_COLOR64, BUF_EXPOSURE, BUF_HISTOGRAM = range(47, 51)
 BUF_WF_COUNTERS = 100
 BUF_WIDE_NODES, BUF_WIDE_TRIS, BUF_WIDE_STAT = 101, 102, 103
 MULTI_ROWS, MULTI_SAMPLES = 0, 1
+NOALLOC_MAX_RAYS = 65536          # RTRT_NOALLOC_MAX_RAYS (include/rtrt.h)
 
 
 class Config(C.Structure):
@@ -99,6 +100,7 @@ SYMBOLS = {
     "rtrt_build_bvh": (C.c_int, [C.c_void_p]),
     "rtrt_traverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int]),
     "rtrt_traverse_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int]),
+    "rtrt_traverse_host_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rtrt_get_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "rtrt_read_buffer": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "rtrt_get_counts": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),

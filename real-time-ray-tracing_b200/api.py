@@ -198,6 +198,15 @@ class RayTracer:
         self._check(self._lib.rtrt_traverse_host(self._h, _ptr(rays), rays.shape[0], _ptr(hits), int(any_hit)))
         return hits
 
+    def traverse_noalloc(self, rays, any_hit=False):
+        """rtrt_traverse_host_noalloc: the same query with the device staging in the library's static scratch (no cudaMalloc;
+        at most L.NOALLOC_MAX_RAYS rays).  Returns (hits, node_visits, leaf_tests)."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.empty(rays.shape[0], dtype=HIT_DTYPE)
+        nv, lt = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._lib.rtrt_traverse_host_noalloc(self._h, _ptr(rays), rays.shape[0], _ptr(hits), int(any_hit), C.byref(nv), C.byref(lt)))
+        return hits, int(nv.value), int(lt.value)
+
     def traverse_device(self, d_rays, n, d_hits, any_hit=False):
         self._check(self._lib.rtrt_traverse(self._h, C.c_void_p(d_rays), n, C.c_void_p(d_hits), int(any_hit)))
 
