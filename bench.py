@@ -22,7 +22,8 @@ N > 1    : one process per GPU, the frame is partitioned BY SAMPLE (north_star: 
 `--workload C5` : BASELINE config 5 — 3840x2160, 64 spp progressive (no denoiser), 16 777 216-triangle terrain, row bands,
            one gather of the fp32 accumulation buffer per step (always `--mode rows`).
 `--impl reference` : the reference has no CPU path and does not build on Linux; this tier's reference arm times the CPU
-           oracle (oracle/, multithreaded C++ restatement) with all host threads on a bounded sample of the workload.
+           oracle (oracle/, multithreaded C++ restatement) with all host threads; every step is one WHOLE frame of the workload
+           (about 1.3 s on 16 threads), `ms_per_step` is that step's own wall time.
 """
 import argparse
 import importlib
@@ -50,7 +51,7 @@ DENOISE_BYTES_PER_PX = 252         # reference pass sequence; fuse
 GBUF_BYTES_PER_PX = 30             # path-trace outputs: colour 8 + normal 8 + albedo 8 + depth 2 + motion 4
 NODE_BYTES, TRI_BYTES = 64, 128    # reference layout bytes per node visit / leaf test (SURVEY §8d "secondary")
 WIDE_NODE_BYTES, WIDE_TRI_BYTES = 80, 48   # wide layout (csrc/wide_bvh.cuh): 80 used bytes of one 128-byte line per visit, 48-byte triangles
-CPU_ROWS = 540                     # rows of the frame the CPU baseline path-traces and denoises (1/2 of 1080)
+CPU_ROWS = 1080                    # rows of the frame the CPU baseline path-traces and denoises: the whole frame (no extrapolation)
 
 
 def peaks():
@@ -114,8 +115,8 @@ class CpuArm:
         h = CPU_ROWS // nb
         self.bands = [(int((k + 0.5) * HEIGHT / nb) - h // 2, int((k + 0.5) * HEIGHT / nb) - h // 2 + h) for k in range(nb)]
         self.state = orc.DenoiseState(WIDTH, h * nb)
-        self.sample = (f"full LBVH build of {self.idx.shape[0]} tris + path trace + denoise of {h * nb}/{HEIGHT} rows "
-                       f"({nb} bands of {h} rows); frame time = build + {HEIGHT}/{h * nb} x (pt + dn)")
+        self.sample = (f"one whole step per sample: LBVH build of {self.idx.shape[0]} tris + path trace + denoise of all {h * nb} rows of the {WIDTH}x{HEIGHT} frame "
+                       f"(no extrapolation), {self.cores} host threads")
 
     def step(self, frame):
         orc = self.orc
@@ -203,11 +204,12 @@ def emit_line(line):
     os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
-def ncu_traffic(key):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture (profiles/ncu_traffic.json)."""
+def ncu_traffic(key, field="dram_bytes"):
+    """dram__bytes_read.sum + dram__bytes_write.sum (or another counter) of one launch, from the committed ncu --set full capture of this
+    command (profiles/ncu_traffic.json, written by tools/ncu_to_profiles.py)."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            return json.load(f)[key]["dram_bytes"]
+            return json.load(f)[key][field]
     except Exception:
         return None
 
@@ -276,6 +278,135 @@ def reference_kernels(pkg, rt, pos, nrm, idx, cam, rays_per_frame, warm=10, time
         return out
     except Exception as e:                                     # baseline leg: never fail the bench line
         return {"unavailable": repr(e)}
+
+
+def _gpu_time(torch, rt, flush, fn, n=8, warm=2):
+    """median CUDA-event time of fn(i) on the library's stream, L2 flushed before every call"""
+    stream = torch.cuda.ExternalStream(rt.stream)
+    ts = []
+    for i in range(n + warm):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); fn(i); b.record(stream); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts[warm:]))
+
+
+def other_configs(pkg, torch, local, flush, hbm_peak):
+    """BASELINE configs 1, 3 and 4 (the ones that are not the bench line) as sub-records of the N = 1 line, so that every config has a
+    driver-run number: product times with CUDA events (L2 flushed), the reference kernels beside them where they can run the size."""
+    out = {}
+    try:
+        from oracle.refcuda import ref
+        have_ref = ref.available() and hasattr(ref.load(), "refcuda_frame_create")
+    except Exception:
+        ref, have_ref = None, False
+    # C1: 10 240-triangle mesh, LBVH build + 256 x 256 primary closest hit
+    W = H = 256
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C1"], seed=1)
+    cam = pkg.scenes.make_camera(CAMERA["pos"], CAMERA["yaw"], CAMERA["pitch"], W, H)
+    rays = pkg.scenes.primary_rays(cam, W, H)
+    with pkg.RayTracer(W, H, device=local) as rt:
+        rt.set_mesh(pos, idx, nrm)
+        d_rays = torch.from_numpy(rays.view(np.uint8).reshape(-1)).cuda(); d_hits = torch.empty(rays.shape[0] * 16, dtype=torch.uint8, device="cuda")
+        c1 = {"workload": "C1: 10 240-tri mesh, LBVH build + 256x256 primary closest hit", "build_ms": _gpu_time(torch, rt, flush, lambda i: rt.build_bvh()),
+              "traverse_ms": _gpu_time(torch, rt, flush, lambda i: rt.traverse_device(d_rays.data_ptr(), rays.shape[0], d_hits.data_ptr()))}
+    if have_ref:
+        rb = ref.build_bvh(pos, nrm, idx, iterations=11); c1["ref_kernels_build_ms"] = rb.ms
+        _, c1["ref_kernels_traverse_ms"] = ref.traverse(rb, rays, iterations=11)
+    out["c1"] = c1
+    # C3: 4 194 304 triangles rebuilt per frame (vertex upload excluded, Morton-ordered input: per-batch sort + global top level)
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C3"], seed=1)
+    with pkg.RayTracer(64, 64, device=local) as rt:
+        rt.set_mesh(pos, idx, nrm)
+        ms = _gpu_time(torch, rt, flush, lambda i: rt.build_bvh())
+    gbs = BUILD_BYTES_PER_TRI * idx.shape[0] / (ms * 1e-3) / 1e9
+    out["c3"] = {"workload": "C3: per-frame LBVH rebuild of 4 194 304 triangles (4096 batches, global top level)", "triangles": int(idx.shape[0]), "build_ms": ms,
+                 "mtris_s": idx.shape[0] / ms / 1e3, "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak},
+                 "reference_kernels": "not runnable (its top level is limited to 1023 batches, src/init.cu:126)"}
+    # C4: temporal accumulation + a-trous denoise at 3840 x 2160 on path-traced G-buffers: the reference's schedule (7x7 + 5x5 with strides 3, 6, 12)
+    # and the 5-iteration schedule the config names (5x5 with strides 1, 2, 4, 8, 16); 4K path trace beside it
+    W, H = 3840, 2160
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES[SCENE], seed=1)
+    cam = pkg.scenes.make_camera(CAMERA["pos"], CAMERA["yaw"], CAMERA["pitch"], W, H)
+    c4 = {"workload": "C4: temporal + a-trous denoise at 3840x2160 on path-traced G-buffers of the C2 scene", "width": W, "height": H}
+    with pkg.RayTracer(W, H, device=local) as rt:
+        rt.set_mesh(pos, idx, nrm); rt.build_bvh(); rt.set_camera(cam, reset_history=True)
+        def pt(i): rt.set_frame_number(2 + i); rt.pathtrace()
+        c4["pathtrace_ms"] = _gpu_time(torch, rt, flush, pt, n=5); c4["pathtrace_mrays_s"] = rt.timings()["rays_traced"] / c4["pathtrace_ms"] / 1e3
+        for name, wide_pass in (("denoise_ms", 1), ("denoise_5_iterations_ms", 2)):
+            rt.set_denoise_params(None, pkg.PassSettings(1, 1, wide_pass, 1))
+            stream = torch.cuda.ExternalStream(rt.stream); ts = []
+            for i in range(8):
+                rt.set_frame_number(20 + i); rt.pathtrace()
+                with torch.cuda.stream(stream):
+                    flush.zero_()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream); rt.denoise(); b.record(stream); torch.cuda.synchronize()
+                ts.append(a.elapsed_time(b))
+            c4[name] = float(np.median(ts[2:]))
+        gbs = DENOISE_BYTES_PER_PX * W * H / (c4["denoise_ms"] * 1e-3) / 1e9
+        c4["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "bytes_per_px": DENOISE_BYTES_PER_PX}
+        if have_ref:
+            from oracle import orc
+            sky = orc.Sky(); sky.sky = rt.read_buffer(pkg.BUF_SKY); sky.sky_cdf = rt.read_buffer(pkg.BUF_SKY_CDF)
+            sky.sun = rt.read_buffer(pkg.BUF_SUN); sky.sun_cdf = rt.read_buffer(pkg.BUF_SUN_CDF); sky.sun_dir, sky.cos_theta_max = rt.get_sun()
+    if have_ref:
+        rb = ref.build_bvh(pos, nrm, idx)
+        with ref.RefFrame(W, H) as rf:
+            rf.set_tables(orc.load_tables()[0]); rf.set_scene(rb); rf.set_materials(orc.default_materials(), np.full(rb.num_batches * 1024, 3, np.int32))
+            rf.set_texture(0, orc.mip_chain(orc.DEFAULT_TEX[0])); rf.set_texture(1, orc.mip_chain(orc.DEFAULT_TEX[1])); rf.set_sky(sky)
+            c4["ref_kernels_pathtrace_ms"] = rf.pathtrace(cam, 2, iterations=3)
+            for name, wide_pass in (("ref_kernels_denoise_ms", 1), ("ref_kernels_denoise_5_iterations_ms", 2)):
+                ts = []
+                for fr in range(1, 6):
+                    rf.pathtrace(cam, fr); ts.append(rf.denoise(fr, passes=(1, 1, wide_pass, 1)))
+                c4[name] = float(np.median(ts[2:]))
+    out["c4"] = c4
+    return out
+
+
+def strong_c5(args, pkg, torch, dist, rank, world, local, make_group):
+    """BASELINE config 5 as a sub-record of every --gpus N line: 3840x2160, 64 spp progressive (no denoiser), 16 777 216-triangle terrain,
+    partitioned BY SAMPLE through the library's own multi-GPU entry point (rtrt_render_progressive_multi: rank r renders samples r, r + N, ...
+    of the whole frame, BVH rebuilt per GPU, one NCCL all-reduce of the fp32 accumulation image).  Fixed total work -> strong scaling."""
+    W, H, spp = 3840, 2160, C5_SPP
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C5"], seed=1)
+    cam = pkg.scenes.make_camera(CAMERA["pos"], CAMERA["yaw"], CAMERA["pitch"], W, H)
+    rt = pkg.RayTracer(W, H, device=local).init()
+    rt.set_option("wide_bvh", int(args.layout == "wide"))
+    rt.set_mesh(pos, idx, nrm); rt.set_camera(cam, reset_history=True)
+    mg = make_group(rt, "samples")
+    stream = torch.cuda.ExternalStream(rt.stream, device=torch.device("cuda", local))
+    def step():
+        if mg is None:
+            rt.build_bvh()
+            for s in range(spp):
+                rt.set_frame_number(1 + s); rt.pathtrace(); rt.accumulate(reset=(s == 0))
+        else:
+            mg.render_progressive(spp, first_frame=1)
+    step(); rt.sync()
+    r0 = rt.timings()["rays_traced_total"]
+    if world > 1: dist.barrier()
+    torch.cuda.synchronize()
+    steps = 2
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(steps): step()
+    b.record(stream)
+    if world > 1: dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
+    r = torch.tensor([float(rt.timings()["rays_traced_total"] - r0)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(r, op=dist.ReduceOp.SUM)
+    rt.cleanup()
+    ms = t.item() / steps
+    return {"workload": f"C5: 3840x2160, {spp} spp progressive path trace (no denoiser), {idx.shape[0]}-tri terrain (16 384 batches, global top level), "
+                        f"sample-partitioned x{world}, BVH rebuilt per GPU and step, one NCCL all-reduce of the fp32 accumulation image",
+            "scaling": "strong", "steps": steps, "ms_per_step": ms, "ms_per_sample": ms / spp, "rays_per_step": r.item() / steps,
+            "mrays_s": r.item() / steps / (ms * 1e-3) / 1e6}
 
 
 def run_c5(args, rank, world, local, torch, dist, pkg):
@@ -368,6 +499,8 @@ def main():
     ap.add_argument("--layout", default="wide", choices=["wide", "reference"],
                     help="traversal layout of the timed steps: the 8-wide compressed BVH (option wide_bvh, derived from the reference-layout arrays "
                          "inside every rtrt_build_bvh) or the reference's own node / triangle arrays; the other one is timed as a sub-record")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling sub-records (C5 at 64 spp, C2 rows mode)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 sub-records of the N = 1 line")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-kernels", action="store_true")
     args = ap.parse_args()
@@ -403,50 +536,40 @@ def main():
     rt.set_option("wide_bvh", int(wide))
     node_bytes, tri_bytes = (WIDE_NODE_BYTES, WIDE_TRI_BYTES) if wide else (NODE_BYTES, TRI_BYTES)
     by_rows = args.mode == "rows"
-    sh = pkg.RowShardedRayTracer(rt, WIDTH, HEIGHT, rank, world, bvh=args.bvh) if by_rows else None
-    rows = sh.band if by_rows else (0, HEIGHT)
+    # N > 1: the library's own multi-GPU entry points (csrc/multi.cu: NCCL inside librtrt.so); torch.distributed only hands out the NCCL id,
+    # synchronises the ranks around the timed regions and reduces the timing scalars
+    def make_group(ctx, mode):
+        return pkg.parallel.MultiGpuRayTracer.bootstrap(ctx, mode=mode) if world > 1 else None
+    mg = make_group(rt, "rows" if by_rows else "samples")
+    rows = mg.band()[:2] if (mg is not None and by_rows) else (0, HEIGHT)
     stream = torch.cuda.ExternalStream(rt.stream, device=torch.device("cuda", local))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     h_pos = torch.from_numpy(pos.reshape(-1).copy()).pin_memory()
     h_nrm = torch.from_numpy(nrm.reshape(-1).copy()).pin_memory()
     h_out = [torch.empty(n_px * 8, dtype=torch.uint8).pin_memory() for _ in range(2)]     # frames in flight: two host frame buffers
     torch.cuda.synchronize()
-    frame_no = [1 + (rank if not by_rows else 0)]
+    frame_no = [1]
+    lib_stage_ms = []                           # N > 1: per step, the library's own CUDA-event stage times (build, path trace, denoise)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def combine():
-        """sample mode: average the ranks' denoised frames (NCCL all-reduce over NVLink), on the library's stream"""
-        if world == 1 or by_rows:
-            return
-        ptr, nbytes = rt.get_buffer(pkg.BUF_RENDER_COLOR)
-        with torch.cuda.stream(stream):
-            dist.all_reduce(torch.as_tensor(DevView(ptr, nbytes), device="cuda"), op=dist.ReduceOp.AVG)
-
     def frame(e):
-        """build | path trace | (G-buffer exchange) | denoise | (frame gather / combine)"""
-        rt.set_frame_number(frame_no[0]); frame_no[0] += world if not by_rows else 1
-        if by_rows:
-            sh.build_bvh()
-            if e: e[1].record(stream)
-            sh.pathtrace()
-            if e: e[2].record(stream)
-            sh.exchange_gbuffers()
-            if e: e[3].record(stream)
-            sh.denoise()
-            if e: e[4].record(stream)
-            sh.gather_frame()
-        else:
-            rt.build_bvh()
-            if e: e[1].record(stream)
-            rt.pathtrace()
-            if e: e[2].record(stream); e[3].record(stream)
-            rt.denoise()
-            if e: e[4].record(stream)
-            combine()
+        """build | path trace | (G-buffer redistribution) | denoise with halo exchange | (frame gather / sample combine)"""
+        rt.set_frame_number(frame_no[0])
+        if mg is not None:
+            frame_no[0] += 1 if by_rows else world       # samples mode: rank r renders sample index frame + r
+            mg.draw()                                    # rtrt_render_frame_multi: every stage and every NCCL exchange inside the library
+            return
+        frame_no[0] += 1
+        rt.build_bvh()
+        if e: e[1].record(stream)
+        rt.pathtrace()
+        if e: e[2].record(stream); e[3].record(stream)
+        rt.denoise()
+        if e: e[4].record(stream)
 
     def step_device(e):
         if e: e[0].record(stream)
@@ -456,9 +579,13 @@ def main():
     def step_e2e(i):
         """One frame through the public API with HOST buffers, nothing blocks the host: vertex upload (copy stream, overlaps the
         previous frame's path trace), frame, read-back of the denoised frame (snapshot + copy stream, overlaps the next frame)."""
-        rt.update_vertices(h_pos.data_ptr(), h_nrm.data_ptr())             # H2D, pinned
+        if mg is None:
+            rt.update_vertices(h_pos.data_ptr(), h_nrm.data_ptr())             # H2D, pinned
+        else:                                                                  # rank 0 uploads once, NCCL broadcast over NVLink to the other GPUs
+            mg.update_vertices(h_pos.data_ptr() if rank == 0 else None, h_nrm.data_ptr() if rank == 0 else None)
         frame(None)
-        rt.read_buffer_async(pkg.BUF_RENDER_COLOR, h_out[i & 1].data_ptr(), h_out[i & 1].numel())   # D2H, pinned
+        if rank == 0:                                                          # the combined frame is needed on one host only
+            rt.read_buffer_async(pkg.BUF_RENDER_COLOR, h_out[i & 1].data_ptr(), h_out[i & 1].numel())   # D2H, pinned
 
     def timed_e2e(steps, warmup):
         """K frames in flight, timed as ONE region on the library's stream: start event, K x (L2 flush, step), join of the copy
@@ -494,12 +621,16 @@ def main():
             tmg = rt.timings()                                           # synchronises the stream (outside the event pair)
             rays += tmg["rays_traced"]
             kms.append(tmg["pt_kernel_ms"])
+            lib_stage_ms.append([tmg["build_bvh_ms"], tmg["pathtrace_ms"], tmg["denoise_ms"]])
         barrier()
         nl = rt.timings()["kernel_launches"] - lbefore
         tot = float(np.sum([e[0].elapsed_time(e[5]) for e in evs]))
         stages = None
-        if step_fn is step_device:
+        if step_fn is step_device and mg is None:
             stages = [float(np.mean([e[k].elapsed_time(e[k + 1]) for e in evs])) for k in range(5)]
+        elif step_fn is step_device:
+            b_ms, p_ms, d_ms = np.mean(np.asarray(lib_stage_ms[-steps:], np.float64), axis=0)    # denoise_ms includes its halo exchanges
+            stages = [float(b_ms), float(p_ms), 0.0, float(d_ms), max(tot / steps - float(b_ms + p_ms + d_ms), 0.0)]
         return tot, stages, int(nl), int(rays)
 
     kms = []                                    # per step: CUDA-event times of the path-trace kernels (library option kernel_timing)
@@ -509,6 +640,10 @@ def main():
     kernel_ms = np.mean(np.asarray(kms, np.float64), axis=0) if kms and not by_rows else np.zeros(6)
     rt.set_option("kernel_timing", 0)
     sampler.stop_flag = True; sampler.join()
+    frame_sha1 = None
+    if world == 1:                              # the frame the timed region ended on: two runs of one commit can be compared
+        import hashlib
+        frame_sha1 = hashlib.sha1(rt.read_buffer(pkg.BUF_RENDER_COLOR).tobytes()).hexdigest()
     e2e_steps = max(3, args.steps // 2)
     e2e_ms, e2e_rays = timed_e2e(e2e_steps, 3)
 
@@ -522,6 +657,45 @@ def main():
 
     # untimed: the ceilings a traversal without RT cores runs against on this GPU (csrc/microbench.cu)
     mb = rt.microbench() if rank == 0 else None
+
+    # ---- strong-scaling sub-records (fixed total work): ONE C2 frame sharded by rows, and BASELINE config 5 at 64 spp ----
+    strong = None
+    if not args.no_strong:
+        strong = {}
+        if mg is not None and not by_rows:
+            mg.set_mode("rows")
+            k = 0
+            def rows_step():
+                nonlocal k
+                rt.set_frame_number(100 + k); k += 1
+                mg.draw()
+            for _ in range(3): rows_step()
+            barrier()
+            r0 = rt.timings()["rays_traced_total"]
+            n_rows_steps, ev = 10, []
+            for _ in range(n_rows_steps):
+                with torch.cuda.stream(stream):
+                    flush.zero_()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream); rows_step(); b.record(stream); ev.append((a, b))
+            barrier()
+            tt = torch.tensor([float(np.sum([a.elapsed_time(b) for a, b in ev]))], dtype=torch.float64, device="cuda")
+            rr = torch.tensor([float(rt.timings()["rays_traced_total"] - r0)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX); dist.all_reduce(rr, op=dist.ReduceOp.SUM)
+            band = mg.band()
+            strong["c2_rows"] = {"workload": "C2, ONE 1080p frame sharded over the GPUs: path trace in interleaved 8-row strips, G-buffer redistribution, denoise in "
+                                             "16-row-aligned bands with an NCCL halo exchange before every filter pass, frame gather (rtrt_render_frame_multi, rows mode)",
+                                 "scaling": "strong", "steps": n_rows_steps, "ms_per_step": tt.item() / n_rows_steps,
+                                 "mrays_s": rr.item() / (tt.item() * 1e-3) / 1e6, "rank0_band": list(band[:2])}
+            mg.set_mode("samples")
+        strong["c5_64spp"] = strong_c5(args, pkg, torch, dist, rank, world, local, make_group)
+    configs = None
+    if world == 1 and not args.no_configs:
+        try:
+            with quiet_stdout():
+                configs = other_configs(pkg, torch, local, flush, hbm_peak)
+        except Exception as e:                                 # sub-records never fail the bench line
+            configs = {"unavailable": repr(e)}
 
     t = torch.tensor([total_ms, e2e_ms] + stages, dtype=torch.float64, device="cuda")
     r = torch.tensor([rays, e2e_rays], dtype=torch.float64, device="cuda")
@@ -558,10 +732,22 @@ def main():
         floor_l1 = waves * chain * mb["l1_latency_ns"] * 1e-6
         floor_l2 = waves * chain * mb["l2_latency_ns"] * 1e-6
         l2_peak = mb["l2_read_gbs"]
-        trace_roofline = {"kernel": "k_pt_trace, bounce round 1 (%.0f%% of the step)" % (100 * tr_ms / max(ms_step, 1e-9)), "bound": "l2-latency",
-                          "achieved": tr_gbs, "peak": l2_peak, "unit": "GB/s", "frac": tr_gbs / l2_peak if l2_peak else None,
-                          "peak_kind": "measured L2 read bandwidth (rtrt_microbench: 32 MiB L2-resident buffer, ld.global.cg, all SMs)",
-                          "traffic": ncu_traffic("k_pt_trace_round1_wide" if wide else "k_pt_trace_round1"),
+        # The binding ceiling (ncu: neither DRAM nor L2 nor the load chains come close, the SM issue slots do): warp instructions of one launch
+        # (counted by ncu on this very command, profiles/ncu_traffic.json — the workload is deterministic) per second of the LIVE launch time,
+        # against one warp instruction per SM sub-partition and clock at the SM clock sampled during the timed region.
+        tkey = "k_pt_trace_round1_wide" if wide else "k_pt_trace_round1"
+        winst = ncu_traffic(tkey, "warp_instructions")
+        clk = sampler.summary()["sm_mhz"] or sampler.summary()["sm_max_mhz"] or 1965.0
+        issue_peak = props.multi_processor_count * 4 * clk * 1e6 / 1e9                 # G warp-instructions / s
+        issue_ach = (winst / (tr_ms * 1e-3) / 1e9) if (winst and tr_ms > 0) else None
+        trace_roofline = {"kernel": "k_pt_trace, bounce round 1 (%.0f%% of the step)" % (100 * tr_ms / max(ms_step, 1e-9)), "bound": "issue",
+                          "achieved": issue_ach, "peak": issue_peak, "unit": "Gwarp-inst/s", "frac": (issue_ach / issue_peak) if issue_ach else None,
+                          "peak_kind": "1 warp instruction per SM sub-partition and clock: %d SMs x 4 x %.0f MHz (clock sampled under load); instruction count per launch "
+                                       "from the committed ncu capture of this command (profiles/ncu_traffic.json)" % (props.multi_processor_count, clk),
+                          "warp_instructions_per_launch": winst, "lanes_per_instruction": ncu_traffic(tkey, "lanes_per_instruction"),
+                          "traffic": ncu_traffic(tkey),
+                          "l2": {"achieved": tr_gbs, "peak": l2_peak, "unit": "GB/s", "frac": tr_gbs / l2_peak if l2_peak else None,
+                                 "peak_kind": "measured L2 read bandwidth (rtrt_microbench: 32 MiB L2-resident buffer, ld.global.cg, all SMs)"},
                           "hbm_frac": tr_gbs / hbm_peak, "hbm_peak": hbm_peak,
                           "algorithmic_bytes_per_launch": int(tr_bytes), "ms_per_launch": tr_ms,
                           "rays_per_launch": int(r1_rays), "node_visits_per_ray": r1_nodes / max(r1_rays, 1), "leaf_tests_per_ray": r1_leaves / max(r1_rays, 1),
@@ -569,14 +755,16 @@ def main():
                                             "l1_hit_ns": mb["l1_latency_ns"], "l2_hit_ns": mb["l2_latency_ns"], "dram_ns": mb["dram_latency_ns"],
                                             "floor_ms_all_l1_hits": floor_l1, "floor_ms_all_l2_hits": floor_l2,
                                             "frac_of_l2_floor": floor_l2 / tr_ms if tr_ms > 0 else None},
-                          "note": "BVH traversal without RT cores: a chain of dependent node fetches served by L1/L2 (DRAM sees `traffic` bytes per launch, "
-                                  "ncu --set full, profiles/ncu_traffic.json).  `frac` = node/leaf fetch bytes per second against the measured L2 bandwidth; "
-                                  "`latency_floor` = the time the dependent-load chains alone would take at the measured L1 / L2 hit latencies with every "
-                                  "resident lane busy; the rest of the kernel time is the arithmetic of the box / triangle tests and SIMT divergence "
-                                  "(profiles/*_ncu_summary.md)"}
-        par = (f"sample-partitioned x{world}, BVH rebuilt per GPU, NCCL all-reduce of the frame" if not by_rows else
-               f"row bands x{world}, BVH {args.bvh}, NCCL all-gather of the G-buffers (30 B/px) and of the denoised frame + history (24 B/px), "
-               f"denoise of band + 80-row halo")
+                          "note": "BVH traversal without RT cores is instruction-bound on B200: `frac` = issued warp instructions per second against the SM issue "
+                                  "rate.  The other candidate ceilings are far away: `l2` = node / leaf fetch bytes per second against the measured L2 read bandwidth, "
+                                  "`latency_floor` = the time the dependent-load chains alone would take at the measured L1 / L2 hit latencies with every resident "
+                                  "lane busy, `traffic` = DRAM bytes of one launch (ncu --set full).  What is left of the issue rate goes to SIMT divergence: "
+                                  "`lanes_per_instruction` of 32 (profiles/*_ncu_summary.md)"}
+        par = ("1 GPU" if world == 1 else
+               f"sample-partitioned x{world} (weak scaling: N samples per pixel and frame; rank r renders the whole frame with sample index frame + r), BVH rebuilt "
+               f"per GPU, one ncclAllReduce (mean of the rgb lanes) of the denoised frame; all of it inside rtrt_render_frame_multi" if not by_rows else
+               f"ONE frame over {world} GPUs: path trace in interleaved 8-row strips, grouped ncclSend/Recv redistribution of the G-buffers to 16-row-aligned bands "
+               f"(+- 32 rows), denoise per band with a halo exchange before every filter pass, frame gather (16 B/px); rtrt_render_frame_multi")
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if not by_rows else "strong",
@@ -605,10 +793,15 @@ def main():
                                  "note": "252 B/px = the reference's pass-wise traffic; fused lower bound 74 B/px"},
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "ms_per_step": e2e_ms / e2e_steps,
                     "h2d_bytes_per_step": int(h_pos.numel() * 4 + h_nrm.numel() * 4), "d2h_bytes_per_step": int(h_out[0].numel()),
+                    "multi_gpu": None if world == 1 else "rank 0 uploads the vertex + normal buffers once per step and they are broadcast over NVLink (rtrt_update_vertices_multi); "
+                                                         "only rank 0 reads the combined frame back",
                     "note": "frames in flight: every step uploads the vertex + normal buffers from pinned host memory (copy stream), rebuilds the "
                             "BVH, path-traces, denoises and reads the denoised frame back into pinned host memory (snapshot + copy stream); the "
                             "copies overlap the neighbouring frames' kernels; one timed region over all steps, L2 flushes included"},
             "microbench": mb,
+            "last_frame_sha1": frame_sha1,
+            "strong": strong,
+            "other_configs": configs,
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
         }
@@ -616,7 +809,7 @@ def main():
             with quiet_stdout():
                 line["reference_kernels"] = reference_kernels(pkg, rt, pos, nrm, idx, cam, rays / args.steps)
         if not args.no_cpu_baseline and world == 1:
-            _, _, line["cpu_baseline"] = CpuArm(pkg).baseline(steps=1, warmup=0)
+            _, _, line["cpu_baseline"] = CpuArm(pkg).baseline(steps=4, warmup=0)      # four whole frames, ~6 s of CPU work on 16 threads
         emit_line(line)
     rt.cleanup()
     if world > 1:

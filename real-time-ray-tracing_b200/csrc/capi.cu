@@ -22,6 +22,8 @@ template <typename T>
 static void dfree(T*& p) { if (p) cudaFree(p); p = nullptr; }
 
 static void free_mesh(Context& c) {
+    if (c.wideStream) cudaStreamSynchronize(c.wideStream);
+    c.widePending = false;
     if (c.ownsMesh) { dfree(c.dPos); dfree(c.dNrm); dfree(c.dIdx); }
     c.dPos = nullptr; c.dNrm = nullptr; c.dIdx = nullptr; c.ownsMesh = false;
     dfree(c.dTriangles); dfree(c.dAabbs); dfree(c.dMorton); dfree(c.dReorderIdx); dfree(c.dNodes); dfree(c.dMortonPre);
@@ -167,6 +169,9 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     for (auto& st : c.chunkStream) if (st) cudaStreamDestroy(st);
     for (auto& ev : c.chunkJoin) if (ev) cudaEventDestroy(ev);
     if (c.chunkFork) cudaEventDestroy(c.chunkFork);
+    if (c.evWideFork) cudaEventDestroy(c.evWideFork);
+    if (c.evWideDone) cudaEventDestroy(c.evWideDone);
+    if (c.wideStream) cudaStreamDestroy(c.wideStream);
     for (cudaEvent_t e : {c.evGeomReady, c.evGeomFree, c.evStaged, c.evReadDone}) if (e) cudaEventDestroy(e);
     if (c.copyStream) cudaStreamDestroy(c.copyStream);
     if (c.uploadStream) cudaStreamDestroy(c.uploadStream);
@@ -271,7 +276,11 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value) {
     if (!strcmp(name, "keep_presort_morton")) { c.keepPresortMorton = value != 0; return RTRT_OK; }
     if (!strcmp(name, "stack_size")) { if (value < 1 || value > 64) return c.fail(RTRT_ERR_ARG, "stack_size must be 1..64"); c.stackSize = (int)value; return RTRT_OK; }
     if (!strcmp(name, "assume_bvh_valid")) { c.bvhValid = value != 0; c.wideValid = false; return RTRT_OK; }
-    if (!strcmp(name, "wide_bvh")) { if (value < 0 || value > 2) return c.fail(RTRT_ERR_ARG, "wide_bvh must be 0, 1 or 2"); c.wideBvh = value != 0; c.widePrimary = value != 2; return RTRT_OK; }
+    if (!strcmp(name, "wide_bvh")) {
+        if (value < 0 || value > 2) return c.fail(RTRT_ERR_ARG, "wide_bvh must be 0, 1 or 2");
+        { int rc = wide_join(c); if (rc) return rc; }
+        c.wideBvh = value != 0; c.widePrimary = value != 2; return RTRT_OK;
+    }
     if (!strcmp(name, "morton_bits")) { if (value != 60 && value != 63) return c.fail(RTRT_ERR_ARG, "morton_bits must be 60 or 63"); c.mortonBits = (int)value; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "global_sort")) { c.globalSort = value != 0; c.bvhValid = false; return RTRT_OK; }
     if (!strcmp(name, "wavefront")) { c.wavefront = value != 0; return RTRT_OK; }
@@ -289,6 +298,7 @@ int rtrt_build_bvh(rtrt_ctx* ctx) {
     CTX_OR_FAIL(ctx);
     Context& c = ctx->c;
     RTRT_CUDA(c, cudaSetDevice(c.device));
+    { int rc = wide_join(c); if (rc) return rc; }            // a collapse still running on the side stream reads the arrays this build rewrites
     RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_BUILD][0], c.stream));
     int rc = launch_build_bvh(c);
     if (rc) return rc;
@@ -339,6 +349,7 @@ int rtrt_get_buffer(rtrt_ctx* ctx, int which, void** dptr, size_t* bytes) {
         int rc = ensure_frame_resources(c);
         if (rc) return rc;
     }
+    if (which >= RTRT_BUF_WIDE_NODES && which <= RTRT_BUF_WIDE_STAT) { int rc = wide_join(c); if (rc) return rc; }
     const size_t n = (size_t)c.numBatches * kBatchSize, bp = c.numBatchesPadded, px = (size_t)c.gbufW * c.gbufH;
     void* p = nullptr; size_t b = 0;
     switch (which) {

@@ -39,6 +39,8 @@ struct Context {
     bool bvhValid = false;
     // ---- wide traversal layout (option wide_bvh; wide_build.cu) ----
     bool wideBvh = false, wideValid = false, wideStatPending = false;
+    // wide_bvh = 2: the collapse to the wide layout runs on a side stream, concurrently with the primary-ray kernels (which then do not need it)
+    cudaStream_t wideStream = nullptr; cudaEvent_t evWideFork = nullptr, evWideDone = nullptr; bool widePending = false;
     bool widePrimary = true;                              // option wide_bvh = 2: primary rays keep the reference layout (coherent rays: its two-child nodes hit L1), bounce rays the wide one
     void* dWideNodes = nullptr; void* dWideTris = nullptr; void* dWideQueue = nullptr; size_t wideNodeCap = 0;
     uint32_t wideRoot = 0, wideNodes = 0;
@@ -135,6 +137,7 @@ int launch_presort(Context& c);             // bvh_presort.cu
 int ensure_wide(Context& c);                // traverse.cu: builds the wide layout if option wide_bvh is on and it is stale
 int launch_wide_build(Context& c);          // wide_build.cu: 8-wide compressed nodes + 48-byte triangles from the arrays of the build
 int check_wide_error(Context& c);           // wide_build.cu: after a stream sync
+int wide_join(Context& c);                  // wide_build.cu: main stream waits for a wide build running on the side stream
 int wait_geometry(Context& c);              // capi.cu: main stream waits for a pending rtrt_update_vertices upload
 int check_build_error(Context& c);           // capi.cu: after a stream sync, turns the fused build's time-out word into RTRT_ERR_CUDA
 int geometry_consumed(Context& c);          // capi.cu: records that the main stream has read the vertex buffers

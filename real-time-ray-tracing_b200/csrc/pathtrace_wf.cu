@@ -433,6 +433,7 @@ static void launch_chunk(Context& c, const PathTraceParams& P, const WfBuffers& 
     const int maxGrid = wide ? c.traceResidentWide : c.traceResident;
     const int want = (int)(((size_t)c.width * rows + 127) / 128);
     const int traceGrid = want < maxGrid ? (want > 0 ? want : 1) : maxGrid, logicGrid = traceGrid;
+    if (wide && st == c.stream) wide_join(c);        // wide_bvh = 2: the collapse ran beside the primary-ray kernels; the bounce rounds need it
     for (int round = 0; round < 4; ++round) {
         uint32_t* cnt = B.counters;
         if (wide) {
@@ -465,6 +466,7 @@ int launch_pathtrace_wavefront(Context& c) {
     int K = c.ptChunks;
     if (K > (rows + 7) / 8) K = (rows + 7) / 8;
     if (K < 1) K = 1;
+    if (c.wideBvh && (c.widePrimary || K > 1)) { int rcw = wide_join(c); if (rcw) return rcw; }
     if (K > 1 && !c.chunkFork) {
         RTRT_CUDA(c, cudaEventCreateWithFlags(&c.chunkFork, cudaEventDisableTiming));
         for (int k = 0; k < Context::kMaxChunks; ++k) {

@@ -98,6 +98,7 @@ int launch_traverse(Context& c, const Ray* dRays, uint32_t n, Hit* dHits, int an
     if (!c.bvhValid) return c.fail(RTRT_ERR_STATE, "rtrt_traverse: BVH not built");
     if (n == 0) return RTRT_OK;
     { int rc = ensure_wide(c); if (rc) return rc; }
+    if (c.wideBvh) { int rc = wide_join(c); if (rc) return rc; }
     const SceneView sc = make_scene_view(c);
     const uint32_t grid = (n + kTravThreads - 1) / kTravThreads;
     if (c.wideBvh) {

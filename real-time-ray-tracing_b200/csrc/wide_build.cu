@@ -305,11 +305,25 @@ int launch_wide_build(Context& c) {
     p.tlasBase = B * (uint32_t)kWideRegion; p.tlasCap = tlasCap;
     p.stat = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(c.dWideQueue) + (size_t)tlasCap * sizeof(WideEntry));
     p.tlasQueue = reinterpret_cast<WideEntry*>(c.dWideQueue);
-    RTRT_CUDA(c, cudaMemsetAsync(p.stat, 0, 64, c.stream));
-    k_wide_blas<<<B, kWbThreads, 0, c.stream>>>(p);
+    // wide_bvh = 2 (primary rays on the reference layout): the collapse runs on a side stream behind the build and overlaps the primary-ray
+    // kernels of the frame; the first kernel that traverses the wide layout waits for it (wide_join)
+    cudaStream_t st = c.stream;
+    if (!c.widePrimary) {
+        if (!c.wideStream) {
+            RTRT_CUDA(c, cudaStreamCreateWithFlags(&c.wideStream, cudaStreamNonBlocking));
+            RTRT_CUDA(c, cudaEventCreateWithFlags(&c.evWideFork, cudaEventDisableTiming));
+            RTRT_CUDA(c, cudaEventCreateWithFlags(&c.evWideDone, cudaEventDisableTiming));
+        }
+        RTRT_CUDA(c, cudaEventRecord(c.evWideFork, c.stream));
+        RTRT_CUDA(c, cudaStreamWaitEvent(c.wideStream, c.evWideFork, 0));
+        st = c.wideStream;
+    }
+    RTRT_CUDA(c, cudaMemsetAsync(p.stat, 0, 64, st));
+    k_wide_blas<<<B, kWbThreads, 0, st>>>(p);
     WideBuildParams pt = p;
     pt.binNodes = reinterpret_cast<const float4*>(c.dTlasNodes);
-    k_wide_tlas<<<1, kWtThreads, 0, c.stream>>>(pt);
+    k_wide_tlas<<<1, kWtThreads, 0, st>>>(pt);
+    if (st != c.stream) { RTRT_CUDA(c, cudaEventRecord(c.evWideDone, st)); c.widePending = true; }
     c.launches += 2;
     c.wideRoot = p.tlasBase;
     c.wideValid = true; c.wideStatPending = true;
@@ -318,8 +332,14 @@ int launch_wide_build(Context& c) {
 }
 
 // after a stream synchronisation: error flags of the last wide build (region overflow / triangle count mismatch)
+int wide_join(Context& c) {
+    if (c.widePending) { RTRT_CUDA(c, cudaStreamWaitEvent(c.stream, c.evWideDone, 0)); c.widePending = false; }
+    return RTRT_OK;
+}
+
 int check_wide_error(Context& c) {
     if (!c.wideStatPending || !c.dWideQueue) return RTRT_OK;
+    if (c.wideStream) RTRT_CUDA(c, cudaStreamSynchronize(c.wideStream));
     c.wideStatPending = false;
     const uint32_t tlasCap = 2u * c.numBatches + 8u;
     uint32_t st[4] = {0, 0, 0, 0};
