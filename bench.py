@@ -168,7 +168,7 @@ def run_reference(args, rank, world):
         return
     pkg = importlib.import_module(PKG)
     arm = CpuArm(pkg)
-    val, ms, cb = arm.baseline(steps=args.steps, warmup=min(args.warmup, 1))
+    val, ms, cb = arm.baseline(steps=args.steps, warmup=args.warmup)
     line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": arm.sample},

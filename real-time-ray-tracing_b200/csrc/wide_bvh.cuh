@@ -159,6 +159,9 @@ __device__ __forceinline__ uint2 wide_pop(const WideStack& st, WideState& s) {
 #ifndef RTRT_WIDE_TRI_DEN
 #define RTRT_WIDE_TRI_DEN 8
 #endif
+#ifndef RTRT_WIDE_TRI_MUST
+#define RTRT_WIDE_TRI_MUST 1
+#endif
 __device__ __forceinline__ uint2 wide_peek(const WideStack& st, const WideState& s) {
     const int i = s.sp - 1;
     return i < kWideStackSmem ? st.smem[i * st.stride] : st.spill[i - kWideStackSmem];
@@ -218,7 +221,13 @@ __device__ __forceinline__ bool wide_step(const WideView& wv, const WideRay& w, 
     const bool must = want && s.ngroup.y <= 0x00FFFFFFu;                      // (after the fetch) nothing but triangles left to do
     const unsigned wm = __ballot_sync(full, want), mm = __ballot_sync(full, must), am = __ballot_sync(full, active);
     bool finished = false;
-    if (wm != 0u && (mm != 0u || __popc(wm) * RTRT_WIDE_TRI_DEN >= __popc(am) * RTRT_WIDE_TRI_NUM)) {
+#if RTRT_WIDE_TRI_MUST
+    const bool force = mm != 0u;                                              // a lane with nothing but triangles left forces the phase
+#else
+    const bool force = __ballot_sync(full, active && s.ngroup.y > 0x00FFFFFFu) == 0u;   // ... only when NO lane has node work left: lanes that can only
+                                                                              // test triangles wait for company instead of running the test with a few lanes
+#endif
+    if (wm != 0u && (force || __popc(wm) * RTRT_WIDE_TRI_DEN >= __popc(am) * RTRT_WIDE_TRI_NUM)) {
         if (want) {
             const RayPrep rp = wide_tri_prep(w);
             const uint32_t bit = 31u - (uint32_t)__clz(s.tgroup.y);
