@@ -23,6 +23,7 @@ static void dfree(T*& p) { if (p) cudaFree(p); p = nullptr; }
 
 static void free_mesh(Context& c) {
     if (c.wideStream) cudaStreamSynchronize(c.wideStream);
+    if (c.wideTlasStream) cudaStreamSynchronize(c.wideTlasStream);
     c.widePending = false;
     if (c.ownsMesh) { dfree(c.dPos); dfree(c.dNrm); dfree(c.dIdx); }
     c.dPos = nullptr; c.dNrm = nullptr; c.dIdx = nullptr; c.ownsMesh = false;
@@ -172,6 +173,9 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     if (c.evWideFork) cudaEventDestroy(c.evWideFork);
     if (c.evWideDone) cudaEventDestroy(c.evWideDone);
     if (c.wideStream) cudaStreamDestroy(c.wideStream);
+    if (c.evTlasFork) cudaEventDestroy(c.evTlasFork);
+    if (c.evTlasDone) cudaEventDestroy(c.evTlasDone);
+    if (c.wideTlasStream) cudaStreamDestroy(c.wideTlasStream);
     for (cudaEvent_t e : {c.evGeomReady, c.evGeomFree, c.evStaged, c.evReadDone}) if (e) cudaEventDestroy(e);
     if (c.copyStream) cudaStreamDestroy(c.copyStream);
     if (c.uploadStream) cudaStreamDestroy(c.uploadStream);

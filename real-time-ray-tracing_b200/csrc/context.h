@@ -41,6 +41,7 @@ struct Context {
     bool wideBvh = false, wideValid = false, wideStatPending = false;
     // wide_bvh = 2: the collapse to the wide layout runs on a side stream, concurrently with the primary-ray kernels (which then do not need it)
     cudaStream_t wideStream = nullptr; cudaEvent_t evWideFork = nullptr, evWideDone = nullptr; bool widePending = false;
+    cudaStream_t wideTlasStream = nullptr; cudaEvent_t evTlasFork = nullptr, evTlasDone = nullptr;   // the top-level collapse runs beside the batches' collapse
     bool widePrimary = true;                              // option wide_bvh = 2: primary rays keep the reference layout (coherent rays: its two-child nodes hit L1), bounce rays the wide one
     void* dWideNodes = nullptr; void* dWideTris = nullptr; void* dWideQueue = nullptr; size_t wideNodeCap = 0;
     uint32_t wideRoot = 0, wideNodes = 0;

@@ -30,7 +30,7 @@ namespace rtrt {
 constexpr int kTraceThreads = RTRT_TRACE_THREADS;
 constexpr int kLogicThreads = RTRT_LOGIC_THREADS;
 #ifndef RTRT_PRIMARY_MINB
-#define RTRT_PRIMARY_MINB 1
+#define RTRT_PRIMARY_MINB 14       // <= 72 registers for the wide layout's primary kernel (96 unbounded): 0.670 -> 0.644 ms (12: 0.655); the reference layout's needs 64 anyway
 #endif
 #ifndef RTRT_TRACE_MINB
 #define RTRT_TRACE_MINB 6        // measured: 2.80 -> 2.73 ms per path-traced 1080p frame against no bound (4, 5: no change; 8: 2.75)

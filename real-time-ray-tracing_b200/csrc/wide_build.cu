@@ -15,7 +15,10 @@
 
 namespace rtrt {
 
-constexpr int kWbThreads = 256;                          // k_wide_blas: 32 groups of 8 lanes
+#ifndef RTRT_WB_THREADS
+#define RTRT_WB_THREADS 256
+#endif
+constexpr int kWbThreads = RTRT_WB_THREADS;              // k_wide_blas: groups of 8 lanes, one wide node per group and round
 constexpr int kWtThreads = 1024;                         // k_wide_tlas: 128 groups
 constexpr uint32_t kCopyFlag = 0x80000000u;              // queue entry: "copy the wide root of batch (link & ~flag)"
 enum { K_EMPTY = 0, K_INNER = 1, K_LEAF = 2, K_BATCH = 3 };
@@ -87,11 +90,7 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
     WideEntry e{};
     if (valid) e = queue[w];
     float4* outNode = p.nodes + (size_t)(regionBase + w) * kWideStride;
-    if (TLAS && valid && (e.link & kCopyFlag)) {           // top-level leaf: the node is the batch's wide root, children / triangles stay where they are
-        const float4* src = p.nodes + (size_t)((e.link & ~kCopyFlag) * (uint32_t)kWideRegion) * kWideStride;
-        outNode[g] = __ldcg(src + g);
-        valid = false;
-    }
+    if (TLAS && valid && (e.link & kCopyFlag)) valid = false;      // top-level leaf: the node is a copy of the batch's wide root (k_wide_copy, once both trees exist)
     Slot s; s.kind = K_EMPTY; s.idx = 0; s.f = 0; s.l = 0;
     for (int a = 0; a < 3; ++a) { s.lo[a] = 0.0f; s.hi[a] = 0.0f; }
     int nSlots = 0;
@@ -112,6 +111,7 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
             const float ob = __shfl_xor_sync(full, best, o); const int ow = __shfl_xor_sync(full, who, o);
             if (ob > best || (ob == best && ow < who)) { best = ob; who = ow; }
         }
+        if (!__any_sync(full, valid && best >= 0.0f && nSlots < 8)) break;     // no group of this warp has an inner child left to open
         const uint32_t widx = __shfl_sync(full, s.idx, gb + who), wf = __shfl_sync(full, s.f, gb + who), wl = __shfl_sync(full, s.l, gb + who);
         if (valid && best >= 0.0f && nSlots < 8) {
             float4 rec[4];
@@ -126,16 +126,24 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
     const float cx = (s.lo[0] + s.hi[0]) - (e.lo[0] + e.hi[0]), cy = (s.lo[1] + s.hi[1]) - (e.lo[1] + e.hi[1]), cz = (s.lo[2] + s.hi[2]) - (e.lo[2] + e.hi[2]);
     int mySlot = -1;
     uint32_t freeMask = 0xFFu;
+    // the child's score for each of the 8 slots does not change between the rounds of the auction (only the free mask does): computed once
+    float sc[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        float c = ((t & 4) ? cx : -cx) + ((t & 2) ? cy : -cy) + ((t & 1) ? cz : -cz);
+        if (!(c == c)) c = 0.0f;                                          // a NaN box must not lose its child
+        sc[t] = c;
+    }
+    const bool bidder = valid && s.kind != K_EMPTY;
+    const int rounds = __shfl_sync(full, nSlots, gb);                     // one child is placed per round
 #pragma unroll 1
     for (int it = 0; it < 8; ++it) {
+        if (__all_sync(full, it >= rounds)) break;
         float best = -3.0e38f; int bs = 0;
-        if (valid && s.kind != K_EMPTY && mySlot < 0) {
+        if (bidder && mySlot < 0) {
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                float c = ((t & 4) ? cx : -cx) + ((t & 2) ? cy : -cy) + ((t & 1) ? cz : -cz);
-                if (!(c == c)) c = 0.0f;                                  // a NaN box must not lose its child
-                if (((freeMask >> t) & 1u) && c > best) { best = c; bs = t; }
-            }
+            for (int t = 0; t < 8; ++t)
+                if (((freeMask >> t) & 1u) && sc[t] > best) { best = sc[t]; bs = t; }
         }
         int who = g; float wb = best;
 #pragma unroll
@@ -282,6 +290,17 @@ __global__ void __launch_bounds__(kWtThreads) k_wide_tlas(const WideBuildParams 
     if (threadIdx.x == 0) { p.stat[2] = tail; atomicAdd(p.stat + 1, tail); }
 }
 
+// Top-level leaves: node = the wide root of the batch (its children / triangles stay where they are).  Runs after BOTH collapses, so that the
+// top-level tree (one CTA, ~0.1 ms of dependent steps) is collapsed CONCURRENTLY with the batches instead of behind them.
+__global__ void __launch_bounds__(256) k_wide_copy(const WideBuildParams p) {
+    const uint32_t w = (blockIdx.x * 256u + threadIdx.x) >> 3, g = threadIdx.x & 7u;
+    if (w >= p.stat[2]) return;
+    const uint32_t link = p.tlasQueue[w].link;
+    if (!(link & kCopyFlag)) return;
+    const float4* src = p.nodes + (size_t)((link & ~kCopyFlag) * (uint32_t)kWideRegion) * kWideStride;
+    p.nodes[(size_t)(p.tlasBase + w) * kWideStride + g] = __ldcg(src + g);
+}
+
 int launch_wide_build(Context& c) {
     const uint32_t B = c.numBatches;
     const uint32_t tlasCap = 2u * B + 8u;
@@ -318,13 +337,23 @@ int launch_wide_build(Context& c) {
         RTRT_CUDA(c, cudaStreamWaitEvent(c.wideStream, c.evWideFork, 0));
         st = c.wideStream;
     }
+    if (!c.wideTlasStream) {
+        RTRT_CUDA(c, cudaStreamCreateWithFlags(&c.wideTlasStream, cudaStreamNonBlocking));
+        RTRT_CUDA(c, cudaEventCreateWithFlags(&c.evTlasFork, cudaEventDisableTiming));
+        RTRT_CUDA(c, cudaEventCreateWithFlags(&c.evTlasDone, cudaEventDisableTiming));
+    }
     RTRT_CUDA(c, cudaMemsetAsync(p.stat, 0, 64, st));
-    k_wide_blas<<<B, kWbThreads, 0, st>>>(p);
+    RTRT_CUDA(c, cudaEventRecord(c.evTlasFork, st));
+    RTRT_CUDA(c, cudaStreamWaitEvent(c.wideTlasStream, c.evTlasFork, 0));
     WideBuildParams pt = p;
     pt.binNodes = reinterpret_cast<const float4*>(c.dTlasNodes);
-    k_wide_tlas<<<1, kWtThreads, 0, st>>>(pt);
+    k_wide_tlas<<<1, kWtThreads, 0, c.wideTlasStream>>>(pt);                     // beside the batches
+    RTRT_CUDA(c, cudaEventRecord(c.evTlasDone, c.wideTlasStream));
+    k_wide_blas<<<B, kWbThreads, 0, st>>>(p);
+    RTRT_CUDA(c, cudaStreamWaitEvent(st, c.evTlasDone, 0));
+    k_wide_copy<<<(tlasCap * 8u + 255u) / 256u, 256, 0, st>>>(p);
     if (st != c.stream) { RTRT_CUDA(c, cudaEventRecord(c.evWideDone, st)); c.widePending = true; }
-    c.launches += 2;
+    c.launches += 3;
     c.wideRoot = p.tlasBase;
     c.wideValid = true; c.wideStatPending = true;
     RTRT_CUDA(c, cudaGetLastError());

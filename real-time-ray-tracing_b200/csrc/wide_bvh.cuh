@@ -36,7 +36,11 @@ namespace rtrt {
 
 constexpr int kWideStride = 8;                   // float4 rows per node (128 B)
 constexpr int kWideRegion = 512;                 // node slots reserved per 1024-triangle batch (bound: see wide_build.cu)
-constexpr int kWideMaxLeaf = 3;                  // triangles per leaf slot
+#ifndef RTRT_WIDE_MAX_LEAF
+#define RTRT_WIDE_MAX_LEAF 1      // measured on the bench frame, 3 -> 2 -> 1: triangle tests per bounce ray 6.9 -> 5.1 -> 3.4, node visits 23.0 -> 23.5 -> 24.1,
+                                  // path trace 2.29 -> 2.20 -> 2.12 ms, collapse 0.22 -> 0.24 -> 0.29 ms: the ~100-instruction triangle test runs with few lanes
+#endif
+constexpr int kWideMaxLeaf = RTRT_WIDE_MAX_LEAF;  // triangles per leaf slot (<= 3: the meta byte has three triangle bits)
 constexpr int kWideStackSmem = 16;               // stack entries per thread in shared memory (8 B each: the reference stack's footprint) ...
 constexpr int kWideStackSpill = 48;              // ... and in local memory behind them (short shared stack with spill)
 
