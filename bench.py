@@ -658,6 +658,30 @@ def main():
     # untimed: the ceilings a traversal without RT cores runs against on this GPU (csrc/microbench.cu)
     mb = rt.microbench() if rank == 0 else None
 
+    # ---- the other traversal layout on the same workload (N = 1): both modes in one line ----
+    other_layout = None
+    if world == 1:
+        rt.set_option("wide_bvh", 0 if wide else 1)
+        for _ in range(3):
+            step_device(None)
+        torch.cuda.synchronize()
+        ev, r0 = [], rt.timings()["rays_traced_total"]
+        n_other = max(5, args.steps // 3)
+        for _ in range(n_other):
+            with torch.cuda.stream(stream):
+                flush.zero_()
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+            step_device(e); ev.append(e)
+        torch.cuda.synchronize()
+        o_ms = float(np.sum([e[0].elapsed_time(e[5]) for e in ev])) / n_other
+        o_rays = (rt.timings()["rays_traced_total"] - r0) / n_other
+        other_layout = {"layout": "reference" if wide else "wide", "steps": n_other, "ms_per_step": o_ms, "value": o_rays / (o_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                        "stages_ms": {k: float(np.mean([e[i].elapsed_time(e[i + 1]) for e in ev])) for i, k in ((0, "build_bvh"), (1, "pathtrace"), (3, "denoise"))},
+                        "note": "reference = the reference's node / triangle arrays walked with its loop, caps and quirks (per-ray hits bit-identical to it); "
+                                "wide = 8-wide fp16 layout derived from them inside every build"}
+        rt.set_option("wide_bvh", int(wide))
+        rt.build_bvh()
+
     # ---- strong-scaling sub-records (fixed total work): ONE C2 frame sharded by rows, and BASELINE config 5 at 64 spp ----
     strong = None
     if not args.no_strong:
@@ -800,6 +824,7 @@ def main():
                             "copies overlap the neighbouring frames' kernels; one timed region over all steps, L2 flushes included"},
             "microbench": mb,
             "last_frame_sha1": frame_sha1,
+            "other_layout": other_layout,
             "strong": strong,
             "other_configs": configs,
             "gpu_launches": int(launches),
