@@ -193,7 +193,10 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
     if (!TLAS && cnt) for (uint32_t k = 0; k < cnt; ++k) triSrc[triBase + triOff + k] = (uint16_t)(c.f + k);
     // ---- child planes relative to the node origin in units of the per-axis scale, as fp16: lo rounded down, hi rounded up (the difference
     // and the power-of-two scaling are evaluated in double; both roundings go the conservative way) ----
-    const uint32_t ex = exp_byte(e.hi[0] - e.lo[0]), ey = exp_byte(e.hi[1] - e.lo[1]), ez = exp_byte(e.hi[2] - e.lo[2]);
+    // extent rounded UP (the float difference may round down onto a power of two that is then smaller than the true extent: the far planes of a
+    // child touching the parent's hi side would be clamped to 1.0 = below the child — found by tests/test_wide_bvh_gpu.py's enclosure check)
+    const uint32_t ex = exp_byte(__double2float_ru((double)e.hi[0] - (double)e.lo[0])), ey = exp_byte(__double2float_ru((double)e.hi[1] - (double)e.lo[1])),
+                   ez = exp_byte(__double2float_ru((double)e.hi[2] - (double)e.lo[2]));
     const uint32_t eb[3] = {ex, ey, ez};
     uint8_t* ob = reinterpret_cast<uint8_t*>(outNode);
     __half* oh = reinterpret_cast<__half*>(outNode);

@@ -149,6 +149,19 @@ def _nccl_worker(rank, world, port, out_dir):
         rt = pkg.RayTracer(W, H, device=rank).init(); rt.set_mesh(pos, idx, nrm)
         mg = pkg.parallel.MultiGpuRayTracer.bootstrap(rt, mode="rows")
         full = pkg.RayTracer(W, H, device=rank).init(); full.set_mesh(pos, idx, nrm)
+        # rtrt_create_multi = rtrt_create + rtrt_multi_init in one call (a second communicator on the same GPUs); a bad rank is an error, not a hang
+        import ctypes as C
+        box = [pkg.parallel.MultiGpuRayTracer.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        h = C.c_void_p()
+        cfg = pkg.config_defaults(); cfg.width, cfg.height = W, H
+        buf = (C.c_ubyte * 128).from_buffer_copy(box[0])
+        lib = pkg._lib.load()
+        assert lib.rtrt_create_multi(C.byref(cfg), rank, buf, world, world, C.byref(h)) == -1 and not h       # rank out of range -> RTRT_ERR_ARG
+        assert lib.rtrt_create_multi(C.byref(cfg), rank, buf, rank, world, C.byref(h)) == 0 and h
+        b, e = C.c_int32(), C.c_int32()
+        assert lib.rtrt_multi_get_band(h, C.byref(b), C.byref(e), None, None) == 0 and (b.value, e.value) == pkg.parallel.band_bounds(H, world)[rank]
+        assert lib.rtrt_destroy(h) == 0
         for frame in range(1, 5):
             cam = pkg.scenes.make_camera((0.3 * frame, 30, -60 + 0.2 * frame), 0.01 * frame, -0.4, W, H)
             rt.set_camera(cam, reset_history=(frame == 1))
