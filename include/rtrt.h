@@ -76,7 +76,8 @@ typedef struct rtrt_timings {
     float pt_kernel_ms[6];
     /* option "count_visits" = 1: node visits / leaf tests of the bounce rounds 1..4 of the last rtrt_pathtrace */
     uint32_t round_node_visits[4], round_leaf_tests[4], round_rays[4];
-    uint32_t reserved_;
+    float wide_build_ms;          /* option wide_bvh: the collapse to the wide layout inside the last rtrt_build_bvh (build_bvh_ms then covers the LBVH build only;
+                                     0 when the collapse ran on the side stream, wide_bvh = 2) */
 } rtrt_timings;
 
 /* Buffers observable through rtrt_get_buffer.  The first block are the DebugPrintFile observation

@@ -48,7 +48,7 @@ class Timings(C.Structure):
                 ("denoise_ms", C.c_float), ("kernel_launches", C.c_uint64), ("rays_traced", C.c_uint64),
                 ("node_visits", C.c_uint64), ("leaf_tests", C.c_uint64), ("rays_traced_total", C.c_uint64),
                 ("pt_kernel_ms", C.c_float * 6), ("round_node_visits", C.c_uint32 * 4), ("round_leaf_tests", C.c_uint32 * 4),
-                ("round_rays", C.c_uint32 * 4), ("reserved_", C.c_uint32)]
+                ("round_rays", C.c_uint32 * 4), ("wide_build_ms", C.c_float)]
 
 
 class SkyParams(C.Structure):      # src/settingParams.h:41-45

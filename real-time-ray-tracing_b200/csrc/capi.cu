@@ -167,6 +167,7 @@ int rtrt_destroy(rtrt_ctx* ctx) {
     dfree(c.dRayStage); dfree(c.dHitStage); dfree(c.dTicket);
     for (auto& e : c.ev) { if (e[0]) cudaEventDestroy(e[0]); if (e[1]) cudaEventDestroy(e[1]); }
     for (auto& e : c.kev) if (e) cudaEventDestroy(e);
+    if (c.evWideBegin) cudaEventDestroy(c.evWideBegin);
     for (auto& st : c.chunkStream) if (st) cudaStreamDestroy(st);
     for (auto& ev : c.chunkJoin) if (ev) cudaEventDestroy(ev);
     if (c.chunkFork) cudaEventDestroy(c.chunkFork);
@@ -307,7 +308,13 @@ int rtrt_build_bvh(rtrt_ctx* ctx) {
     int rc = launch_build_bvh(c);
     if (rc) return rc;
     c.wideValid = false;
-    if (c.wideBvh) { rc = launch_wide_build(c); if (rc) return rc; }     // part of the build (and of its time) when the option is on
+    c.evWidePending = false;
+    if (c.wideBvh) {                                                      // part of rtrt_build_bvh when the option is on; timed separately (wide_build_ms)
+        if (!c.evWideBegin) RTRT_CUDA(c, cudaEventCreate(&c.evWideBegin));
+        RTRT_CUDA(c, cudaEventRecord(c.evWideBegin, c.stream));
+        c.evWidePending = c.widePrimary;                                  // wide_bvh = 2: the collapse is on the side stream, outside this stage
+        rc = launch_wide_build(c); if (rc) return rc;
+    }
     RTRT_CUDA(c, cudaEventRecord(c.ev[STAGE_BUILD][1], c.stream));
     c.bvhValid = true;
     c.evPending[STAGE_BUILD] = true;    // resolved lazily in rtrt_get_timings
@@ -481,6 +488,16 @@ int rtrt_get_timings(rtrt_ctx* ctx, rtrt_timings* out) {
         if (c.evPending[s]) {
             float ms = 0.0f;
             *slots[s] = (cudaEventElapsedTime(&ms, c.ev[s][0], c.ev[s][1]) == cudaSuccess) ? ms : 0.0f;
+            if (s == STAGE_BUILD) {
+                c.timings.wide_build_ms = 0.0f;
+                if (c.evWidePending) {                                    // split the stage: LBVH build | collapse to the wide layout
+                    float lb = 0.0f, wb = 0.0f;
+                    if (cudaEventElapsedTime(&lb, c.ev[s][0], c.evWideBegin) == cudaSuccess && cudaEventElapsedTime(&wb, c.evWideBegin, c.ev[s][1]) == cudaSuccess) {
+                        c.timings.build_bvh_ms = lb; c.timings.wide_build_ms = wb;
+                    }
+                    c.evWidePending = false;
+                }
+            }
             c.evPending[s] = false;
         }
     if (c.raysOnDevice && c.dRayCounter) {

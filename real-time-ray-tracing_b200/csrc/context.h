@@ -109,6 +109,7 @@ struct Context {
     // ---- bookkeeping ----
     unsigned long long launches = 0;                     // kernels launched by this library
     cudaEvent_t ev[4][2] = {};                           // [build, traverse, pathtrace, denoise][begin, end]
+    cudaEvent_t evWideBegin = nullptr; bool evWidePending = false;   // between the LBVH build and the wide collapse of rtrt_build_bvh
     bool evPending[4] = {false, false, false, false};
     bool kernelTiming = false; cudaEvent_t kev[7] = {}; bool kevPending = false;   // option kernel_timing: boundaries of the path-trace kernels
     bool raysOnDevice = false;                           // rays_traced of the last pathtrace still in dRayCounter
