@@ -3,9 +3,9 @@
 OUT=gpurun_out; mkdir -p $OUT
 nvidia-smi --query-gpu=index,name --format=csv,noheader
 timeout 600 python -m pytest tests/test_multi_gpu.py tests/test_parallel_gpu.py -x -q -m gpu 2>&1 | tail -8
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 > $OUT/r2h_bench_n2.json 2> $OUT/r2h_bench_n2.err; echo "bench n2 exit $?"
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 > $OUT/r2h_bench_n2.json 2> $OUT/r2h_bench_n2.err; echo "bench n2 exit $?"
 tail -5 $OUT/r2h_bench_n2.err
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 10 --warmup 3 --mode rows --no-strong > $OUT/r2h_bench_n2_rows.json 2> $OUT/r2h_bench_n2_rows.err; echo "bench n2 rows exit $?"
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --mode rows --no-strong > $OUT/r2h_bench_n2_rows.json 2> $OUT/r2h_bench_n2_rows.err; echo "bench n2 rows exit $?"
 tail -5 $OUT/r2h_bench_n2_rows.err
 python - <<'PY'
 import json
