@@ -199,7 +199,7 @@ int rtrt_set_option_i(rtrt_ctx* ctx, const char* name, int64_t value);
 /*   "keep_presort_morton" 0/1  : also fill RTRT_BUF_*MORTON_PRESORT (debug observation point)
  *   "wide_bvh"            0/1  : traversal layout.  0 = the reference's arrays (64-byte two-child nodes, one 128-byte triangle per leaf),
  *                                traversed with the reference's loop, caps and quirks: per-ray (tri, t, u, v) bit-identical to it.
- *                                1 = rtrt_build_bvh additionally derives an 8-wide BVH with 8-bit quantised child boxes (one 128-byte line
+ *                                1 = rtrt_build_bvh additionally derives an 8-wide BVH with fp16 child boxes relative to the node box (one 128-byte line
  *                                per visit) and 48-byte triangles from those arrays (they stay available and bit-exact), and rtrt_traverse /
  *                                rtrt_pathtrace use it: same watertight triangle test on the same vertex bits, conservative box test, spill
  *                                stack and no iteration cap -> (tri, t) bit-identical to the reference's search on every ray where the

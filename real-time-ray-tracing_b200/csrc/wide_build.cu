@@ -6,7 +6,7 @@
 // The binary tree is never re-derived: ranges of sorted positions are carried down with Karras' numbering (the inner left / right
 // children of the node that splits at gamma are nodes gamma / gamma + 1, bvh_block.cuh), which gives every subtree's triangle count
 // for free.  Collapse rule (Ylitie et al. 2017, section 4.1, greedy form): start from the two children of the binary node, keep
-// opening the inner child with the largest surface area until there are 8 children; subtrees of <= 3 triangles are leaves.
+// opening the inner child with the largest surface area until there are 8 children; subtrees of <= kWideMaxLeaf triangles (1 since round 2, the format allows 3) are leaves.
 // Nodes are allocated breadth-first from a per-batch region (inner children of a node are consecutive), triangles are copied
 // (positions only, original index in row0.w) in the order the leaves were allocated, so a node's leaf triangles are consecutive too.
 #include "wide_bvh.cuh"
@@ -20,6 +20,9 @@ namespace rtrt {
 #endif
 constexpr int kWbThreads = RTRT_WB_THREADS;              // k_wide_blas: groups of 8 lanes, one wide node per group and round
 constexpr int kWtThreads = 1024;                         // k_wide_tlas: 128 groups
+#ifndef RTRT_WIDE_PACK_LEAVES
+#define RTRT_WIDE_PACK_LEAVES 0      // measured, see wide_process: fewer nodes (321 k -> 248 k) but MORE visits per ray (24.1 -> 26.9), bounce round 0.85 -> 0.91 ms
+#endif
 constexpr uint32_t kCopyFlag = 0x80000000u;              // queue entry: "copy the wide root of batch (link & ~flag)"
 enum { K_EMPTY = 0, K_INNER = 1, K_LEAF = 2, K_BATCH = 3 };
 
@@ -102,9 +105,18 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
         nSlots = singleLeaf ? 1 : 2;
     }
     // ---- open the inner child with the largest surface area until 8 slots are in use ----
+    // Leaf packing (RTRT_WIDE_PACK_LEAVES, off): a node over more than 8 items (triangles / batches) only opens children that themselves hold more than 8,
+    // so every maximal subtree of <= 8 items becomes ONE node whose slots are its items.  Pure largest-area opening gives 4.3 children per node
+    // (3.3 triangles + 1.0 inner) on the bench scene, packing 5.3 — but packed triangles always sit one level lower, in nodes of their own, whereas the
+    // mixed nodes of the greedy collapse let a ray test triangle boxes and inner boxes in one visit: measured slower (tools/gpu_r2w.sh).
+    const bool smallNode = (e.l - e.f + 1u) <= 8u;
 #pragma unroll 1
     for (int it = 0; it < 6; ++it) {
+#if RTRT_WIDE_PACK_LEAVES
+        float best = (valid && s.kind == K_INNER && (smallNode || (s.l - s.f + 1u) > 8u)) ? box_area(s) : -1.0f;
+#else
         float best = (valid && s.kind == K_INNER) ? box_area(s) : -1.0f;
+#endif
         int who = g;
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) {

@@ -4,8 +4,8 @@
 // Why: B200 has no RT cores.  The reference's layout (src/bvhNode.cuh:5-13: 64-byte two-child nodes, src/geometry.h:52-97: 128-byte
 // triangles, ONE triangle per leaf; loop src/traverse.h:132-250) costs ~70 dependent node fetches + 3.3 leaf fetches per incoherent
 // ray on the 1 M-triangle bench scene, and that chain — not bandwidth — bounds the path tracer (profiles/r1j_ncu_summary.md).
-// An 8-wide node answers three binary levels with ONE cache line, leaves hold up to 3 triangles, and the whole node array of the bench
-// scene is ~9 MB (vs 64 MB), i.e. it lives in L2.
+// An 8-wide node answers three binary levels with ONE cache line, a leaf slot holds one triangle (kWideMaxLeaf), and the whole node array of the bench
+// scene is 41 MB (+ 50 MB of 48-byte triangles; the reference layout's traversal reads 64 + 134 MB), i.e. it lives in the 126 MB L2.
 //
 // Layout (node = 128 bytes = one L1/L2 line per visit; the slot / octant scheme follows Ylitie, Karras, Laine 2017, "Efficient
 // Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs"):
@@ -149,7 +149,7 @@ __device__ __forceinline__ uint2 wide_pop(const WideStack& st, WideState& s) {
 
 // One traversal step of a whole warp (every lane calls it, `active` = the lane has a ray in flight):
 //   fetch      a lane whose node group is used up takes the next group off its stack;
-//   node       every lane with a pending inner child visits ONE node: 8 quantised box tests -> hit inner children + hit triangles;
+//   node       every lane with a pending inner child visits ONE node: 8 box tests -> hit inner children + hit triangles;
 //   triangles  POSTPONED (Ylitie et al. 2017, section 5.2): the hit triangles of a node wait in the lane's pending group (an older
 //              pending group goes onto the stack) and are tested, one per lane and step, only when the warp votes that enough lanes
 //              have one pending (>= RTRT_WIDE_TRI_NUM / RTRT_WIDE_TRI_DEN of the lanes in flight), or when some lane has nothing else
