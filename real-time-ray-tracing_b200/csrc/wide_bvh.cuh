@@ -5,7 +5,7 @@
 // triangles, ONE triangle per leaf; loop src/traverse.h:132-250) costs ~70 dependent node fetches + 3.3 leaf fetches per incoherent
 // ray on the 1 M-triangle bench scene, and that chain — not bandwidth — bounds the path tracer (profiles/r1j_ncu_summary.md).
 // An 8-wide node answers three binary levels with ONE cache line, a leaf slot holds one triangle (kWideMaxLeaf), and the whole node array of the bench
-// scene is 41 MB (+ 50 MB of 48-byte triangles; the reference layout's traversal reads 64 + 134 MB), i.e. it lives in the 126 MB L2.
+// scene is 28 MB (+ 50 MB of 48-byte triangles; the reference layout's traversal reads 64 + 134 MB), i.e. it lives in the 126 MB L2.
 //
 // Layout (node = 128 bytes = one L1/L2 line per visit; the slot / octant scheme follows Ylitie, Karras, Laine 2017, "Efficient
 // Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs"):

@@ -15,14 +15,14 @@ for k, v in [a.split("=") for a in sys.argv[1:]]:
 rt.set_option("kernel_timing", 1)
 stream = torch.cuda.ExternalStream(rt.stream)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-rows, builds = [], []
+rows, builds, wides = [], [], []
 for i in range(14):
     with torch.cuda.stream(stream): flush.zero_()
     rt.build_bvh(); rt.set_frame_number(2 + i); rt.pathtrace()
     t = rt.timings()
-    rows.append(t["pt_kernel_ms"] + [t["pathtrace_ms"]]); builds.append(t["build_bvh_ms"])
+    rows.append(t["pt_kernel_ms"] + [t["pathtrace_ms"]]); builds.append(t["build_bvh_ms"]); wides.append(t["wide_build_ms"])
 m = np.median(np.asarray(rows[2:]), axis=0)
 rt.set_option("count_visits", 1); rt.set_frame_number(2); rt.pathtrace(); t = rt.timings()
-print(os.path.basename(os.environ.get("RTRT_LIB", "in-tree")), " ".join(sys.argv[1:]), "| build %.3f | primary %.3f logic1 %.3f trace1 %.3f logic %.3f trace2 %.3f rest %.3f | pathtrace %.3f ms | r1 visits/ray %.1f tris/ray %.1f" %
-      (float(np.median(builds[2:])), m[0], m[1], m[2], m[3], m[4], m[5], m[6], t["round_node_visits"][0] / max(t["round_rays"][0], 1), t["round_leaf_tests"][0] / max(t["round_rays"][0], 1)), flush=True)
+print(os.path.basename(os.environ.get("RTRT_LIB", "in-tree")), " ".join(sys.argv[1:]), "| build %.3f + collapse %.3f | primary %.3f logic1 %.3f trace1 %.3f logic %.3f trace2 %.3f rest %.3f | pathtrace %.3f ms | r1 visits/ray %.1f tris/ray %.1f" %
+      (float(np.median(builds[2:])), float(np.median(wides[2:])), m[0], m[1], m[2], m[3], m[4], m[5], m[6], t["round_node_visits"][0] / max(t["round_rays"][0], 1), t["round_leaf_tests"][0] / max(t["round_rays"][0], 1)), flush=True)
 rt.cleanup()
