@@ -446,7 +446,13 @@ int rtrt_multi_link_local(rtrt_ctx** ctxs, int n) {
     for (int i = 0; i < n; ++i) {
         Multi* m = new Multi(); m->rank = i; m->world = n; m->local = g;
         int rc = attach(ctxs[i]->c, m);
-        if (rc) { delete m; for (int j = 0; j < i; ++j) { g->refs = 1; multi_release(ctxs[j]->c); } return rc; }
+        if (rc) {                                               // undo: the i contexts attached so far leave the group, the last one frees it
+            delete m;
+            g->refs = i;
+            if (i == 0) delete g;
+            for (int j = 0; j < i; ++j) multi_release(ctxs[j]->c);
+            return rc;
+        }
     }
     return RTRT_OK;
 }
