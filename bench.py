@@ -772,8 +772,10 @@ def main():
         clk = sampler.summary()["sm_mhz"] or sampler.summary()["sm_max_mhz"] or 1965.0
         issue_peak = props.multi_processor_count * 4 * clk * 1e6 / 1e9                 # G warp-instructions / s
         issue_ach = (winst / (tr_ms * 1e-3) / 1e9) if (winst and tr_ms > 0) else None
-        trace_roofline = {"kernel": "k_pt_trace, bounce round 1 (%.0f%% of the step)" % (100 * tr_ms / max(ms_step, 1e-9)), "bound": "issue",
-                          "achieved": issue_ach, "peak": issue_peak, "unit": "Gwarp-inst/s", "frac": (issue_ach / issue_peak) if issue_ach else None,
+        have_inst = issue_ach is not None      # no committed ncu instruction count for this layout: fall back to the L2-bandwidth ceiling
+        trace_roofline = {"kernel": "k_pt_trace, bounce round 1 (%.0f%% of the step)" % (100 * tr_ms / max(ms_step, 1e-9)), "bound": "issue" if have_inst else "l2",
+                          "achieved": issue_ach if have_inst else tr_gbs, "peak": issue_peak if have_inst else l2_peak, "unit": "Gwarp-inst/s" if have_inst else "GB/s",
+                          "frac": (issue_ach / issue_peak) if have_inst else (tr_gbs / l2_peak if l2_peak else None),
                           "peak_kind": "1 warp instruction per SM sub-partition and clock: %d SMs x 4 x %.0f MHz (clock sampled under load); instruction count per launch "
                                        "from the committed ncu capture of this command (profiles/ncu_traffic.json)" % (props.multi_processor_count, clk),
                           "warp_instructions_per_launch": winst, "lanes_per_instruction": ncu_traffic(tkey, "lanes_per_instruction"),
