@@ -86,6 +86,9 @@ static NcclApi& nccl_api() {
 
 // ------------------------------------------------------------------------------------------------------------------ partition + plans (host)
 enum { X_GBUF = 0, X_HALO = 1, X_FRAME = 2 };
+#ifndef RTRT_MULTI_DIRECT
+#define RTRT_MULTI_DIRECT 1     // 0: every exchange through the pack / unpack kernels (A/B)
+#endif
 constexpr int kGbufReach = 32;                   // rows around the band on which the denoiser reads G-buffers (guide reach of the widest dilated pass)
 
 // bands of whole 16-row tiles; begin[r] .. begin[r + 1]
@@ -119,13 +122,16 @@ static void plan_rows(int height, int world, int stripH, int rank, int peer, int
     }
 }
 
+struct XBufs { unsigned char* ptr[5]; int rowBytes[5]; int n; int rowBytesAll; };
+
 struct XPlan {
     std::vector<int> sendStart, recvStart;       // world + 1 offsets into the concatenated row lists
+    std::vector<int> sendFirst, recvFirst;       // first row of every peer's block
+    bool contiguous = false;                     // every block is ONE range of consecutive rows (halo and frame exchanges: bands are contiguous):
+                                                 // the rows then travel straight between the images, without the pack / unpack kernels
     int* dSendRows = nullptr; int* dRecvRows = nullptr;
     int sendTotal = 0, recvTotal = 0;
 };
-
-struct XBufs { unsigned char* ptr[5]; int rowBytes[5]; int n; int rowBytesAll; };
 
 struct LocalGroup;
 
@@ -138,6 +144,7 @@ struct Multi {
     std::map<int, XPlan> plans;
     unsigned char* sendStage = nullptr; unsigned char* recvStage = nullptr; size_t stageBytes = 0;
     XPlan* current = nullptr; size_t curRowBytes = 0;   // plan / packed row size of the exchange in flight (read by the peers of the in-process transport)
+    XBufs curBufs{};                             // ... and its images (direct exchanges: the peers copy out of them)
     int width = 0, height = 0;                   // frame size the plans were made for
     unsigned long long exchanges = 0, bytesSent = 0;
 };
@@ -170,11 +177,16 @@ static int get_plan(Context& c, Multi& m, int kind, int halo, XPlan** out) {
         XPlan p;
         std::vector<int> send, recv, rows;
         p.sendStart.assign(m.world + 1, 0); p.recvStart.assign(m.world + 1, 0);
+        p.sendFirst.assign(m.world, 0); p.recvFirst.assign(m.world, 0);
+        p.contiguous = kind != X_GBUF;
+        auto one_range = [](const std::vector<int>& r) { return r.empty() || r.back() - r.front() + 1 == (int)r.size(); };
         for (int d = 0; d < m.world; ++d) {
             plan_rows(c.height, m.world, m.stripH, m.rank, d, kind, halo, rows);
             send.insert(send.end(), rows.begin(), rows.end()); p.sendStart[d + 1] = (int)send.size();
+            p.sendFirst[d] = rows.empty() ? 0 : rows.front(); p.contiguous = p.contiguous && one_range(rows);
             plan_rows(c.height, m.world, m.stripH, d, m.rank, kind, halo, rows);
             recv.insert(recv.end(), rows.begin(), rows.end()); p.recvStart[d + 1] = (int)recv.size();
+            p.recvFirst[d] = rows.empty() ? 0 : rows.front(); p.contiguous = p.contiguous && one_range(rows);
         }
         p.sendTotal = (int)send.size(); p.recvTotal = (int)recv.size();
         if (p.sendTotal) {
@@ -250,9 +262,47 @@ static int transport(Context& c, Multi& m, const std::vector<size_t>& sendOff, c
     return RTRT_OK;
 }
 
+// contiguous blocks: rows go straight from the sender's image into the same rows of the receiver's image
+static int exchange_direct(Context& c, Multi& m, XPlan& p, const XBufs& bufs) {
+    m.current = &p; m.curBufs = bufs;
+    size_t sent = 0;
+    if (m.local) {
+        RTRT_CUDA(c, cudaStreamSynchronize(c.stream));                      // my rows are computed
+        m.local->barrier();
+        for (int s = 0; s < m.world; ++s) {
+            const int rows = p.recvStart[s + 1] - p.recvStart[s];
+            if (s == m.rank || rows == 0) continue;
+            Context* pc = m.local->members[s];
+            const XBufs& pb = multi_of(*pc)->curBufs;
+            for (int j = 0; j < bufs.n; ++j) {
+                const size_t off = (size_t)p.recvFirst[s] * bufs.rowBytes[j], bytes = (size_t)rows * bufs.rowBytes[j];
+                RTRT_CUDA(c, cudaMemcpyPeerAsync(bufs.ptr[j] + off, c.device, pb.ptr[j] + off, pc->device, bytes, c.stream));
+            }
+        }
+        RTRT_CUDA(c, cudaStreamSynchronize(c.stream));
+        m.local->barrier();
+    } else {
+        NcclApi& N = nccl_api();
+        RTRT_NCCL(c, N.GroupStart());
+        for (int d = 0; d < m.world; ++d) {
+            if (d == m.rank) continue;
+            const int sr = p.sendStart[d + 1] - p.sendStart[d], rr = p.recvStart[d + 1] - p.recvStart[d];
+            for (int j = 0; j < bufs.n; ++j) {
+                if (sr) RTRT_NCCL(c, N.Send(bufs.ptr[j] + (size_t)p.sendFirst[d] * bufs.rowBytes[j], (size_t)sr * bufs.rowBytes[j], ncclUint8, d, m.comm, c.stream));
+                if (rr) RTRT_NCCL(c, N.Recv(bufs.ptr[j] + (size_t)p.recvFirst[d] * bufs.rowBytes[j], (size_t)rr * bufs.rowBytes[j], ncclUint8, d, m.comm, c.stream));
+            }
+        }
+        RTRT_NCCL(c, N.GroupEnd());
+    }
+    for (int j = 0; j < bufs.n; ++j) sent += (size_t)p.sendTotal * bufs.rowBytes[j];
+    m.exchanges++; m.bytesSent += sent;
+    return RTRT_OK;
+}
+
 static int exchange(Context& c, Multi& m, int kind, int halo, XBufs bufs) {
     XPlan* p = nullptr;
     { int rc = get_plan(c, m, kind, halo, &p); if (rc) return rc; }
+    if (p->contiguous && RTRT_MULTI_DIRECT) return exchange_direct(c, m, *p, bufs);
     bufs.rowBytesAll = 0;
     bool wide16 = true;
     for (int j = 0; j < bufs.n; ++j) { bufs.rowBytesAll += bufs.rowBytes[j]; wide16 = wide16 && bufs.rowBytes[j] % 16 == 0 && (reinterpret_cast<uintptr_t>(bufs.ptr[j]) & 15) == 0; }
