@@ -33,6 +33,30 @@ __constant__ float cG3[9] = {0.0578968, 0.0921378, 0.0584323, 0.0921378, 0.14662
 __constant__ float cG5[25] = {0.00360466, 0.0144464, 0.0229902, 0.01458, 0.0036719, 0.0144464, 0.0578968, 0.0921378, 0.0584323, 0.0147159,
                               0.0229902, 0.0921378, 0.146629, 0.09299, 0.023419, 0.01458, 0.0584322, 0.0929898, 0.0589727, 0.014852,
                               0.00367191, 0.0147158, 0.0234191, 0.0148519, 0.0037404};
+// the same tables as compile-time constants: immediates in the fully unrolled tap loops (the __constant__ copies serve the rolled loops)
+__device__ constexpr float kG5[25] = {0.00360466, 0.0144464, 0.0229902, 0.01458, 0.0036719, 0.0144464, 0.0578968, 0.0921378, 0.0584323, 0.0147159,
+                                      0.0229902, 0.0921378, 0.146629, 0.09299, 0.023419, 0.01458, 0.0584322, 0.0929898, 0.0589727, 0.014852,
+                                      0.00367191, 0.0147158, 0.0234191, 0.0148519, 0.0037404};
+__device__ constexpr float kG7[49] = {3.47404e-05, 0.000353875, 0.00141822, 0.00225698, 0.00143134, 0.000360475, 3.57221e-05,
+                                      0.000353875, 0.00360466, 0.0144464, 0.0229902, 0.01458, 0.0036719, 0.000363875,
+                                      0.00141822, 0.0144464, 0.0578968, 0.0921378, 0.0584323, 0.0147159, 0.0014583,
+                                      0.00225698, 0.0229902, 0.0921378, 0.146629, 0.09299, 0.023419, 0.00232076,
+                                      0.00143134, 0.01458, 0.0584322, 0.0929898, 0.0589727, 0.014852, 0.00147179,
+                                      0.000360475, 0.00367191, 0.0147158, 0.0234191, 0.0148519, 0.0037404, 0.000370662,
+                                      3.57221e-05, 0.000363875, 0.0014583, 0.00232075, 0.00147179, 0.000370662, 3.67315e-05};
+// log2 of the tables (RTRT_DN_FMA: the Gaussian rides in the exponent)
+__device__ constexpr float kLg2G7[49] = {-14.8130264f, -11.4644728f, -9.4617033f, -8.79139042f, -9.44841766f, -11.4378128f, -14.7728233f,
+                                          -11.4644728f, -8.11592102f, -6.11314631f, -5.44283724f, -6.09986544f, -8.08925724f, -11.4242697f,
+                                          -9.4617033f, -6.11314631f, -4.11037254f, -3.440063f, -4.09709024f, -6.08648062f, -9.42149639f,
+                                          -8.79139042f, -5.44283724f, -3.440063f, -2.76975751f, -3.42678046f, -5.4161768f, -8.75118732f,
+                                          -9.44841766f, -6.09986544f, -4.09709263f, -3.42678356f, -4.0838089f, -6.0731988f, -9.40821266f,
+                                          -11.4378128f, -8.08925343f, -6.08649015f, -5.4161706f, -6.07320881f, -8.06259155f, -11.3976078f,
+                                          -14.7728233f, -11.4242697f, -9.42149639f, -8.75119305f, -9.40821266f, -11.3976078f, -14.7326231f};
+__device__ constexpr float kLg2G5[25] = {-8.11592102f, -6.11314631f, -5.44283724f, -6.09986544f, -8.08925724f,
+                                          -6.11314631f, -4.11037254f, -3.440063f, -4.09709024f, -6.08648062f,
+                                          -5.44283724f, -3.440063f, -2.76975751f, -3.42678046f, -5.4161768f,
+                                          -6.09986544f, -4.09709263f, -3.42678356f, -4.0838089f, -6.0731988f,
+                                          -8.08925343f, -6.08649015f, -5.4161706f, -6.07320881f, -8.06259155f};
 __constant__ float cG7[49] = {3.47404e-05, 0.000353875, 0.00141822, 0.00225698, 0.00143134, 0.000360475, 3.57221e-05,
                               0.000353875, 0.00360466, 0.0144464, 0.0229902, 0.01458, 0.0036719, 0.000363875,
                               0.00141822, 0.0144464, 0.0578968, 0.0921378, 0.0584323, 0.0147159, 0.0014583,
@@ -291,6 +315,43 @@ __global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_temporal(const DnParam
     block_noise_levels(P, sOut, sDepth, sN8, tid);
 }
 
+#ifndef RTRT_DN_FAST
+#define RTRT_DN_FAST 1          // tiles whose taps all lie inside the image: tap addresses = row pointer + immediate, no clamps, and the per-tap
+                                // NaN test of the colour moved behind the loop (a NaN tap makes the sum NaN: the pixel is then redone by the exact
+                                // loop).  Same operations in the same order for every pixel: results bit-identical with RTRT_DN_FAST 0.
+#endif
+#ifndef RTRT_DN_FMA
+#define RTRT_DN_FMA 0           // 1: fast path with explicit FMAs and the Gaussian folded into the exponent (NOT bit-identical; inside the 2e-2 tolerance)
+#endif
+
+// weight of the fast paths: RTRT_DN_FMA 0 = bilateral_weight (bit-identical with the exact loops); 1 = explicit FMAs, log2 of the Gaussian added
+// to the exponent, x^0 = 1 through the floor (max(dot, 1) -> log2 = 0) instead of a select
+VD float floor_eff(const BilateralK& k) { return (RTRT_DN_FMA && k.sigN == 0.0f) ? 1.0f : k.floorDot; }
+VD void tap_fast(ushort4 q, ushort4 gg, Float3 n0, float d0, unsigned short maskValue, const BilateralK& k, float floorEff, float g, float lg2g, Float3& sumC, float& sumW) {
+    const Float3 color = px_rgb(q), n1 = px_rgb(gg);
+#if RTRT_DN_FMA
+    const float dn = sel_max(fmaf(n0.z, n1.z, fmaf(n0.y, n1.y, n0.x * n1.x)), floorEff);
+    const float dd = (d0 - h2f(gg.w)) * k.invD;
+    const float e = fmaf(dd * dd, -0.72134752044448170368f, lg2g);
+    float w = fast_ex2(fmaf(k.sigN, fast_lg2(dn), e));
+    if (maskValue != q.w) w *= k.invM;
+    sumC = Float3{fmaf(color.x, w, sumC.x), fmaf(color.y, w, sumC.y), fmaf(color.z, w, sumC.z)}; sumW += w;
+#else
+    const float w = bilateral_weight(n0, n1, d0, h2f(gg.w), maskValue != q.w, k, g);
+    sumC = sumC + color * w; sumW += w;
+#endif
+}
+
+template <int PAR, int TP>
+VD void taps7(const ushort4* bC, const ushort4* bG, Float3 n0, float d0, unsigned short maskValue, const BilateralK& k, Float3& sumC, float& sumW) {
+    const float fe = floor_eff(k);
+#pragma unroll
+    for (int i = 0; i < 24; ++i) {
+        const int j = PAR + 2 * i, si = (j / 7) * TP + j % 7;
+        tap_fast(bC[si], bG[si], n0, d0, maskValue, k, fe, kG7[j], kLg2G7[j], sumC, sumW);
+    }
+}
+
 // -------------------------------------------------------------------------------------------------------------------
 // Pass B: SpatialFilter7x7 (24 of 49 taps, parity-alternating) + accumulation copy + tile noise of its output.
 // 16x16 pixels per CTA, 22x22 staged tile.  gate16 = noise level of the INPUT (written by the previous pass).
@@ -323,6 +384,13 @@ __global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial7(const DnParam
         if (!(depthValue >= kRayMax)) {
             const BilateralK bk = bilateral_k(P.local_n, P.local_d, P.local_m, 0.0001f);
             Float3 sumC = f3(0.0f); float sumW = 0.0f;
+#if RTRT_DN_FAST
+            // the 24 taps of either parity with compile-time offsets: shared-memory addresses = one base + immediate, Gaussian = immediate
+            const ushort4* bC = sC + threadIdx.y * TP + threadIdx.x + OX;
+            const ushort4* bG = sG + threadIdx.y * TP + threadIdx.x + OX;
+            if (P.frameNum % 2) taps7<1, TP>(bC, bG, normalValue, depthValue, maskValue, bk, sumC, sumW);
+            else taps7<0, TP>(bC, bG, normalValue, depthValue, maskValue, bk, sumC, sumW);
+#else
             int j = P.frameNum % 2;
 #pragma unroll 4
             for (int i = 0; i < 24; ++i) {
@@ -333,6 +401,7 @@ __global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial7(const DnParam
                 sumC = sumC + px_rgb(q) * w; sumW += w;
                 j += 2;
             }
+#endif
             if (isnan3(sumC)) sumC = f3(0.0f);
             if (sumW != sumW) sumW = 0.0f;
             Float3 fin = (sumW == 0.0f) ? f3(0.0f) : sumC / sumW;
@@ -354,6 +423,14 @@ __global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial7(const DnParam
 // -------------------------------------------------------------------------------------------------------------------
 // Pass C: SpatialFilterGlobal5x5<S>, S = 3, 6, 12 — dilated taps straight from global memory (L1/L2 resident).
 // -------------------------------------------------------------------------------------------------------------------
+// one tap exactly as the reference loop orders it (src/temporalDenoising.cuh:556-582): NaN colours drop out with their weight
+VD void tap5_exact(ushort4 q, ushort4 gg, Float3 normalValue, float depthValue, unsigned short maskValue, const BilateralK& bk, float g, Float3& sumC, float& sumW) {
+    Float3 color = px_rgb(q);
+    float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w, bk, g);
+    if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
+    sumC = sumC + color * w; sumW += w;
+}
+
 template <int S>
 __global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial5(const DnParams P, const ushort4* __restrict__ in, ushort4* __restrict__ out, const __half* __restrict__ gate16) {
     const int x = blockIdx.x * 16 + threadIdx.x, y = (blockIdx.y + P.by0) * 16 + threadIdx.y;
@@ -369,21 +446,38 @@ __global__ void __launch_bounds__(256, RTRT_DN_MINB) k_dn_spatial5(const DnParam
         if (!(depthValue >= 10e9f)) {
             const BilateralK bk = bilateral_k(P.large_n, P.large_d, P.large_m, 0.0f);
             Float3 sumC = f3(0.0f); float sumW = 0.0f;
-            // rows outside, columns inside, both fully unrolled: tap offsets and Gaussian weights are immediates, the row clamp and the
-            // row base are computed 5 times instead of 25 (same tap order k = 5 j + i as the reference loop)
+            // uniform per CTA: every tap of every pixel of the tile is inside the image
+            const int tx0 = blockIdx.x * 16, ty0 = (blockIdx.y + P.by0) * 16;
+            const bool interior = RTRT_DN_FAST && tx0 >= 2 * S && tx0 + 15 + 2 * S < P.W && ty0 >= 2 * S && ty0 + 15 + 2 * S < P.H;
+            bool redo = !interior;
+            if (interior) {
+                // rows outside, columns inside, both fully unrolled: the column offsets and the Gaussian weights are immediates, one pointer
+                // step per row and image (same tap order k = 5 j + i as the reference loop)
+                const ptrdiff_t rowStep = (ptrdiff_t)S * P.W;
+                const ushort4* rc = in + c - 2 * rowStep;
+                const ushort4* rg = P.guide + c - 2 * rowStep;
+                const float fe = floor_eff(bk);
 #pragma unroll
-            for (int j = 0; j < 5; ++j) {
-                const int sy = clampi(y + (j - 2) * S, 0, P.H - 1);
-                const size_t row = (size_t)sy * P.W;
+                for (int j = 0; j < 5; ++j) {
 #pragma unroll
-                for (int i = 0; i < 5; ++i) {
-                    const int sx = clampi(x + (i - 2) * S, 0, P.W - 1);
-                    const size_t g = row + sx;
-                    const ushort4 q = __ldg(in + g), gg = __ldg(P.guide + g);
-                    Float3 color = px_rgb(q);
-                    float w = bilateral_weight(normalValue, px_rgb(gg), depthValue, h2f(gg.w), maskValue != q.w, bk, cG5[5 * j + i]);
-                    if (isnan3(color)) { color = f3(0.0f); w = 0.0f; }
-                    sumC = sumC + color * w; sumW += w;
+                    for (int i = 0; i < 5; ++i)
+                        tap_fast(__ldg(rc + (i - 2) * S), __ldg(rg + (i - 2) * S), normalValue, depthValue, maskValue, bk, fe, kG5[5 * j + i], kLg2G5[5 * j + i], sumC, sumW);
+                    rc += rowStep; rg += rowStep;
+                }
+                redo = isnan3(sumC) || sumW != sumW;          // a NaN colour (or weight) somewhere: the exact loop decides what drops out
+            }
+            if (redo) {
+                sumC = f3(0.0f); sumW = 0.0f;
+#pragma unroll 1
+                for (int j = 0; j < 5; ++j) {
+                    const int sy = clampi(y + (j - 2) * S, 0, P.H - 1);
+                    const size_t row = (size_t)sy * P.W;
+#pragma unroll 1
+                    for (int i = 0; i < 5; ++i) {
+                        const int sx = clampi(x + (i - 2) * S, 0, P.W - 1);
+                        const size_t g = row + sx;
+                        tap5_exact(__ldg(in + g), __ldg(P.guide + g), normalValue, depthValue, maskValue, bk, cG5[5 * j + i], sumC, sumW);
+                    }
                 }
             }
             if (isnan3(sumC)) sumC = f3(0.0f);
