@@ -5,6 +5,23 @@ import pytest
 
 
 @pytest.mark.parametrize("H,world,strip", [(1080, 2, 8), (1080, 8, 8), (2160, 4, 8), (256, 3, 8), (270, 5, 16), (64, 4, 8)])
+def test_halo_and_frame_blocks_are_single_row_ranges(pkg, H, world, strip):
+    """What the direct (unpacked) exchange of csrc/multi.cu relies on: the rows one rank sends another for a halo exchange or the frame gather are
+    ONE range of consecutive rows (bands are contiguous), so they can travel image to image; the strip-interleaved G-buffer blocks are not."""
+    par = pkg.parallel
+    interleaved = False
+    for r in range(world):
+        for d in range(world):
+            for kind, halos in ((1, (1, 3, 6, 12, 24, 32)), (2, (0,))):
+                for halo in halos:
+                    s = par.plan_rows(H, world, strip, r, d, kind, halo)
+                    assert s.size == 0 or s[-1] - s[0] + 1 == s.size, (r, d, kind, halo)
+            s = par.plan_rows(H, world, strip, r, d, 0)
+            interleaved |= s.size > 0 and s[-1] - s[0] + 1 != s.size
+    assert interleaved or H // strip <= world
+
+
+@pytest.mark.parametrize("H,world,strip", [(1080, 2, 8), (1080, 8, 8), (2160, 4, 8), (256, 3, 8), (270, 5, 16), (64, 4, 8)])
 def test_plans_cover_exactly_what_each_rank_needs(pkg, H, world, strip):
     par = pkg.parallel
     bands = par.band_bounds(H, world)
