@@ -76,3 +76,44 @@ def tree_leaves(nodes, n):
                 stack.append(int(idx))
     assert visited == n - 1
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Golden vectors made by the reference's own kernels (tools/make_golden_refkernels.py -> tests/golden/refkernels_c1.npz):
+# the inputs are regenerated from these seeds on both sides, only the reference's outputs are stored.
+# ---------------------------------------------------------------------------------------------------------------------
+GOLDEN_W = GOLDEN_H = 48
+
+
+def golden_refkernels_inputs(pkg):
+    """BASELINE config 1 in miniature: the 10 240-triangle terrain, 64x48 primary rays + 1 000 incoherent rays, three 48x48 frames
+    (frames 1 and 2 from one camera, frame 3 from a moved one, each with the previous frame's camera as history camera)."""
+    pos, nrm, idx = pkg.scenes.terrain(*pkg.scenes.TERRAIN_SIZES["C1"], seed=1)
+    rays = pkg.scenes.primary_rays(pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, 64, 48), 64, 48)
+    rng = np.random.default_rng(7)
+    extra = np.zeros(1000, rays.dtype)
+    extra["orig"] = np.stack([rng.uniform(-50, 50, 1000), rng.uniform(5, 30, 1000), rng.uniform(-50, 50, 1000)], -1).astype(np.float32)
+    d = rng.normal(size=(1000, 3)).astype(np.float32); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    extra["dir"] = d
+    cams = [pkg.scenes.make_camera((0, 30, -60), 0.0, -0.4, GOLDEN_W, GOLDEN_H), pkg.scenes.make_camera((0.5, 30.2, -59.5), 0.02, -0.41, GOLDEN_W, GOLDEN_H)]
+    return {"pos": pos, "nrm": nrm, "idx": idx, "rays": np.concatenate([rays, extra]), "frames": [(1, cams[0]), (2, cams[0]), (3, cams[1])]}
+
+
+def golden_stage1_digests(b, node_dtype_fields=None):
+    """SHA-1 per observation point of a stage-1 result `b` (oracle Bvh or an object of the same shape): sorted Morton codes, reorder
+    indices, triangle vertices / normals, BLAS nodes (the 1 023 real nodes of every batch), top-level keys, order, boxes (bits) and nodes."""
+    import hashlib
+    B = b.num_batches
+    valid = np.zeros(B * 1024, bool)
+    for k in range(B):
+        valid[k * 1024: k * 1024 + 1023] = True
+    sha = lambda a: hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()
+    out = {"morton": sha(b.morton), "reorder_idx": sha(b.reorder_idx), "tlas_morton": sha(b.tlas_morton[:B]), "tlas_reorder_idx": sha(b.tlas_reorder_idx[:B])}
+    for f in ["v1", "v2", "v3", "n1", "n2", "n3"]:
+        out["triangles." + f] = sha(b.triangles[f])
+    for f in NODE_LINK_FIELDS + NODE_BOX_FIELDS:
+        out["nodes." + f] = sha(b.nodes[f][valid])
+        out["tlas_nodes." + f] = sha(b.tlas_nodes[f][:B - 1])
+    for f in ["min", "max"]:
+        out["tlas_aabbs." + f] = sha(b.tlas_aabbs[f][:B])
+    return out

@@ -1,6 +1,7 @@
 """CPU tests (-m "not gpu"): the oracle against known answers and against domain properties.
 
-The reference ships no golden vectors for this path (parity unpinned), so the oracle is pinned by
+The reference ships no golden vectors for this path; the oracle is pinned against the reference's own kernels (golden vectors made by
+them: tests/test_golden_refkernels_cpu.py; live on the GPU: tests/test_refcuda*_gpu.py).  This file adds
 (1) hand-computed known answers of the integer pieces, (2) structural invariants of the hierarchy,
 (3) a brute-force closest-hit over all triangles using the same watertight test.
 """
