@@ -112,7 +112,9 @@ __device__ __forceinline__ void wide_process(const WideBuildParams& p, const flo
     // so every maximal subtree of <= 8 items becomes ONE node whose slots are its items.  Pure largest-area opening gives 4.3 children per node
     // (3.3 triangles + 1.0 inner) on the bench scene, packing 5.3 — but packed triangles always sit one level lower, in nodes of their own, whereas the
     // mixed nodes of the greedy collapse let a ray test triangle boxes and inner boxes in one visit: measured slower (tools/gpu_r2w.sh).
+#if RTRT_WIDE_PACK_LEAVES
     const bool smallNode = (e.l - e.f + 1u) <= 8u;
+#endif
 #pragma unroll 1
     for (int it = 0; it < 6; ++it) {
 #if RTRT_WIDE_PACK_LEAVES
