@@ -690,6 +690,7 @@ def main():
     if not args.no_strong:
         strong = {}
         if mg is not None and not by_rows:
+          try:                                                     # sub-records never fail the bench line (an error every rank sees alike)
             mg.set_mode("rows")
             k = 0
             def rows_step():
@@ -714,8 +715,14 @@ def main():
                                              "16-row-aligned bands with an NCCL halo exchange before every filter pass, frame gather (rtrt_render_frame_multi, rows mode)",
                                  "scaling": "strong", "steps": n_rows_steps, "ms_per_step": tt.item() / n_rows_steps,
                                  "mrays_s": rr.item() / (tt.item() * 1e-3) / 1e6, "rank0_band": list(band[:2])}
+          except Exception as e:
+            strong["c2_rows"] = {"unavailable": repr(e)}
+          finally:
             mg.set_mode("samples")
-        strong["c5_64spp"] = strong_c5(args, pkg, torch, dist, rank, world, local, make_group)
+        try:
+            strong["c5_64spp"] = strong_c5(args, pkg, torch, dist, rank, world, local, make_group)
+        except Exception as e:
+            strong["c5_64spp"] = {"unavailable": repr(e)}
     configs = None
     if world == 1 and not args.no_configs:
         try:
